@@ -1,0 +1,122 @@
+"""ctypes binding of libarcb200.so (include/arcb200.h).
+
+The product path has NO fallback: if the shared library is missing or a call fails, a RuntimeError is
+raised.  Nothing here imports oracle/.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, 'libarcb200.so')
+
+P = C.c_void_p      # device or host pointer
+I = C.c_int
+L = C.c_int64
+F = C.c_float
+U64 = C.c_uint64
+
+# name -> argtypes (all return int unless listed in _RESTYPE)
+_SIGS = {
+    'arcb200_version': [],
+    'arcb200_last_error': [],
+    'arcb200_device_count': [],
+    'arcb200_rng_init': [U64, C.POINTER(U64), C.POINTER(U64)],
+    'arcb200_rng_advance': [C.POINTER(U64), U64, L],
+    'arcb200_aabb_intersection': [P, P, P, P, P, P, P, L, L, P],
+    'arcb200_check_pts_in_occ_voxel': [P, P, P, I, P, L, P],
+    'arcb200_sparse_volume_sampling': [P, P, P, P, I, F, P, I, P, F, P, P, L, U64, U64, P],
+    'arcb200_sparse_volume_sampling_bit': [P, P, P, P, I, F, P, I, P, F, P, P, L, U64, U64, P],
+    'arcb200_tensor_reduce_max': [P, P, I, P, L, P],
+    'arcb200_generate_grid_samples': [P, I, L, I, F, P, P, U64, U64, P],
+    'arcb200_splat_grid_samples': [P, P, L, P, P],
+    'arcb200_ema_grid_samples_nerf': [P, L, F, P, P],
+    'arcb200_update_bitfield': [P, F, P, P, F, L, P],
+    'arcb200_count_bitfield': [P, P, L, I, P],
+    'arcb200_sparse_sampling_in_multivol_bitfield': [P, P, P, P, I, F, F, F, P, P, I, I, P, F, I, P, P, L, U64, U64, P],
+    'arcb200_generate_grid_samples_multivol': [P, I, L, P, I, I, F, I, P, P, U64, U64, P],
+    'arcb200_march_packed_scratch_bytes': [L, I],
+    'arcb200_march_packed': [I, P, P, P, P, I, F, P, I, P, F, L, U64, U64, P, P, P, P, L, P, P, P, P],
+}
+_RESTYPE = {
+    'arcb200_last_error': C.c_char_p,
+    'arcb200_rng_init': None,
+    'arcb200_rng_advance': None,
+    'arcb200_march_packed_scratch_bytes': L,
+}
+
+_lib = None
+
+
+def load():
+    """Load libarcb200.so; raises RuntimeError if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            'libarcb200.so not found at %s: build it with `python -m arcnerf_b200.build` '
+            '(there is no CPU or PyTorch fallback for this path)' % LIB_PATH)
+    lib = C.CDLL(LIB_PATH)
+    for name, args in _SIGS.items():
+        try:
+            fn = getattr(lib, name)
+        except AttributeError:
+            continue  # entry point of a later source file that is not in this build
+        fn.argtypes = args
+        fn.restype = _RESTYPE.get(name, I)
+    _lib = lib
+    return lib
+
+
+def register(name, argtypes, restype=I):
+    """Used by host modules that add entry points (keeps the table next to its caller)."""
+    _SIGS[name] = argtypes
+    if restype is not I:
+        _RESTYPE[name] = restype
+    if _lib is not None:
+        fn = getattr(_lib, name)
+        fn.argtypes = argtypes
+        fn.restype = restype
+
+
+def last_error():
+    msg = load().arcb200_last_error()
+    return msg.decode() if msg else ''
+
+
+def call(name, *args):
+    """Invoke an int-returning entry point; a negative return raises RuntimeError (the reference's
+    pybind layer raises RuntimeError from TORCH_CHECK / std::runtime_error, arcnerf/ops/include/utils.h:17-27)."""
+    lib = load()
+    fn = getattr(lib, name, None)
+    if fn is None:
+        raise RuntimeError('libarcb200.so does not export %s (stale build?)' % name)
+    rc = fn(*args)
+    if rc is not None and rc < 0:
+        raise RuntimeError('%s failed (%d): %s' % (name, rc, last_error()))
+    return rc
+
+
+def ptr(t):
+    """Device pointer of a torch tensor (None -> NULL)."""
+    return None if t is None else t.data_ptr()
+
+
+def current_stream():
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+class Rng:
+    """Caller-held pcg32 state matching the reference's per-module `static pcg32 rng{9121}`."""
+    SEED = 9121
+
+    def __init__(self, seed=SEED):
+        s, i = U64(), U64()
+        load().arcb200_rng_init(U64(seed), C.byref(s), C.byref(i))
+        self.state, self.inc = s.value, i.value
+
+    def advance(self, delta=1 << 32):
+        s = U64(self.state)
+        load().arcb200_rng_advance(C.byref(s), U64(self.inc), L(delta))
+        self.state = s.value
