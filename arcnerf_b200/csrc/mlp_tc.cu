@@ -1,0 +1,571 @@
+// Small fully-fused MLP (tiny-cuda-nn "FullyFusedMLP": no biases, 16-multiple widths) on the Blackwell tensor
+// cores: tcgen05.mma with fp16 operands in shared memory, fp32 accumulators in tensor memory (TMEM), weights
+// staged once per CTA by the TMA engine (1-D bulk copy), activations never leaving the SM between layers.
+//
+// Semantics: /root/reference/include/tiny-cuda-nn/src/fully_fused_mlp.cu (kernel_mlp_fused :499-557, layer
+// order and weight layout :658-671, backward :150-259 + split-k weight gradients :781-822), as driven by
+// ArcNerf's FusedMLPGeoNet / FusedMLPRadianceNet (tcnn_fusedmlp_module.py:66-77,162-173):
+//   y = act_out( W_last . act( ... act( W_0 . x ) ) ), weights row-major (out x in), input layer first,
+//   the last matrix padded to 16 rows; inputs narrower than a multiple of 16 are padded with ONES
+//   (encodings/identity.h:63-64), so the pad columns of W_0 act as trainable biases.
+// Precision: fp16 weights and activations like the reference, but fp32 accumulation (the reference accumulates
+// in fp16 inside wmma, fully_fused_mlp.cu:68).
+//
+// Kernel shape: one CTA = 128 threads = one 128-row tile at a time (thread r owns row r = TMEM lane r);
+// persistent grid-stride loop over tiles.  Per layer: one elected thread issues K/16 tcgen05.mma
+// (M=128, N=layer width), commits to an mbarrier; all threads then pull their accumulator row out of TMEM
+// (tcgen05.ld 32x32b), apply the activation and write the fp16 row back into the shared-memory operand tile of
+// the next layer.  The backward kernel re-computes the forward activations (tensor-core FLOPs are cheaper than
+// an HBM round trip for them), chains the data gradients the same way and accumulates the weight gradients
+// dW = G^T . H over ALL tiles of the CTA in TMEM (batch = contraction dimension, operands read MN-major from the
+// very same tiles), flushing them once per CTA with fp32 atomics.
+#include "common.cuh"
+#include "tc05.cuh"
+
+namespace {
+
+constexpr int kMaxMM = 4;            // matmuls per network (hidden layers + 1)
+constexpr int kRows = 128;           // rows per tile
+constexpr uint32_t kTileLBO = kRows * 16;   // column-group stride of a 128-row tile (bytes)
+
+enum Act { ACT_NONE = 0, ACT_RELU = 1, ACT_SIGMOID = 2, ACT_SOFTPLUS = 3, ACT_EXP = 4 };
+
+struct MlpCfg {
+    int n_mm;              // number of matmuls
+    int in_dim, in_pad;    // real and 16-padded input width
+    int width;             // hidden width (64 or 128 for training; 16..128 forward)
+    int out_dim, out_pad;  // real and 16-padded output width
+    int hidden_act, out_act;
+    int K[kMaxMM], N[kMaxMM];
+    uint32_t w_off[kMaxMM];   // byte offset of layer l's weight tile in the packed blob
+    uint32_t w_bytes;         // blob size
+    uint32_t p_off[kMaxMM];   // element offset of layer l in the flat parameter vector
+};
+
+__device__ __forceinline__ float act_fwd(int a, float x) {
+    switch (a) {
+        case ACT_RELU: return x > 0.f ? x : 0.f;
+        case ACT_SIGMOID: return 1.0f / (1.0f + __expf(-x));
+        case ACT_SOFTPLUS: return __logf(__expf(x * 10.0f) + 1.0f) / 10.0f;
+        case ACT_EXP: return __expf(x);
+        default: return x;
+    }
+}
+// derivative expressed through the activation OUTPUT y (as the reference does, common_device.h:180-225)
+__device__ __forceinline__ float act_bwd(int a, float y) {
+    switch (a) {
+        case ACT_RELU: return y > 0.f ? 1.f : 0.f;
+        case ACT_SIGMOID: return y * (1.0f - y);
+        case ACT_SOFTPLUS: return 1.0f - __expf(-y * 10.0f);
+        case ACT_EXP: return y;
+        default: return 1.f;
+    }
+}
+
+template <typename T> __device__ __forceinline__ float ld_f32(const T *p);
+template <> __device__ __forceinline__ float ld_f32<float>(const float *p) { return __ldg(p); }
+template <> __device__ __forceinline__ float ld_f32<__half>(const __half *p) { return __half2float(__ldg(p)); }
+template <typename T> __device__ __forceinline__ void st_val(T *p, float v);
+template <> __device__ __forceinline__ void st_val<float>(float *p, float v) { *p = v; }
+template <> __device__ __forceinline__ void st_val<__half>(__half *p, float v) { *p = __float2half_rn(v); }
+
+// 16-byte word of row `r`, column group `cg` in a 128-row core-matrix tile
+__device__ __forceinline__ uint4 *tile_word(uint8_t *tile, int r, int cg) {
+    return reinterpret_cast<uint4 *>(tile + (size_t)cg * kTileLBO + (size_t)r * 16);
+}
+
+// Row `grow` of X (fp32 or fp16, leading dimension ldx) -> fp16 row r of the tile; columns >= in_dim are 1.0
+// (the reference's identity-encoding padding), rows beyond n are zero.
+template <typename TIN>
+__device__ __forceinline__ void load_input_row(uint8_t *tile, int r, const TIN *__restrict__ X, int64_t ldx, int64_t grow,
+                                               int64_t n, int in_dim, int in_pad) {
+    for (int cg = 0; cg < in_pad / 8; ++cg) {
+        float v[8];
+        #pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const int c = cg * 8 + k;
+            v[k] = (grow < n) ? (c < in_dim ? ld_f32<TIN>(X + grow * ldx + c) : 1.0f) : 0.0f;
+        }
+        uint4 w;
+        w.x = tc05::pack_half2(v[0], v[1]); w.y = tc05::pack_half2(v[2], v[3]);
+        w.z = tc05::pack_half2(v[4], v[5]); w.w = tc05::pack_half2(v[6], v[7]);
+        *tile_word(tile, r, cg) = w;
+    }
+}
+
+// A (128 x K, K-major tile) . B^T with B = weight tile (N rows x K cols, K-major)  ->  TMEM (128 x N)
+__device__ __forceinline__ void issue_forward_mm(uint32_t tmem_d, uint32_t a_tile, uint32_t w_tile, int K, int N) {
+    const uint32_t idesc = tc05::make_idesc(128, (uint32_t)N, 0, 0);
+    const uint32_t w_lbo = (uint32_t)N * 16;
+    for (int k = 0; k < K / 16; ++k) {
+        const uint64_t da = tc05::make_desc(a_tile + (uint32_t)k * 2 * kTileLBO, kTileLBO, 128);
+        const uint64_t db = tc05::make_desc(w_tile + (uint32_t)k * 2 * w_lbo, w_lbo, 128);
+        tc05::mma_f16_ss(tmem_d, da, db, idesc, k > 0);
+    }
+}
+// data gradient: G (128 x N, K-major tile) . W (N rows x K cols, read MN-major: "N" index = input column) -> (128 x K)
+__device__ __forceinline__ void issue_dgrad_mm(uint32_t tmem_d, uint32_t g_tile, uint32_t w_tile, int K, int N) {
+    const uint32_t idesc = tc05::make_idesc(128, (uint32_t)K, 0, 1);
+    const uint32_t w_sbo = (uint32_t)N * 16;     // stride between 8-column groups of the weight tile
+    for (int k = 0; k < N / 16; ++k) {
+        const uint64_t da = tc05::make_desc(g_tile + (uint32_t)k * 2 * kTileLBO, kTileLBO, 128);
+        const uint64_t db = tc05::make_desc(w_tile + (uint32_t)k * 256, 128, w_sbo);
+        tc05::mma_f16_ss(tmem_d, da, db, idesc, k > 0);
+    }
+}
+// weight gradient: P^T . Q over the 128 rows of the tile, P (128 x M) and Q (128 x N) both read MN-major -> (M x N)
+__device__ __forceinline__ void issue_wgrad_mm(uint32_t tmem_d, uint32_t p_tile, uint32_t q_tile, int M, int N, bool accumulate) {
+    const uint32_t idesc = tc05::make_idesc((uint32_t)M, (uint32_t)N, 1, 1);
+    for (int k = 0; k < kRows / 16; ++k) {
+        const uint64_t da = tc05::make_desc(p_tile + (uint32_t)k * 256, 128, kTileLBO);
+        const uint64_t db = tc05::make_desc(q_tile + (uint32_t)k * 256, 128, kTileLBO);
+        tc05::mma_f16_ss(tmem_d, da, db, idesc, (accumulate || k > 0) ? 1u : 0u);
+    }
+}
+
+struct Shared {
+    uint64_t mbar_w;
+    uint64_t mbar_mma;
+    uint32_t tmem_base;
+    uint32_t pad;
+};
+
+// ---------------------------------------------------------------------------------------------- forward
+template <typename TIN, typename TOUT, uint32_t TMEM_COLS>
+__global__ void __launch_bounds__(kRows)
+mlp_fwd_kernel(int64_t n, const TIN *__restrict__ X, int64_t ldx, const uint8_t *__restrict__ blob, MlpCfg cfg,
+               TOUT *__restrict__ Y, int64_t ldy) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    Shared *sh = reinterpret_cast<Shared *>(smem);
+    uint8_t *w_s = smem + 128;
+    uint8_t *a_s = w_s + ((cfg.w_bytes + 127u) & ~127u);
+    const int tid = threadIdx.x, warp = tid >> 5;
+
+    if (tid == 32) {
+        tc05::mbar_init(&sh->mbar_w, 1);
+        tc05::mbar_init(&sh->mbar_mma, 1);
+        tc05::fence_mbar_init();
+    }
+    if (warp == 0) tc05::tmem_alloc<TMEM_COLS>(&sh->tmem_base);
+    tc05::fence_before_sync();
+    __syncthreads();
+    tc05::fence_after_sync();
+    const uint32_t tmem = sh->tmem_base;
+    if (tid == 0) {
+        tc05::mbar_expect_tx(&sh->mbar_w, cfg.w_bytes);
+        tc05::bulk_g2s(w_s, blob, cfg.w_bytes, &sh->mbar_w);
+    }
+    const uint32_t a_addr = tc05::smem_u32(a_s), w_addr = tc05::smem_u32(w_s);
+    const uint32_t my_tmem = tmem + ((uint32_t)(warp * 32) << 16);
+    uint32_t phase = 0;
+    bool weights_ready = false;
+
+    const int64_t n_tiles = (n + kRows - 1) / kRows;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t grow = tile * kRows + tid;
+        load_input_row<TIN>(a_s, tid, X, ldx, grow, n, cfg.in_dim, cfg.in_pad);
+        if (!weights_ready) { tc05::mbar_wait(&sh->mbar_w, 0); weights_ready = true; }
+        for (int l = 0; l < cfg.n_mm; ++l) {
+            tc05::fence_proxy_async();
+            tc05::fence_before_sync();
+            __syncthreads();
+            if (tid == 0) {
+                tc05::fence_after_sync();
+                issue_forward_mm(tmem, a_addr, w_addr + cfg.w_off[l], cfg.K[l], cfg.N[l]);
+                tc05::mma_commit(&sh->mbar_mma);
+            }
+            tc05::mbar_wait(&sh->mbar_mma, phase);
+            phase ^= 1u;
+            tc05::fence_after_sync();
+            const bool last = (l == cfg.n_mm - 1);
+            const int act = last ? cfg.out_act : cfg.hidden_act;
+            for (int cb = 0; cb < cfg.N[l] / 16; ++cb) {
+                uint32_t r[16];
+                tc05::tmem_ld16(my_tmem + (uint32_t)cb * 16, r);
+                tc05::tmem_ld_wait();
+                float v[16];
+                #pragma unroll
+                for (int k = 0; k < 16; ++k) v[k] = act_fwd(act, __uint_as_float(r[k]));
+                if (!last) {
+                    uint4 w0, w1;
+                    w0.x = tc05::pack_half2(v[0], v[1]);   w0.y = tc05::pack_half2(v[2], v[3]);
+                    w0.z = tc05::pack_half2(v[4], v[5]);   w0.w = tc05::pack_half2(v[6], v[7]);
+                    w1.x = tc05::pack_half2(v[8], v[9]);   w1.y = tc05::pack_half2(v[10], v[11]);
+                    w1.z = tc05::pack_half2(v[12], v[13]); w1.w = tc05::pack_half2(v[14], v[15]);
+                    *tile_word(a_s, tid, 2 * cb) = w0;
+                    *tile_word(a_s, tid, 2 * cb + 1) = w1;
+                } else if (grow < n) {
+                    #pragma unroll
+                    for (int k = 0; k < 16; ++k) {
+                        const int c = cb * 16 + k;
+                        if (c < cfg.out_dim) st_val<TOUT>(Y + grow * ldy + c, v[k]);
+                    }
+                }
+            }
+        }
+    }
+    tc05::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc05::tmem_dealloc<TMEM_COLS>(tmem);
+}
+
+// ---------------------------------------------------------------------------------------------- backward
+// TMEM columns: [0, act_cols) data tile of the layer in flight; then one weight-gradient accumulator per layer.
+struct BwdPlan {
+    int wg_m[kMaxMM], wg_n[kMaxMM];   // accumulator shape; wg_t = 1: it holds dW^T (M = input columns)
+    int wg_t[kMaxMM];
+    uint32_t wg_col[kMaxMM];
+    uint32_t act_cols;
+};
+
+template <typename TIN, typename TGX, uint32_t TMEM_COLS>
+__global__ void __launch_bounds__(kRows)
+mlp_bwd_kernel(int64_t n, const TIN *__restrict__ X, int64_t ldx, const uint8_t *__restrict__ blob, MlpCfg cfg,
+               BwdPlan plan, const float *__restrict__ dY, int64_t ldy, float loss_scale, TGX *__restrict__ dX,
+               int64_t ldgx, float *__restrict__ dW) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    Shared *sh = reinterpret_cast<Shared *>(smem);
+    uint8_t *w_s = smem + 128;
+    uint8_t *x_s = w_s + ((cfg.w_bytes + 127u) & ~127u);                  // 128 x in_pad
+    uint8_t *h_s = x_s + (size_t)kRows * cfg.in_pad * 2;                  // (n_mm-1) tiles of 128 x width
+    uint8_t *g_s = h_s + (size_t)(cfg.n_mm - 1) * kRows * cfg.width * 2;  // 128 x max(width, out_pad)
+    const size_t h_bytes = (size_t)kRows * cfg.width * 2;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (tid == 32) {
+        tc05::mbar_init(&sh->mbar_w, 1);
+        tc05::mbar_init(&sh->mbar_mma, 1);
+        tc05::fence_mbar_init();
+    }
+    if (warp == 0) tc05::tmem_alloc<TMEM_COLS>(&sh->tmem_base);
+    tc05::fence_before_sync();
+    __syncthreads();
+    tc05::fence_after_sync();
+    const uint32_t tmem = sh->tmem_base;
+    if (tid == 0) {
+        tc05::mbar_expect_tx(&sh->mbar_w, cfg.w_bytes);
+        tc05::bulk_g2s(w_s, blob, cfg.w_bytes, &sh->mbar_w);
+    }
+    const uint32_t w_addr = tc05::smem_u32(w_s), x_addr = tc05::smem_u32(x_s), h_addr = tc05::smem_u32(h_s),
+                   g_addr = tc05::smem_u32(g_s);
+    const uint32_t my_tmem = tmem + ((uint32_t)(warp * 32) << 16);
+    uint32_t phase = 0;
+    bool weights_ready = false, first_tile = true;
+    const float inv_scale = 1.0f / loss_scale;
+
+    auto sync_issue_wait = [&](auto issue) {
+        tc05::fence_proxy_async();
+        tc05::fence_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            tc05::fence_after_sync();
+            issue();
+            tc05::mma_commit(&sh->mbar_mma);
+        }
+        tc05::mbar_wait(&sh->mbar_mma, phase);
+        phase ^= 1u;
+        tc05::fence_after_sync();
+    };
+    auto store16 = [&](uint8_t *tile, int cb, const float (&v)[16]) {
+        uint4 w0, w1;
+        w0.x = tc05::pack_half2(v[0], v[1]);   w0.y = tc05::pack_half2(v[2], v[3]);
+        w0.z = tc05::pack_half2(v[4], v[5]);   w0.w = tc05::pack_half2(v[6], v[7]);
+        w1.x = tc05::pack_half2(v[8], v[9]);   w1.y = tc05::pack_half2(v[10], v[11]);
+        w1.z = tc05::pack_half2(v[12], v[13]); w1.w = tc05::pack_half2(v[14], v[15]);
+        *tile_word(tile, tid, 2 * cb) = w0;
+        *tile_word(tile, tid, 2 * cb + 1) = w1;
+    };
+
+    const int64_t n_tiles = (n + kRows - 1) / kRows;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t grow = tile * kRows + tid;
+        load_input_row<TIN>(x_s, tid, X, ldx, grow, n, cfg.in_dim, cfg.in_pad);
+        if (!weights_ready) { tc05::mbar_wait(&sh->mbar_w, 0); weights_ready = true; }
+
+        // ---- forward re-computation; hidden activations stay in shared memory
+        for (int l = 0; l < cfg.n_mm; ++l) {
+            const uint32_t a_tile = l == 0 ? x_addr : h_addr + (uint32_t)((l - 1) * h_bytes);
+            sync_issue_wait([&] { issue_forward_mm(tmem, a_tile, w_addr + cfg.w_off[l], cfg.K[l], cfg.N[l]); });
+            const bool last = (l == cfg.n_mm - 1);
+            for (int cb = 0; cb < cfg.N[l] / 16; ++cb) {
+                uint32_t r[16];
+                tc05::tmem_ld16(my_tmem + (uint32_t)cb * 16, r);
+                tc05::tmem_ld_wait();
+                float v[16];
+                if (!last) {
+                    #pragma unroll
+                    for (int k = 0; k < 16; ++k) v[k] = act_fwd(cfg.hidden_act, __uint_as_float(r[k]));
+                    store16(h_s + (size_t)l * h_bytes, cb, v);
+                } else {
+                    // gradient w.r.t. the last pre-activation, scaled; padded outputs and rows carry none
+                    #pragma unroll
+                    for (int k = 0; k < 16; ++k) {
+                        const int c = cb * 16 + k;
+                        const float y = act_fwd(cfg.out_act, __uint_as_float(r[k]));
+                        const float g = (grow < n && c < cfg.out_dim) ? __ldg(dY + grow * ldy + c) : 0.0f;
+                        v[k] = g * act_bwd(cfg.out_act, y) * loss_scale;
+                    }
+                    store16(g_s, cb, v);
+                }
+            }
+        }
+
+        // ---- backward chain
+        for (int l = cfg.n_mm - 1; l >= 0; --l) {
+            const uint32_t in_tile = l == 0 ? x_addr : h_addr + (uint32_t)((l - 1) * h_bytes);
+            const bool need_dgrad = (l > 0) || (dX != nullptr);
+            sync_issue_wait([&] {
+                if (plan.wg_t[l]) issue_wgrad_mm(tmem + plan.wg_col[l], in_tile, g_addr, plan.wg_m[l], plan.wg_n[l], !first_tile);
+                else issue_wgrad_mm(tmem + plan.wg_col[l], g_addr, in_tile, plan.wg_m[l], plan.wg_n[l], !first_tile);
+                if (need_dgrad) issue_dgrad_mm(tmem, g_addr, w_addr + cfg.w_off[l], cfg.K[l], cfg.N[l]);
+            });
+            if (!need_dgrad) continue;
+            for (int cb = 0; cb < cfg.K[l] / 16; ++cb) {
+                uint32_t r[16];
+                tc05::tmem_ld16(my_tmem + (uint32_t)cb * 16, r);
+                tc05::tmem_ld_wait();
+                float v[16];
+                if (l > 0) {
+                    // through the hidden activation of layer l-1 (derivative from its stored output)
+                    const uint8_t *hp = h_s + (size_t)(l - 1) * h_bytes;
+                    const uint4 a = *tile_word(const_cast<uint8_t *>(hp), tid, 2 * cb);
+                    const uint4 b = *tile_word(const_cast<uint8_t *>(hp), tid, 2 * cb + 1);
+                    const uint32_t hw[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+                    #pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const float2 h2 = __half22float2(*reinterpret_cast<const __half2 *>(&hw[k]));
+                        v[2 * k] = __uint_as_float(r[2 * k]) * act_bwd(cfg.hidden_act, h2.x);
+                        v[2 * k + 1] = __uint_as_float(r[2 * k + 1]) * act_bwd(cfg.hidden_act, h2.y);
+                    }
+                    store16(g_s, cb, v);
+                } else if (grow < n) {
+                    #pragma unroll
+                    for (int k = 0; k < 16; ++k) {
+                        const int c = cb * 16 + k;
+                        if (c < cfg.in_dim) st_val<TGX>(dX + grow * ldgx + c, __uint_as_float(r[k]) * inv_scale);
+                    }
+                }
+            }
+        }
+        first_tile = false;
+    }
+
+    // ---- flush the weight-gradient accumulators of this CTA
+    tc05::fence_before_sync();
+    __syncthreads();
+    tc05::fence_after_sync();
+    if (!first_tile) {
+        for (int l = 0; l < cfg.n_mm; ++l) {
+            const int M = plan.wg_m[l], Nn = plan.wg_n[l];
+            // M = 128: row = TMEM lane; M = 64: row 16*w + lane lives in lane 32*w + lane (lanes 0..15 of each warp)
+            const int row = (M == 128) ? tid : (warp * 16 + lane);
+            const bool owner = (M == 128) || (lane < 16);
+            float *dst = dW + cfg.p_off[l];
+            for (int cb = 0; cb < Nn / 16; ++cb) {
+                uint32_t r[16];
+                tc05::tmem_ld16(my_tmem + plan.wg_col[l] + (uint32_t)cb * 16, r);
+                tc05::tmem_ld_wait();
+                if (!owner) continue;
+                #pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    const int col = cb * 16 + k;
+                    const float g = __uint_as_float(r[k]) * inv_scale;
+                    // plain: acc[out][in]; transposed: acc[in][out]; parameters are (out x in) row-major
+                    const int o = plan.wg_t[l] ? col : row, i = plan.wg_t[l] ? row : col;
+                    if (g != 0.0f) atomicAdd(dst + (size_t)o * cfg.K[l] + i, g);
+                }
+            }
+        }
+    }
+    tc05::fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tc05::tmem_dealloc<TMEM_COLS>(tmem);
+}
+
+// fp32 flat parameters (out x in row-major per layer) -> fp16 core-matrix tiles (see tc05.cuh)
+__global__ void pack_weights_kernel(MlpCfg cfg, const float *__restrict__ params, uint8_t *__restrict__ blob) {
+    const int l = blockIdx.y;
+    if (l >= cfg.n_mm) return;
+    const int K = cfg.K[l], N = cfg.N[l];
+    for (int e = blockIdx.x * blockDim.x + threadIdx.x; e < K * N; e += gridDim.x * blockDim.x) {
+        const int r = e / K, c = e - r * K;
+        __half *tile = reinterpret_cast<__half *>(blob + cfg.w_off[l]);
+        tile[(size_t)(c >> 3) * (N * 8) + (size_t)r * 8 + (c & 7)] = __float2half_rn(params[cfg.p_off[l] + e]);
+    }
+}
+
+int make_cfg(MlpCfg &c, int in_dim, int width, int n_hidden, int out_dim, int hidden_act, int out_act) {
+    if (n_hidden < 1 || n_hidden + 1 > kMaxMM) return -1;
+    if (width % 16 != 0 || width < 16 || width > 128) return -1;
+    if (in_dim < 1 || out_dim < 1) return -1;
+    c.n_mm = n_hidden + 1;
+    c.in_dim = in_dim;
+    c.in_pad = (in_dim + 15) / 16 * 16;
+    c.width = width;
+    c.out_dim = out_dim;
+    c.out_pad = (out_dim + 15) / 16 * 16;
+    if (c.in_pad > 128 || c.out_pad > 128) return -1;
+    c.hidden_act = hidden_act;
+    c.out_act = out_act;
+    uint32_t off = 0, poff = 0;
+    for (int l = 0; l < c.n_mm; ++l) {
+        c.K[l] = l == 0 ? c.in_pad : width;
+        c.N[l] = l == c.n_mm - 1 ? c.out_pad : width;
+        c.w_off[l] = off;
+        c.p_off[l] = poff;
+        off += (uint32_t)c.K[l] * c.N[l] * 2;
+        poff += (uint32_t)c.K[l] * c.N[l];
+    }
+    c.w_bytes = off;
+    return (int)poff;
+}
+
+int make_plan(const MlpCfg &c, BwdPlan &p) {
+    uint32_t act_cols = 16;
+    for (int l = 0; l < c.n_mm; ++l) { act_cols = max(act_cols, (uint32_t)c.N[l]); act_cols = max(act_cols, (uint32_t)c.K[l]); }
+    p.act_cols = act_cols;
+    uint32_t col = act_cols;
+    for (int l = 0; l < c.n_mm; ++l) {
+        if (c.N[l] == 64 || c.N[l] == 128) { p.wg_t[l] = 0; p.wg_m[l] = c.N[l]; p.wg_n[l] = c.K[l]; }
+        else if (c.K[l] == 64 || c.K[l] == 128) { p.wg_t[l] = 1; p.wg_m[l] = c.K[l]; p.wg_n[l] = c.N[l]; }
+        else return -1;
+        p.wg_col[l] = col;
+        col += (uint32_t)p.wg_n[l];
+    }
+    return (int)col;
+}
+
+static size_t fwd_smem(const MlpCfg &c) {
+    const int maxk = c.in_pad > c.width ? c.in_pad : c.width;
+    return 128 + ((c.w_bytes + 127u) & ~127u) + (size_t)kRows * maxk * 2;
+}
+static size_t bwd_smem(const MlpCfg &c) {
+    const int gw = c.width > c.out_pad ? c.width : c.out_pad;
+    return 128 + ((c.w_bytes + 127u) & ~127u) + (size_t)kRows * c.in_pad * 2 + (size_t)(c.n_mm - 1) * kRows * c.width * 2 +
+           (size_t)kRows * gw * 2;
+}
+
+template <typename K>
+static int set_smem(K kernel, size_t bytes) {
+    if (bytes > 227 * 1024) { arcb200_set_error("mlp: %zu bytes of shared memory needed, 227 KB available", bytes); return ARCB200_ERR_LIMIT; }
+    cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e != cudaSuccess) { arcb200_set_error("cudaFuncSetAttribute -> %s", cudaGetErrorString(e)); return ARCB200_ERR_CUDA; }
+    return ARCB200_OK;
+}
+
+static unsigned mlp_grid(int64_t n, size_t smem_bytes, uint32_t tmem_cols) {
+    const int64_t tiles = (n + kRows - 1) / kRows;
+    int per_sm = (int)((227 * 1024) / (smem_bytes + 1024));
+    const int by_tmem = (int)(512 / tmem_cols);
+    if (per_sm > by_tmem) per_sm = by_tmem;
+    if (per_sm > 8) per_sm = 8;
+    if (per_sm < 1) per_sm = 1;
+    const int64_t cap = (int64_t)arc_sm_count() * per_sm;
+    return (unsigned)(tiles < cap ? tiles : cap);
+}
+
+}  // namespace
+
+extern "C" {
+
+// Number of parameters (elements of the flat fp32 vector) of the network, tcnn layout; negative on a bad shape.
+int arcb200_mlp_n_params(int in_dim, int width, int n_hidden, int out_dim) {
+    MlpCfg c;
+    const int n = make_cfg(c, in_dim, width, n_hidden, out_dim, 0, 0);
+    if (n < 0) arcb200_set_error("mlp: unsupported shape (width multiple of 16 in [16,128], 1..3 hidden layers, dims <= 128)");
+    return n;
+}
+
+// Bytes of the packed fp16 weight blob produced by arcb200_mlp_pack_weights.
+int arcb200_mlp_blob_bytes(int in_dim, int width, int n_hidden, int out_dim) {
+    MlpCfg c;
+    if (make_cfg(c, in_dim, width, n_hidden, out_dim, 0, 0) < 0) return ARCB200_ERR_ARG;
+    return (int)c.w_bytes;
+}
+
+// params: flat fp32, tcnn order (input layer first, each matrix (out x in) row-major, in = padded input width,
+// last matrix padded to 16 rows).  blob: device buffer of arcb200_mlp_blob_bytes() bytes, 16-byte aligned.
+int arcb200_mlp_pack_weights(const float *params, void *blob, int in_dim, int width, int n_hidden, int out_dim,
+                             void *stream) {
+    MlpCfg c;
+    ARC_REQUIRE(make_cfg(c, in_dim, width, n_hidden, out_dim, 0, 0) >= 0, "mlp_pack_weights: unsupported shape");
+    ARC_REQUIRE(params && blob && ((uintptr_t)blob & 15u) == 0, "mlp_pack_weights: null or misaligned pointer");
+    pack_weights_kernel<<<dim3(8, c.n_mm), 256, 0, (cudaStream_t)stream>>>(c, params, (uint8_t *)blob);
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// Forward.  X (n, in_dim) fp32 or fp16 (x_is_half), leading dimension ldx elements; Y (n, out_dim) fp32 or fp16,
+// leading dimension ldy.  Activation codes: 0 none, 1 ReLU, 2 sigmoid, 3 softplus (tcnn, beta 10), 4 exp.
+// Replaces tcnn Module.fwd for a FullyFusedMLP network (bindings.cpp:78-109 -> fully_fused_mlp.cu:499-700).
+int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                    int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, int64_t n,
+                    void *stream) {
+    ARC_REQUIRE(n >= 0, "mlp_fwd: negative n");
+    if (n == 0) return ARCB200_OK;
+    MlpCfg c;
+    ARC_REQUIRE(make_cfg(c, in_dim, width, n_hidden, out_dim, hidden_act, out_act) >= 0, "mlp_fwd: unsupported shape");
+    ARC_REQUIRE(X && blob && Y, "mlp_fwd: null pointer");
+    ARC_REQUIRE(((uintptr_t)blob & 15u) == 0, "mlp_fwd: weight blob must be 16-byte aligned");
+    ARC_REQUIRE(ldx >= in_dim && ldy >= out_dim, "mlp_fwd: leading dimension too small");
+    const size_t smem = fwd_smem(c);
+    cudaStream_t st = (cudaStream_t)stream;
+    constexpr uint32_t COLS = 128;
+    const unsigned grid = mlp_grid(n, smem, COLS);
+#define LAUNCH_FWD(TI, TO)                                                                                  \
+    do {                                                                                                    \
+        int rc = set_smem(mlp_fwd_kernel<TI, TO, COLS>, smem);                                              \
+        if (rc != ARCB200_OK) return rc;                                                                    \
+        mlp_fwd_kernel<TI, TO, COLS><<<grid, kRows, smem, st>>>(n, (const TI *)X, ldx, (const uint8_t *)blob, c, (TO *)Y, ldy); \
+    } while (0)
+    if (x_is_half) { if (y_is_half) LAUNCH_FWD(__half, __half); else LAUNCH_FWD(__half, float); }
+    else { if (y_is_half) LAUNCH_FWD(float, __half); else LAUNCH_FWD(float, float); }
+#undef LAUNCH_FWD
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// Backward.  dY (n, out_dim) fp32 (leading dimension ldy); dX (n, in_dim) fp32 or fp16 or NULL; dW: flat fp32
+// gradient in the parameter layout, ACCUMULATED (caller zeroes it).  Gradients flow through fp16 tiles scaled by
+// loss_scale (128 in the reference, tinycudann/modules.py:141) and are unscaled on the way out.
+// width must be 64 or 128.  Replaces tcnn Module.bwd for a FullyFusedMLP (bindings.cpp:111-170 ->
+// fully_fused_mlp.cu:702-857).
+int arcb200_mlp_bwd(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                    int out_dim, int hidden_act, int out_act, const float *dY, int64_t ldy, float loss_scale,
+                    void *dX, int dx_is_half, int64_t ldgx, float *dW, int64_t n, void *stream) {
+    ARC_REQUIRE(n >= 0, "mlp_bwd: negative n");
+    if (n == 0) return ARCB200_OK;
+    MlpCfg c;
+    ARC_REQUIRE(make_cfg(c, in_dim, width, n_hidden, out_dim, hidden_act, out_act) >= 0, "mlp_bwd: unsupported shape");
+    BwdPlan plan;
+    const int cols = make_plan(c, plan);
+    ARC_REQUIRE(cols > 0, "mlp_bwd: hidden width must be 64 or 128");
+    ARC_REQUIRE(X && blob && dY && dW, "mlp_bwd: null pointer");
+    ARC_REQUIRE(loss_scale > 0.0f, "mlp_bwd: loss_scale must be positive");
+    ARC_REQUIRE(ldx >= in_dim && ldy >= out_dim && (!dX || ldgx >= in_dim), "mlp_bwd: leading dimension too small");
+    if (cols > 512) { arcb200_set_error("mlp_bwd: %d TMEM columns needed, 512 available", cols); return ARCB200_ERR_LIMIT; }
+    const size_t smem = bwd_smem(c);
+    cudaStream_t st = (cudaStream_t)stream;
+#define LAUNCH_BWD(TI, TG, COLS)                                                                            \
+    do {                                                                                                    \
+        int rc = set_smem(mlp_bwd_kernel<TI, TG, COLS>, smem);                                              \
+        if (rc != ARCB200_OK) return rc;                                                                    \
+        const unsigned grid = mlp_grid(n, smem, COLS);                                                      \
+        mlp_bwd_kernel<TI, TG, COLS><<<grid, kRows, smem, st>>>(n, (const TI *)X, ldx, (const uint8_t *)blob, c, plan, dY, \
+                                                               ldy, loss_scale, (TG *)dX, ldgx, dW);        \
+    } while (0)
+#define LAUNCH_BWD_T(COLS)                                                                                  \
+    do {                                                                                                    \
+        if (x_is_half) { if (dx_is_half) LAUNCH_BWD(__half, __half, COLS); else LAUNCH_BWD(__half, float, COLS); } \
+        else { if (dx_is_half) LAUNCH_BWD(float, __half, COLS); else LAUNCH_BWD(float, float, COLS); }      \
+    } while (0)
+    if (cols <= 128) LAUNCH_BWD_T(128);
+    else if (cols <= 256) LAUNCH_BWD_T(256);
+    else LAUNCH_BWD_T(512);
+#undef LAUNCH_BWD_T
+#undef LAUNCH_BWD
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+}  // extern "C"

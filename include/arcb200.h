@@ -145,6 +145,129 @@ int arcb200_march_packed(int bit, const float *rays_o, const float *rays_d, cons
                          void *scratch, int32_t *counts, int32_t *offsets, int32_t *meta, int64_t capacity,
                          float *t_out, float *xyz_out, int32_t *ray_id_out, void *stream);
 
+
+/* ---------------------------------------------------------------- tiny-cuda-nn binding: HashGrid ------
+ * ArcNerf reaches these through tinycudann.Encoding / tinycudann.Network (HashGridEmbedder
+ * hashgrid_encoder.py:102-113,182-184; SHEmbedder sh_encoder.py:59-65,116-118; FusedMLP*
+ * tcnn_fusedmlp_module.py:66-77,162-173).  "tcnn" below = /root/reference/include/tiny-cuda-nn. */
+
+/* Level geometry on the host (tcnn include/tiny-cuda-nn/encodings/grid.h:195-204,982-1012).  offsets
+ * (n_levels+1, in table entries), scales, resolutions (n_levels) are HOST arrays.  Returns the number of
+ * table entries (parameters = entries * n_features) or a negative error. */
+int64_t arcb200_grid_geometry(int n_levels, int log2_hashmap_size, int base_resolution, float per_level_scale,
+                              uint32_t *offsets, float *scales, uint32_t *resolutions);
+
+/* fp32 master parameters -> fp16 working copy (tcnn bindings/torch/tinycudann/modules.py:156 does this cast
+ * on every forward; callers of this library do it only after the parameters changed). */
+int arcb200_cast_f32_to_f16(const float *src, void *dst_half, int64_t n, void *stream);
+
+/* Replaces tcnn Module.fwd for a HashGrid encoding (bindings/torch/tinycudann/bindings.cpp:78-109 ->
+ * grid.h:220-392,1034-1105).  xyz (n,3) fp32 in [0,1]; table: fp16, flat [level][entry][feature];
+ * out (n, n_levels*n_features) fp16 row-major; dy_dx (n, n_levels*n_features, 3) fp32 or NULL.
+ * offsets/scales/resolutions: HOST arrays from arcb200_grid_geometry. */
+int arcb200_grid_fwd(const float *xyz, const void *table_half, int n_levels, int n_features, const uint32_t *offsets,
+                     const float *scales, const uint32_t *resolutions, void *out_half, float *dy_dx, int64_t n,
+                     void *stream);
+
+/* Replaces the parameter-gradient half of tcnn Module.bwd for a HashGrid (bindings.cpp:111-170 ->
+ * kernel_grid_backward, grid.h:394-517).  grad_table (fp32, table layout) += ...; the caller zeroes it.
+ * dL_dy (n, L*F) fp16 (dy_is_half) or fp32, multiplied by gscale on the fly. */
+int arcb200_grid_bwd(const float *xyz, const void *dL_dy, int dy_is_half, float gscale, int n_levels, int n_features,
+                     const uint32_t *offsets, const float *scales, const uint32_t *resolutions, float *grad_table,
+                     int64_t n, void *stream);
+
+/* Replaces the input-gradient half of tcnn Module.bwd (kernel_grid_backward_input, grid.h:549-576):
+ * dL_dx (n,3) = dL_dy . dy_dx. */
+int arcb200_grid_bwd_input(const void *dL_dy, int dy_is_half, float gscale, const float *dy_dx, int n_levels,
+                           int n_features, float *dL_dx, int64_t n, void *stream);
+
+/* Replaces tcnn Module.bwd_bwd_input for a HashGrid (bindings.cpp:172-241 -> grid.h:578-895): double backward
+ * of the input gradient (eikonal loss).  v = dL2/d(dL/dx) (n,3).  Optional outputs: grad_table (accumulated),
+ * d_dLdy (n, L*F) fp32, d_x (n,3) fp32 (zeroed by the call). */
+int arcb200_grid_bwd_bwd_input(const float *xyz, const void *table_half, const void *dL_dy, int dy_is_half,
+                               float gscale, const float *v, int n_levels, int n_features, const uint32_t *offsets,
+                               const float *scales, const uint32_t *resolutions, float *grad_table, float *d_dLdy,
+                               float *d_x, int64_t n, void *stream);
+
+/* ---------------------------------------------------------------- tiny-cuda-nn binding: SH -------------
+ * Replaces tcnn Module.fwd for a SphericalHarmonics encoding (kernel_sh, encodings/spherical_harmonics.h:46-152)
+ * as SHEmbedder.forward calls it (sh_encoder.py:104-123).  dirs (n_dirs,3) fp32; index (n) int32 or NULL
+ * (per-sample row of dirs, so that per-ray directions need not be repeated per sample); remap != 0: input is a
+ * direction in [-1,1] and the embedder's (d+1)/2 map is applied first; out: n rows of out_stride elements, fp16
+ * (out_is_half) or fp32, first degree^2 written.  degree 1..5. */
+int arcb200_sh_fwd(const float *dirs, const int32_t *index, int degree, int remap, void *out, int out_is_half,
+                   int64_t out_stride, int64_t n, void *stream);
+
+/* ---------------------------------------------------------------- tiny-cuda-nn binding: FullyFusedMLP --
+ * Network: in_dim -> width (x n_hidden, hidden_act) -> out_dim (out_act), no biases; flat fp32 parameters in
+ * tcnn order (fully_fused_mlp.cu:658-671): W_0 (width x in_pad), W_h (width x width) ..., W_last
+ * (out_pad x width), row-major, in_pad/out_pad = dims rounded up to 16; input pad columns are ONES
+ * (encodings/identity.h:63-64).  Activation codes: 0 none, 1 ReLU, 2 sigmoid, 3 softplus (beta 10), 4 exp. */
+int arcb200_mlp_n_params(int in_dim, int width, int n_hidden, int out_dim);
+int arcb200_mlp_blob_bytes(int in_dim, int width, int n_hidden, int out_dim);
+/* fp32 parameters -> fp16 tensor-core operand tiles (blob, 16-byte aligned device buffer).  Call after every
+ * parameter update; the forward/backward take the blob. */
+int arcb200_mlp_pack_weights(const float *params, void *blob, int in_dim, int width, int n_hidden, int out_dim,
+                             void *stream);
+/* Replaces tcnn Module.fwd for a FullyFusedMLP (bindings.cpp:78-109 -> fully_fused_mlp.cu:499-700).
+ * X (n,in_dim) fp32 or fp16, leading dimension ldx; Y (n,out_dim) fp32 or fp16, leading dimension ldy. */
+int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                    int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, int64_t n,
+                    void *stream);
+/* Replaces tcnn Module.bwd for a FullyFusedMLP (bindings.cpp:111-170 -> fully_fused_mlp.cu:150-259,702-857).
+ * dY (n,out_dim) fp32; dX (n,in_dim) fp32/fp16 or NULL; dW flat fp32 in the parameter layout, ACCUMULATED.
+ * loss_scale: internal fp16 gradient scale (128 in the reference, modules.py:141).  width must be 64 or 128. */
+int arcb200_mlp_bwd(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                    int out_dim, int hidden_act, int out_act, const float *dY, int64_t ldy, float loss_scale,
+                    void *dX, int dx_is_half, int64_t ldgx, float *dW, int64_t n, void *stream);
+
+/* ---------------------------------------------------------------- arcnerf/render/ray_helper ------------
+ * Rays are segments of flat per-sample arrays: offsets (n_rays+1) int32, or NULL for dense (n_rays, dense_p)
+ * tensors.  capacity = length of the per-sample arrays (packed samples beyond it were dropped by the sampler).
+ * pmax_dev: device int32, the row length P_max the equivalent padded call of the reference would use
+ * (meta+1 of arcb200_march_packed), or NULL. */
+
+/* Replaces ray_marching + alpha_to_weights (arcnerf/render/ray_helper.py:476-620).  geo = sigma, or alpha when
+ * is_alpha; rad (N,3) or NULL; noise (N) or NULL (already scaled by noise_std); bkg (n_rays,3) if bkg_per_ray else
+ * (1,3), or NULL.  Outputs: rgb (n_rays,3), depth, acc (n_rays); per-sample weights / trans_shift / alpha or NULL
+ * (the closing sample of a segment gets 0). */
+int arcb200_composite_fwd(const int32_t *offsets, int dense_p, int64_t capacity, const int32_t *pmax_dev,
+                          const float *geo, int is_alpha, const float *rad, const float *t, const float *noise,
+                          int add_inf_z, int white_bkg, const float *bkg, int bkg_per_ray, float *rgb, float *depth,
+                          float *acc, float *w_out, float *trans_out, float *alpha_out, int64_t n_rays,
+                          void *stream);
+/* Gradient of the above (the reference uses autograd through ~15 eager ops): d_geo (N), d_rad (N,3) or NULL from
+ * g_rgb (n_rays,3), g_depth, g_acc (n_rays), g_w (N), each optional.  max_samples_per_ray <= 4096. */
+int arcb200_composite_bwd(const int32_t *offsets, int dense_p, int64_t capacity, const int32_t *pmax_dev,
+                          const float *geo, int is_alpha, const float *rad, const float *t, const float *noise,
+                          int add_inf_z, int white_bkg, const float *bkg, int bkg_per_ray, const float *g_rgb,
+                          const float *g_depth, const float *g_acc, const float *g_w, float *d_geo, float *d_rad,
+                          int max_samples_per_ray, int64_t n_rays, void *stream);
+
+/* Replaces sdf_to_alpha (arcnerf/models/neus_model.py:242-265).  sdf, slope, alpha (n_rays,p); zvals (n_rays,p+1);
+ * scale s from s_dev (device float) when not NULL, else s_host. */
+int arcb200_sdf_to_alpha(const float *sdf, const float *zvals, const float *slope, const float *s_dev, float s_host,
+                         int clip, float *alpha, int64_t n_rays, int p, void *stream);
+/* Its gradient; d_s (1 float, optional) is accumulated atomically (zero it first). */
+int arcb200_sdf_to_alpha_bwd(const float *sdf, const float *zvals, const float *slope, const float *s_dev,
+                             float s_host, int clip, const float *g_alpha, float *d_sdf, float *d_slope, float *d_s,
+                             int64_t n_rays, int p, void *stream);
+
+/* Replaces the searchsorted/gather/interpolate core of sample_cdf (arcnerf/render/ray_helper.py:434-473).
+ * bins, cdf (n_rays,n_bins); u (n_rays,n_sample) if u_per_ray else (n_sample); out (n_rays,n_sample) unsorted. */
+int arcb200_sample_cdf(const float *bins, const float *cdf, const float *u, int u_per_ray, float eps, float *out,
+                       int64_t n_rays, int n_bins, int n_sample, void *stream);
+
+/* ---------------------------------------------------------------- training-step helpers ----------------
+ * torch.optim.Adam arithmetic (common/trainer/optimizer.py -> torch) in one pass that also writes the fp16
+ * working copy (p_half, optional) and clears the gradient (zero_grad).  step >= 1. */
+int arcb200_adam_step(float *p, float *m, float *v, float *g, void *p_half, int64_t n, int step, float lr,
+                      float beta1, float beta2, float eps, float weight_decay, float grad_scale, int zero_grad,
+                      void *stream);
+/* ImgLoss with HuberLoss (arcnerf/loss/img_loss.py:48-98): loss_sum[0] += weight * mean(huber), g_rgb = gradient. */
+int arcb200_huber_loss(const float *rgb, const float *target, float delta, float weight, float *g_rgb,
+                       float *loss_sum, int64_t n_rays, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -434,3 +434,27 @@ void orc_count_bitfield(int n_bytes, const uint8_t *bits, float *counter, int fa
             if (faithful ? (bits[i] != 0) : ((bits[i] >> j) & 1)) c += 1.0f;
     counter[0] = c;
 }
+
+/* ------------------------------------------------------------------ hash-grid level geometry
+ * tiny-cuda-nn include/tiny-cuda-nn/encodings/grid.h:195-204 (grid_scale / grid_resolution, evaluated by the
+ * HOST in the encoding's constructor, :982-1012): scale = exp2f(level * log2f(per_level_scale)) * base - 1,
+ * resolution = ceilf(scale) + 1, entries = min(roundup8(res^3), 2^log2_T).  libm's exp2f/log2f as the
+ * reference's host code uses them (numpy's differ by an ulp on some levels). */
+int64_t orc_grid_geometry(int n_levels, int log2_hashmap_size, int base_resolution, float per_level_scale,
+                          uint32_t *offsets, float *scales, uint32_t *resolutions) {
+    const float l2 = log2f(per_level_scale);
+    uint32_t off = 0;
+    for (int l = 0; l < n_levels; ++l) {
+        float s = exp2f((float)l * l2) * (float)base_resolution - 1.0f;
+        uint32_t r = (uint32_t)ceilf(s) + 1u;
+        uint64_t dense = (uint64_t)r * r * r;
+        if (dense > 0xFFFFFFFFull / 2) dense = 0xFFFFFFFFull / 2;
+        dense = (dense + 7) / 8 * 8;
+        uint64_t cap = 1ull << log2_hashmap_size;
+        if (dense > cap) dense = cap;
+        offsets[l] = off; scales[l] = s; resolutions[l] = r;
+        off += (uint32_t)dense;
+    }
+    offsets[n_levels] = off;
+    return (int64_t)off;
+}
