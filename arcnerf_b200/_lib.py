@@ -35,24 +35,27 @@ _SIGS = {
     'arcb200_sparse_sampling_in_multivol_bitfield': [P, P, P, P, I, F, F, F, P, P, I, I, P, F, I, P, P, L, U64, U64, P],
     'arcb200_generate_grid_samples_multivol': [P, I, L, P, I, I, F, I, P, P, U64, U64, P],
     'arcb200_march_packed_scratch_bytes': [L, I],
-    'arcb200_march_packed': [I, P, P, P, P, I, F, P, I, P, F, L, U64, U64, P, P, P, P, L, P, P, P, P],
+    'arcb200_march_packed': [I, P, P, P, P, I, F, P, I, P, F, L, U64, U64, P, P, P, P, L, P, P, P, P, P],
     'arcb200_grid_geometry': [I, I, I, F, P, P, P],
     'arcb200_cast_f32_to_f16': [P, P, L, P],
-    'arcb200_grid_fwd': [P, P, I, I, P, P, P, P, P, L, P],
-    'arcb200_grid_bwd': [P, P, I, F, I, I, P, P, P, P, L, P],
+    'arcb200_grid_fwd': [P, P, I, I, P, P, P, P, P, L, P, P],
+    'arcb200_grid_bwd': [P, P, I, F, I, I, P, P, P, P, L, P, P],
     'arcb200_grid_bwd_input': [P, I, F, P, I, I, P, L, P],
     'arcb200_grid_bwd_bwd_input': [P, P, P, I, F, P, I, I, P, P, P, P, P, P, L, P],
-    'arcb200_sh_fwd': [P, P, I, I, P, I, L, L, P],
+    'arcb200_sh_fwd': [P, P, I, I, P, I, L, L, P, P],
     'arcb200_mlp_n_params': [I, I, I, I],
     'arcb200_mlp_blob_bytes': [I, I, I, I],
     'arcb200_mlp_pack_weights': [P, P, I, I, I, I, P],
-    'arcb200_mlp_fwd': [P, I, L, P, I, I, I, I, I, I, P, I, L, L, P],
-    'arcb200_mlp_bwd': [P, I, L, P, I, I, I, I, I, I, P, L, F, P, I, L, P, L, P],
+    'arcb200_mlp_fwd': [P, I, L, P, I, I, I, I, I, I, P, I, L, L, P, P],
+    'arcb200_mlp_bwd': [P, I, L, P, I, I, I, I, I, I, P, L, F, P, I, L, P, L, P, P],
     'arcb200_composite_fwd': [P, I, L, P, P, I, P, P, P, I, I, P, I, P, P, P, P, P, P, L, P],
     'arcb200_composite_bwd': [P, I, L, P, P, I, P, P, P, I, I, P, I, P, P, P, P, P, P, I, L, P],
     'arcb200_sdf_to_alpha': [P, P, P, P, F, I, P, L, I, P],
     'arcb200_sdf_to_alpha_bwd': [P, P, P, P, F, I, P, P, P, P, L, I, P],
     'arcb200_sample_cdf': [P, P, P, I, F, P, L, I, I, P],
+    'arcb200_trunc_exp_fwd': [P, I, L, P, L, P, P],
+    'arcb200_trunc_exp_bwd': [P, I, L, P, F, P, L, P, P],
+    'arcb200_geo_head_grad': [P, I, L, P, F, P, I, L, I, P, L, P, P],
     'arcb200_adam_step': [P, P, P, P, P, L, I, F, F, F, F, F, F, I, P],
     'arcb200_huber_loss': [P, P, F, F, P, P, L, P],
 }

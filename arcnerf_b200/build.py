@@ -27,6 +27,7 @@ SOURCES = {
     'composite.cu': [],
     'mlp_tc.cu': [],
     'optim.cu': [],
+    'glue.cu': [],
     'noalloc.cu': ['-fmad=false'],
 }
 

@@ -93,9 +93,11 @@ constexpr int kFwdWarps = 8;
 // DYDX: also writes dy/dx (N, L*F, 3) fp32 for the input gradient / normals.
 template <int F, bool DYDX>
 __global__ void __launch_bounds__(kTileSamples * kFwdWarps)
-grid_fwd_kernel(uint32_t n, const float *__restrict__ xyz, const __half *__restrict__ table, GridGeom geom,
-                __half *__restrict__ out, float *__restrict__ dy_dx) {
+grid_fwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__restrict__ xyz,
+                const __half *__restrict__ table, GridGeom geom, __half *__restrict__ out, float *__restrict__ dy_dx) {
     extern __shared__ __half tile[];   // [32][L*F + 2]
+    if (n_dev) n = min(n, (uint32_t)max(*n_dev, 0));
+    if (blockIdx.x * kTileSamples >= n) return;
     const uint32_t L = geom.n_levels;
     const uint32_t row = L * F;
     const uint32_t pitch = row + 2;
@@ -187,9 +189,12 @@ __device__ __forceinline__ void add_entry(float *__restrict__ level_grad, uint32
 // (N,3): the table term of the double backward (reference: kernel_grid_backward_input_backward_grid).
 template <int F, typename T, bool SECOND>
 __global__ void __launch_bounds__(kTileSamples * kFwdWarps)
-grid_bwd_kernel(uint32_t n, const float *__restrict__ xyz, const T *__restrict__ dL_dy, GridGeom geom,
-                float *__restrict__ grad_table, float gscale, const float *__restrict__ v_in) {
+grid_bwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__restrict__ xyz,
+                const T *__restrict__ dL_dy, GridGeom geom, float *__restrict__ grad_table, float gscale,
+                const float *__restrict__ v_in) {
     extern __shared__ float gtile[];   // [32][L*F + 1]
+    if (n_dev) n = min(n, (uint32_t)max(*n_dev, 0));
+    if (blockIdx.x * kTileSamples >= n) return;
     const uint32_t L = geom.n_levels;
     const uint32_t row = L * F;
     const uint32_t pitch = row + 1;
@@ -404,11 +409,13 @@ int arcb200_cast_f32_to_f16(const float *src, void *dst_half, int64_t n, void *s
 
 // Forward.  xyz (n,3) fp32 in [0,1]; table: fp16, flat [level][entry][feature]; out (n, L*F) fp16 row-major;
 // dy_dx (n, L*F, 3) fp32 or NULL.  offsets/scales/resolutions: HOST arrays from arcb200_grid_geometry.
+// n_dev (device int32, optional): only min(n, *n_dev) rows are processed - the row count of a packed sample list
+// can stay on the device (no host synchronisation between the sampler and the encoder).
 // Replaces tcnn Module.fwd for a HashGrid encoding (bindings/torch/tinycudann/bindings.cpp:78-109 ->
 // GridEncodingTemplated::forward_impl, grid.h:1034-1105).
 int arcb200_grid_fwd(const float *xyz, const void *table_half, int n_levels, int n_features, const uint32_t *offsets,
                      const float *scales, const uint32_t *resolutions, void *out_half, float *dy_dx, int64_t n,
-                     void *stream) {
+                     const int32_t *n_dev, void *stream) {
     ARC_REQUIRE(n >= 0 && n < (1ll << 31) - 64, "grid_fwd: n out of range");
     if (n == 0) return ARCB200_OK;
     ARC_REQUIRE(xyz && table_half && out_half && offsets && scales && resolutions, "grid_fwd: null pointer");
@@ -419,9 +426,9 @@ int arcb200_grid_fwd(const float *xyz, const void *table_half, int n_levels, int
     cudaStream_t st = (cudaStream_t)stream;
     GRID_DISPATCH_F(n_features,
         if (dy_dx) grid_fwd_kernel<F, true><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(
-            (uint32_t)n, xyz, (const __half *)table_half, geom, (__half *)out_half, dy_dx);
+            (uint32_t)n, n_dev, xyz, (const __half *)table_half, geom, (__half *)out_half, dy_dx);
         else grid_fwd_kernel<F, false><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(
-            (uint32_t)n, xyz, (const __half *)table_half, geom, (__half *)out_half, nullptr));
+            (uint32_t)n, n_dev, xyz, (const __half *)table_half, geom, (__half *)out_half, nullptr));
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
@@ -431,7 +438,7 @@ int arcb200_grid_fwd(const float *xyz, const void *table_half, int n_levels, int
 // Replaces the grid part of tcnn Module.bwd (bindings.cpp:111-170 -> kernel_grid_backward, grid.h:394-517).
 int arcb200_grid_bwd(const float *xyz, const void *dL_dy, int dy_is_half, float gscale, int n_levels, int n_features,
                      const uint32_t *offsets, const float *scales, const uint32_t *resolutions, float *grad_table,
-                     int64_t n, void *stream) {
+                     int64_t n, const int32_t *n_dev, void *stream) {
     ARC_REQUIRE(n >= 0 && n < (1ll << 31) - 64, "grid_bwd: n out of range");
     if (n == 0) return ARCB200_OK;
     ARC_REQUIRE(xyz && dL_dy && grad_table && offsets && scales && resolutions, "grid_bwd: null pointer");
@@ -442,9 +449,9 @@ int arcb200_grid_bwd(const float *xyz, const void *dL_dy, int dy_is_half, float 
     cudaStream_t st = (cudaStream_t)stream;
     GRID_DISPATCH_F(n_features,
         if (dy_is_half) grid_bwd_kernel<F, __half, false><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(
-            (uint32_t)n, xyz, (const __half *)dL_dy, geom, grad_table, gscale, nullptr);
+            (uint32_t)n, n_dev, xyz, (const __half *)dL_dy, geom, grad_table, gscale, nullptr);
         else grid_bwd_kernel<F, float, false><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(
-            (uint32_t)n, xyz, (const float *)dL_dy, geom, grad_table, gscale, nullptr));
+            (uint32_t)n, n_dev, xyz, (const float *)dL_dy, geom, grad_table, gscale, nullptr));
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
@@ -484,9 +491,9 @@ int arcb200_grid_bwd_bwd_input(const float *xyz, const void *table_half, const v
         const size_t smem = (size_t)kTileSamples * (n_levels * n_features + 1) * sizeof(float);
         GRID_DISPATCH_F(n_features,
             if (dy_is_half) grid_bwd_kernel<F, __half, true><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(
-                (uint32_t)n, xyz, (const __half *)dL_dy, geom, grad_table, gscale, v);
+                (uint32_t)n, nullptr, xyz, (const __half *)dL_dy, geom, grad_table, gscale, v);
             else grid_bwd_kernel<F, float, true><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(
-                (uint32_t)n, xyz, (const float *)dL_dy, geom, grad_table, gscale, v));
+                (uint32_t)n, nullptr, xyz, (const float *)dL_dy, geom, grad_table, gscale, v));
         ARC_LAUNCH_CHECK();
     }
     if (d_dLdy || d_x) {

@@ -308,7 +308,7 @@ pack_samples_kernel(uint32_t n_rays, uint32_t n_pts, const float *__restrict__ r
                     const int32_t *__restrict__ counts, int32_t *__restrict__ offsets,
                     const int32_t *__restrict__ tile_prefix, const int32_t *__restrict__ total,
                     int64_t capacity, float *__restrict__ t_out, float *__restrict__ xyz_out,
-                    int32_t *__restrict__ ray_id_out) {
+                    int32_t *__restrict__ ray_id_out, const float *__restrict__ aabb, float *__restrict__ unit_out) {
     const uint32_t ray = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31u;
     if (ray > n_rays) return;
@@ -327,9 +327,13 @@ pack_samples_kernel(uint32_t n_rays, uint32_t n_pts, const float *__restrict__ r
         if (s >= capacity) break;    // caller-provided capacity exceeded: samples beyond it are dropped
         const float t = z[k];
         t_out[s] = t;
-        if (xyz_out) {
-            const F3 p = ray_at(o, d, t);
-            xyz_out[3 * s] = p.x; xyz_out[3 * s + 1] = p.y; xyz_out[3 * s + 2] = p.z;
+        const F3 p = ray_at(o, d, t);
+        if (xyz_out) { xyz_out[3 * s] = p.x; xyz_out[3 * s + 1] = p.y; xyz_out[3 * s + 2] = p.z; }
+        if (unit_out) {   // (p - min) / (max - min): the normalisation HashGridEmbedder applies (hashgrid_encoder.py:183)
+            const Box b = load_box(aabb);
+            unit_out[3 * s] = (p.x - b.lo.x) / (b.hi.x - b.lo.x);
+            unit_out[3 * s + 1] = (p.y - b.lo.y) / (b.hi.y - b.lo.y);
+            unit_out[3 * s + 2] = (p.z - b.lo.z) / (b.hi.z - b.lo.z);
         }
         if (ray_id_out) ray_id_out[s] = (int32_t)ray;
     }
@@ -433,13 +437,14 @@ int64_t arcb200_march_packed_scratch_bytes(int64_t n_rays, int n_pts) {
 
 // March + pack.  Outputs: counts[n_rays], offsets[n_rays+1] (exclusive prefix; offsets[n_rays] = total),
 // meta[0] = total samples, meta[1] = max samples on one ray, and the packed per-sample arrays
-// t[capacity], xyz[capacity*3] (world position, optional), ray_id[capacity] (optional).  Samples of a ray
+// t[capacity], xyz[capacity*3] (world position, optional), ray_id[capacity] (optional), unit[capacity*3] (position
+// normalised to the box, (p-min)/(max-min), optional: the hash-grid encoder's input).  Samples of a ray
 // are contiguous and rays appear in index order.  `scratch` must hold arcb200_march_packed_scratch_bytes().
 int arcb200_march_packed(int bit, const float *rays_o, const float *rays_d, const float *near, const float *far,
                          int n_pts, float dt, const float *aabb, int n_grid, const uint8_t *field,
                          float near_distance, int64_t n_rays, uint64_t rng_state, uint64_t rng_inc,
                          void *scratch, int32_t *counts, int32_t *offsets, int32_t *meta, int64_t capacity,
-                         float *t_out, float *xyz_out, int32_t *ray_id_out, void *stream) {
+                         float *t_out, float *xyz_out, int32_t *ray_id_out, float *unit_out, void *stream) {
     ARC_REQUIRE(n_rays >= 0 && n_rays < (1ll << 27), "march_packed: n_rays out of range");
     ARC_REQUIRE(counts && offsets && meta, "march_packed: null bookkeeping pointer");
     cudaStream_t st = (cudaStream_t)stream;
@@ -462,7 +467,7 @@ int arcb200_march_packed(int bit, const float *rays_o, const float *rays_d, cons
     ARC_LAUNCH_CHECK();
     pack_samples_kernel<<<arc_blocks((n_rays + 1) * 32, 256), 256, 0, st>>>(
         (uint32_t)n_rays, (uint32_t)n_pts, rays_o, rays_d, zrows, counts, offsets, tile_sums, meta, capacity,
-        t_out, xyz_out, ray_id_out);
+        t_out, xyz_out, ray_id_out, aabb, unit_out);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }

@@ -133,9 +133,10 @@ struct Shared {
 // ---------------------------------------------------------------------------------------------- forward
 template <typename TIN, typename TOUT, uint32_t TMEM_COLS>
 __global__ void __launch_bounds__(kRows)
-mlp_fwd_kernel(int64_t n, const TIN *__restrict__ X, int64_t ldx, const uint8_t *__restrict__ blob, MlpCfg cfg,
-               TOUT *__restrict__ Y, int64_t ldy) {
+mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restrict__ X, int64_t ldx,
+               const uint8_t *__restrict__ blob, MlpCfg cfg, TOUT *__restrict__ Y, int64_t ldy) {
     extern __shared__ __align__(128) uint8_t smem[];
+    if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     Shared *sh = reinterpret_cast<Shared *>(smem);
     uint8_t *w_s = smem + 128;
     uint8_t *a_s = w_s + ((cfg.w_bytes + 127u) & ~127u);
@@ -220,10 +221,11 @@ struct BwdPlan {
 
 template <typename TIN, typename TGX, uint32_t TMEM_COLS>
 __global__ void __launch_bounds__(kRows)
-mlp_bwd_kernel(int64_t n, const TIN *__restrict__ X, int64_t ldx, const uint8_t *__restrict__ blob, MlpCfg cfg,
-               BwdPlan plan, const float *__restrict__ dY, int64_t ldy, float loss_scale, TGX *__restrict__ dX,
-               int64_t ldgx, float *__restrict__ dW) {
+mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restrict__ X, int64_t ldx,
+               const uint8_t *__restrict__ blob, MlpCfg cfg, BwdPlan plan, const float *__restrict__ dY, int64_t ldy,
+               float loss_scale, TGX *__restrict__ dX, int64_t ldgx, float *__restrict__ dW) {
     extern __shared__ __align__(128) uint8_t smem[];
+    if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     Shared *sh = reinterpret_cast<Shared *>(smem);
     uint8_t *w_s = smem + 128;
     uint8_t *x_s = w_s + ((cfg.w_bytes + 127u) & ~127u);                  // 128 x in_pad
@@ -500,7 +502,7 @@ int arcb200_mlp_pack_weights(const float *params, void *blob, int in_dim, int wi
 // Replaces tcnn Module.fwd for a FullyFusedMLP network (bindings.cpp:78-109 -> fully_fused_mlp.cu:499-700).
 int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
                     int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, int64_t n,
-                    void *stream) {
+                    const int32_t *n_dev, void *stream) {
     ARC_REQUIRE(n >= 0, "mlp_fwd: negative n");
     if (n == 0) return ARCB200_OK;
     MlpCfg c;
@@ -516,7 +518,7 @@ int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob,
     do {                                                                                                    \
         int rc = set_smem(mlp_fwd_kernel<TI, TO, COLS>, smem);                                              \
         if (rc != ARCB200_OK) return rc;                                                                    \
-        mlp_fwd_kernel<TI, TO, COLS><<<grid, kRows, smem, st>>>(n, (const TI *)X, ldx, (const uint8_t *)blob, c, (TO *)Y, ldy); \
+        mlp_fwd_kernel<TI, TO, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, (TO *)Y, ldy); \
     } while (0)
     if (x_is_half) { if (y_is_half) LAUNCH_FWD(__half, __half); else LAUNCH_FWD(__half, float); }
     else { if (y_is_half) LAUNCH_FWD(float, __half); else LAUNCH_FWD(float, float); }
@@ -532,7 +534,7 @@ int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob,
 // fully_fused_mlp.cu:702-857).
 int arcb200_mlp_bwd(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
                     int out_dim, int hidden_act, int out_act, const float *dY, int64_t ldy, float loss_scale,
-                    void *dX, int dx_is_half, int64_t ldgx, float *dW, int64_t n, void *stream) {
+                    void *dX, int dx_is_half, int64_t ldgx, float *dW, int64_t n, const int32_t *n_dev, void *stream) {
     ARC_REQUIRE(n >= 0, "mlp_bwd: negative n");
     if (n == 0) return ARCB200_OK;
     MlpCfg c;
@@ -551,7 +553,7 @@ int arcb200_mlp_bwd(const void *X, int x_is_half, int64_t ldx, const void *blob,
         int rc = set_smem(mlp_bwd_kernel<TI, TG, COLS>, smem);                                              \
         if (rc != ARCB200_OK) return rc;                                                                    \
         const unsigned grid = mlp_grid(n, smem, COLS);                                                      \
-        mlp_bwd_kernel<TI, TG, COLS><<<grid, kRows, smem, st>>>(n, (const TI *)X, ldx, (const uint8_t *)blob, c, plan, dY, \
+        mlp_bwd_kernel<TI, TG, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, plan, dY, \
                                                                ldy, loss_scale, (TG *)dX, ldgx, dW);        \
     } while (0)
 #define LAUNCH_BWD_T(COLS)                                                                                  \

@@ -51,8 +51,10 @@ __device__ __forceinline__ void sh_basis(float x, float y, float z, int degree, 
 // One thread per direction; dirs may be indexed through `index` (e.g. the ray id of a packed sample, so
 // that per-ray directions need not be repeated per sample as fg_model.py:289 does).
 template <typename OUT>
-__global__ void sh_fwd_kernel(uint32_t n, const float *__restrict__ dirs, const int32_t *__restrict__ index,
-                              int degree, int remap, OUT *__restrict__ out, uint32_t out_stride) {
+__global__ void sh_fwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__restrict__ dirs,
+                              const int32_t *__restrict__ index, int degree, int remap, OUT *__restrict__ out,
+                              uint32_t out_stride) {
+    if (n_dev) n = min(n, (uint32_t)max(*n_dev, 0));
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const size_t src = index ? (size_t)index[i] : (size_t)i;
@@ -76,17 +78,17 @@ extern "C" {
 // Replaces tcnn Module.fwd for a SphericalHarmonics encoding (bindings.cpp:78-109 -> kernel_sh,
 // spherical_harmonics.h:46-152) as called from SHEmbedder.forward (sh_encoder.py:104-123).
 int arcb200_sh_fwd(const float *dirs, const int32_t *index, int degree, int remap, void *out, int out_is_half,
-                   int64_t out_stride, int64_t n, void *stream) {
+                   int64_t out_stride, int64_t n, const int32_t *n_dev, void *stream) {
     ARC_REQUIRE(n >= 0 && n < (1ll << 32), "sh_fwd: n out of range");
     if (n == 0) return ARCB200_OK;
     ARC_REQUIRE(dirs && out, "sh_fwd: null pointer");
     ARC_REQUIRE(degree >= 1 && degree <= 5, "sh_fwd: degree must be 1..5");
     ARC_REQUIRE(out_stride >= degree * degree, "sh_fwd: out_stride smaller than degree^2");
     if (out_is_half)
-        sh_fwd_kernel<__half><<<arc_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>((uint32_t)n, dirs, index, degree, remap,
+        sh_fwd_kernel<__half><<<arc_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>((uint32_t)n, n_dev, dirs, index, degree, remap,
                                                                                    (__half *)out, (uint32_t)out_stride);
     else
-        sh_fwd_kernel<float><<<arc_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>((uint32_t)n, dirs, index, degree, remap,
+        sh_fwd_kernel<float><<<arc_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>((uint32_t)n, n_dev, dirs, index, degree, remap,
                                                                                   (float *)out, (uint32_t)out_stride);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;

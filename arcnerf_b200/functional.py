@@ -61,7 +61,7 @@ def cast_f16(src, dst=None):
     return dst
 
 
-def grid_forward(xyz, table_half, geom, want_dydx=False):
+def grid_forward(xyz, table_half, geom, want_dydx=False, n_dev=None, out=None):
     """xyz (N,3) fp32 in [0,1]; table_half flat fp16 -> (N, L*F) fp16 [, dy_dx (N, L*F, 3) fp32]"""
     _cuda(xyz, 'xyz'), _cuda(table_half, 'table')
     if xyz.dtype != torch.float32 or xyz.dim() != 2 or xyz.shape[1] != 3:
@@ -69,15 +69,16 @@ def grid_forward(xyz, table_half, geom, want_dydx=False):
     if table_half.dtype != torch.float16 or table_half.numel() != geom.n_params:
         raise RuntimeError('table must be float16 with %d elements' % geom.n_params)
     n = xyz.shape[0]
-    out = torch.empty((n, geom.out_dim), dtype=torch.float16, device=xyz.device)
+    if out is None:
+        out = torch.empty((n, geom.out_dim), dtype=torch.float16, device=xyz.device)
     dydx = torch.empty((n, geom.out_dim, 3), dtype=torch.float32, device=xyz.device) if want_dydx else None
     nl, nf, off, sc, rs = geom._args()
     _lib.call('arcb200_grid_fwd', xyz.data_ptr(), table_half.data_ptr(), nl, nf, off, sc, rs, out.data_ptr(),
-              _lib.ptr(dydx), n, _stream())
+              _lib.ptr(dydx), n, _lib.ptr(n_dev), _stream())
     return (out, dydx) if want_dydx else out
 
 
-def grid_backward(xyz, dL_dy, geom, grad_table=None, gscale=1.0):
+def grid_backward(xyz, dL_dy, geom, grad_table=None, gscale=1.0, n_dev=None):
     """Accumulates the table gradient (flat fp32, geom.n_params) of dL_dy (N, L*F) fp16|fp32."""
     _cuda(xyz, 'xyz'), _cuda(dL_dy, 'dL_dy')
     if dL_dy.dtype not in (torch.float16, torch.float32) or dL_dy.shape != (xyz.shape[0], geom.out_dim):
@@ -86,7 +87,7 @@ def grid_backward(xyz, dL_dy, geom, grad_table=None, gscale=1.0):
         grad_table = torch.zeros(geom.n_params, dtype=torch.float32, device=xyz.device)
     nl, nf, off, sc, rs = geom._args()
     _lib.call('arcb200_grid_bwd', xyz.data_ptr(), dL_dy.data_ptr(), int(dL_dy.dtype == torch.float16), float(gscale),
-              nl, nf, off, sc, rs, grad_table.data_ptr(), xyz.shape[0], _stream())
+              nl, nf, off, sc, rs, grad_table.data_ptr(), xyz.shape[0], _lib.ptr(n_dev), _stream())
     return grad_table
 
 
@@ -113,7 +114,7 @@ def grid_double_backward(xyz, table_half, dL_dy, v, geom, grad_table=None, want_
 
 
 # ---------------------------------------------------------------------------------------------- SH
-def sh_forward(dirs, degree=4, index=None, remap=True, out_dtype=torch.float16, out=None, out_col=0):
+def sh_forward(dirs, degree=4, index=None, remap=True, out_dtype=torch.float16, out=None, out_col=0, n_dev=None):
     """dirs (M,3) fp32 -> (N, degree^2); index (N,) int32 selects the row of dirs per output row.
     With `out` (N, S) given, writes columns [out_col, out_col+degree^2) of it (fused concatenation)."""
     _cuda(dirs, 'dirs')
@@ -127,7 +128,7 @@ def sh_forward(dirs, degree=4, index=None, remap=True, out_dtype=torch.float16, 
         raise RuntimeError('sh_forward: bad output tensor')
     esz = out.element_size()
     _lib.call('arcb200_sh_fwd', dirs.data_ptr(), _lib.ptr(index), int(degree), int(bool(remap)),
-              out.data_ptr() + out_col * esz, int(out.dtype == torch.float16), out.stride(0), n, _stream())
+              out.data_ptr() + out_col * esz, int(out.dtype == torch.float16), out.stride(0), n, _lib.ptr(n_dev), _stream())
     return out
 
 
@@ -161,19 +162,21 @@ def mlp_pack(params, spec, blob=None):
     return blob
 
 
-def mlp_forward(x, blob, spec, out_dtype=torch.float32, out=None):
+def mlp_forward(x, blob, spec, out_dtype=torch.float32, out=None, out_col=0, n_dev=None):
     _cuda(x, 'x'), _cuda(blob, 'blob')
-    if x.dtype not in (torch.float16, torch.float32) or x.dim() != 2 or x.shape[1] != spec.in_dim:
-        raise RuntimeError('x must be (N, %d) float16/float32' % spec.in_dim)
+    if x.dtype not in (torch.float16, torch.float32) or x.dim() != 2 or x.shape[1] < spec.in_dim or x.stride(1) != 1:
+        raise RuntimeError('x must be (N, >=%d) float16/float32 with unit column stride' % spec.in_dim)
     n = x.shape[0]
     if out is None:
         out = torch.empty((n, spec.out_dim), dtype=out_dtype, device=x.device)
     _lib.call('arcb200_mlp_fwd', x.data_ptr(), int(x.dtype == torch.float16), x.stride(0), blob.data_ptr(), *spec.dims(),
-              spec.hidden_act, spec.out_act, out.data_ptr(), int(out.dtype == torch.float16), out.stride(0), n, _stream())
+              spec.hidden_act, spec.out_act, out.data_ptr() + out_col * out.element_size(),
+              int(out.dtype == torch.float16), out.stride(0), n, _lib.ptr(n_dev), _stream())
     return out
 
 
-def mlp_backward(x, blob, spec, dy, dW=None, want_dx=True, dx_dtype=torch.float32, loss_scale=128.0):
+def mlp_backward(x, blob, spec, dy, dW=None, want_dx=True, dx_dtype=torch.float32, loss_scale=128.0, n_dev=None,
+                 dx=None):
     """-> (dX (N,in_dim) | None, dW flat fp32 accumulated)"""
     _cuda(x, 'x'), _cuda(blob, 'blob'), _cuda(dy, 'dy')
     if dy.dtype != torch.float32 or dy.shape != (x.shape[0], spec.out_dim):
@@ -181,10 +184,12 @@ def mlp_backward(x, blob, spec, dy, dW=None, want_dx=True, dx_dtype=torch.float3
     n = x.shape[0]
     if dW is None:
         dW = torch.zeros(spec.n_params, dtype=torch.float32, device=x.device)
-    dx = torch.empty((n, spec.in_dim), dtype=dx_dtype, device=x.device) if want_dx else None
+    if dx is None and want_dx:
+        dx = torch.empty((n, spec.in_dim), dtype=dx_dtype, device=x.device)
     _lib.call('arcb200_mlp_bwd', x.data_ptr(), int(x.dtype == torch.float16), x.stride(0), blob.data_ptr(), *spec.dims(),
               spec.hidden_act, spec.out_act, dy.data_ptr(), dy.stride(0), float(loss_scale), _lib.ptr(dx),
-              int(dx_dtype == torch.float16), spec.in_dim, dW.data_ptr(), n, _stream())
+              int(dx is not None and dx.dtype == torch.float16), dx.stride(0) if dx is not None else 0, dW.data_ptr(), n,
+              _lib.ptr(n_dev), _stream())
     return dx, dW
 
 

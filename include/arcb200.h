@@ -135,7 +135,8 @@ int arcb200_generate_grid_samples_multivol(const float *density_grid, int ema_st
  * instead of the padded (n_rays,n_pts) matrix that FgModel re-compacts with boolean indexing
  * (arcnerf/models/fg_model.py:251-318).  Outputs: counts (n_rays) int32; offsets (n_rays+1) int32 exclusive
  * prefix of counts; meta[0] = total samples, meta[1] = largest count; t (capacity) sample distances;
- * xyz (capacity,3) world positions or NULL; ray_id (capacity) or NULL.  Samples of one ray are contiguous,
+ * xyz (capacity,3) world positions or NULL; ray_id (capacity) or NULL; unit (capacity,3) positions normalised to the
+ * box ((p-min)/(max-min), the encoder input, hashgrid_encoder.py:183) or NULL.  Samples of one ray are contiguous,
  * rays in index order; samples beyond `capacity` are dropped (offsets still describe the full list).
  * scratch: arcb200_march_packed_scratch_bytes(n_rays, n_pts) bytes of device memory. */
 int64_t arcb200_march_packed_scratch_bytes(int64_t n_rays, int n_pts);
@@ -143,8 +144,12 @@ int arcb200_march_packed(int bit, const float *rays_o, const float *rays_d, cons
                          int n_pts, float dt, const float *aabb, int n_grid, const uint8_t *field,
                          float near_distance, int64_t n_rays, uint64_t rng_state, uint64_t rng_inc,
                          void *scratch, int32_t *counts, int32_t *offsets, int32_t *meta, int64_t capacity,
-                         float *t_out, float *xyz_out, int32_t *ray_id_out, void *stream);
+                         float *t_out, float *xyz_out, int32_t *ray_id_out, float *unit_out, void *stream);
 
+
+/* Row counts on the device: the entry points below that take `n_dev` (device int32 or NULL) process only
+ * min(n, *n_dev) rows, so the sample count produced by arcb200_march_packed (meta[0]) never has to travel to
+ * the host between the sampler and the field kernels. */
 
 /* ---------------------------------------------------------------- tiny-cuda-nn binding: HashGrid ------
  * ArcNerf reaches these through tinycudann.Encoding / tinycudann.Network (HashGridEmbedder
@@ -167,14 +172,14 @@ int arcb200_cast_f32_to_f16(const float *src, void *dst_half, int64_t n, void *s
  * offsets/scales/resolutions: HOST arrays from arcb200_grid_geometry. */
 int arcb200_grid_fwd(const float *xyz, const void *table_half, int n_levels, int n_features, const uint32_t *offsets,
                      const float *scales, const uint32_t *resolutions, void *out_half, float *dy_dx, int64_t n,
-                     void *stream);
+                     const int32_t *n_dev, void *stream);
 
 /* Replaces the parameter-gradient half of tcnn Module.bwd for a HashGrid (bindings.cpp:111-170 ->
  * kernel_grid_backward, grid.h:394-517).  grad_table (fp32, table layout) += ...; the caller zeroes it.
  * dL_dy (n, L*F) fp16 (dy_is_half) or fp32, multiplied by gscale on the fly. */
 int arcb200_grid_bwd(const float *xyz, const void *dL_dy, int dy_is_half, float gscale, int n_levels, int n_features,
                      const uint32_t *offsets, const float *scales, const uint32_t *resolutions, float *grad_table,
-                     int64_t n, void *stream);
+                     int64_t n, const int32_t *n_dev, void *stream);
 
 /* Replaces the input-gradient half of tcnn Module.bwd (kernel_grid_backward_input, grid.h:549-576):
  * dL_dx (n,3) = dL_dy . dy_dx. */
@@ -196,7 +201,7 @@ int arcb200_grid_bwd_bwd_input(const float *xyz, const void *table_half, const v
  * direction in [-1,1] and the embedder's (d+1)/2 map is applied first; out: n rows of out_stride elements, fp16
  * (out_is_half) or fp32, first degree^2 written.  degree 1..5. */
 int arcb200_sh_fwd(const float *dirs, const int32_t *index, int degree, int remap, void *out, int out_is_half,
-                   int64_t out_stride, int64_t n, void *stream);
+                   int64_t out_stride, int64_t n, const int32_t *n_dev, void *stream);
 
 /* ---------------------------------------------------------------- tiny-cuda-nn binding: FullyFusedMLP --
  * Network: in_dim -> width (x n_hidden, hidden_act) -> out_dim (out_act), no biases; flat fp32 parameters in
@@ -213,13 +218,13 @@ int arcb200_mlp_pack_weights(const float *params, void *blob, int in_dim, int wi
  * X (n,in_dim) fp32 or fp16, leading dimension ldx; Y (n,out_dim) fp32 or fp16, leading dimension ldy. */
 int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
                     int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, int64_t n,
-                    void *stream);
+                    const int32_t *n_dev, void *stream);
 /* Replaces tcnn Module.bwd for a FullyFusedMLP (bindings.cpp:111-170 -> fully_fused_mlp.cu:150-259,702-857).
  * dY (n,out_dim) fp32; dX (n,in_dim) fp32/fp16 or NULL; dW flat fp32 in the parameter layout, ACCUMULATED.
  * loss_scale: internal fp16 gradient scale (128 in the reference, modules.py:141).  width must be 64 or 128. */
 int arcb200_mlp_bwd(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
                     int out_dim, int hidden_act, int out_act, const float *dY, int64_t ldy, float loss_scale,
-                    void *dX, int dx_is_half, int64_t ldgx, float *dW, int64_t n, void *stream);
+                    void *dX, int dx_is_half, int64_t ldgx, float *dW, int64_t n, const int32_t *n_dev, void *stream);
 
 /* ---------------------------------------------------------------- arcnerf/render/ray_helper ------------
  * Rays are segments of flat per-sample arrays: offsets (n_rays+1) int32, or NULL for dense (n_rays, dense_p)
@@ -257,6 +262,20 @@ int arcb200_sdf_to_alpha_bwd(const float *sdf, const float *zvals, const float *
  * bins, cdf (n_rays,n_bins); u (n_rays,n_sample) if u_per_ray else (n_sample); out (n_rays,n_sample) unsorted. */
 int arcb200_sample_cdf(const float *bins, const float *cdf, const float *u, int u_per_ray, float eps, float *out,
                        int64_t n_rays, int n_bins, int n_sample, void *stream);
+
+/* ---------------------------------------------------------------- arcnerf/ops/trunc_exp --------------
+ * Replaces TruncExpOps.forward / .backward (arcnerf/ops/trunc_exp.py:10-37): y = exp(x), gx = g * exp(clamp(x, +-clip)).
+ * x is read with stride ldx (fp16 or fp32) so that a column of a wider activation row can be used in place. */
+int arcb200_trunc_exp_fwd(const void *x, int x_is_half, int64_t ldx, float *y, int64_t n, const int32_t *n_dev,
+                          void *stream);
+int arcb200_trunc_exp_bwd(const void *x, int x_is_half, int64_t ldx, const float *g, float clip, float *gx, int64_t n,
+                          const int32_t *n_dev, void *stream);
+/* Gradient entering FusedMLPGeoNet's network from its two consumers (handle_output_combine,
+ * tcnn_fusedmlp_module.py:99-111, differentiated): dY (n,width) fp32 = d_feat (optional) with channel 0 increased by
+ * g_sigma * exp(clamp(x0)) where x0 is channel 0 of the stored head output. */
+int arcb200_geo_head_grad(const void *x0, int x_is_half, int64_t ldx, const float *g_sigma, float clip,
+                          const void *d_feat, int f_is_half, int64_t ldf, int width, float *dY, int64_t n,
+                          const int32_t *n_dev, void *stream);
 
 /* ---------------------------------------------------------------- training-step helpers ----------------
  * torch.optim.Adam arithmetic (common/trainer/optimizer.py -> torch) in one pass that also writes the fp16

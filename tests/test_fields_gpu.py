@@ -121,7 +121,7 @@ def test_sh(cuda, deg):
     np.testing.assert_allclose(o16, ref.astype(np.float16).astype(np.float32), rtol=2e-3, atol=1e-3)
     # gather by ray index + write into a wider row (the fused [feat | sh] input of the radiance net)
     idx = rng.randint(0, 1000, 333).astype(np.int32)
-    buf = torch.full((333, 40), 7.0, dtype=torch.float16, device=cuda)
+    buf = torch.full((333, 48), 7.0, dtype=torch.float16, device=cuda)
     F.sh_forward(T(d, cuda), deg, index=T(idx, cuda), out=buf, out_col=16)
     got = buf.float().cpu().numpy()
     assert np.all(got[:, :16] == 7.0) and np.all(got[:, 16 + deg * deg:] == 7.0)
@@ -136,6 +136,16 @@ MLP_CFGS = [
     (16, 128, 3, 20, 'softplus', 'exp'),
     (64, 32, 1, 1, 'relu', 'none'),
 ]
+
+
+def close_but(actual, desired, rtol, atol, bad_frac=2e-5, hard=10.0):
+    """allclose, except that a fraction `bad_frac` of the entries may miss the tolerance by up to `hard` times:
+    a hidden unit whose pre-activation rounds to the other side of zero (fp16) flips its ReLU gate in one row."""
+    err = np.abs(actual - desired)
+    lim = atol + rtol * np.abs(desired)
+    bad = err > lim
+    assert bad.mean() <= bad_frac, 'too many entries out of tolerance: %g' % bad.mean()
+    assert np.all(err <= hard * lim), 'entry far out of tolerance: %g' % (err / lim).max()
 
 
 def rand_params(rng, n, scale=0.35):
@@ -171,8 +181,8 @@ def test_mlp_backward(cuda, cfg, n):
     blob = F.mlp_pack(T(params, cuda), spec)
     dx, dw = F.mlp_backward(T(x, cuda), blob, spec, T(dy, cuda))
     dxo, dwo = fields.mlp_backward(x, params, dy, in_dim, width, n_hidden, out_dim, ha, oa)
-    np.testing.assert_allclose(dx.cpu().numpy(), dxo, rtol=1e-2, atol=1e-2 * np.abs(dxo).max())
-    np.testing.assert_allclose(dw.cpu().numpy(), dwo, rtol=1e-2, atol=1e-2 * np.abs(dwo).max())
+    close_but(dx.cpu().numpy(), dxo, rtol=1e-2, atol=1e-2 * np.abs(dxo).max())
+    close_but(dw.cpu().numpy(), dwo, rtol=1e-2, atol=1e-2 * np.abs(dwo).max(), bad_frac=0.0)
     # linearity in dy and accumulation into dW (size-independent properties)
     dx2, dw2 = F.mlp_backward(T(x, cuda), blob, spec, T(2 * dy, cuda), dW=dw.clone(), want_dx=True)
     np.testing.assert_allclose(dw2.cpu().numpy(), 3 * dw.cpu().numpy(), rtol=2e-2, atol=2e-2 * np.abs(dwo).max())

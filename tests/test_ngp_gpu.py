@@ -1,0 +1,97 @@
+"""GPU: the fused NGP pipeline (arcnerf_b200/ngp.py, libarcb200 kernels only) against the composed CPU oracle
+(oracle/ngp.py) on the same rays, occupancy and random-init weights.
+  bit-exact : per-ray sample counts, packed sample distances
+  tolerance : rgb/depth/mask abs 2e-3 (fp16 activations in two MLPs), loss rel 2e-3,
+              gradients rel 2e-2 of the largest entry; parameters after Adam steps abs 1e-3*lr-scale."""
+import numpy as np
+import pytest
+import torch
+
+from arcnerf_b200 import synth
+from arcnerf_b200.ngp import NGPPipeline, NGP_DEFAULTS, init_params
+from oracle.ngp import NGPOracle
+
+pytestmark = pytest.mark.gpu
+
+
+def setup(n_rays, seed, occupancy='lego', grid_scale=0.3, **over):
+    cfg = dict(NGP_DEFAULTS); cfg.update(over)
+    params = init_params(cfg, seed=seed, grid_scale=grid_scale)     # "trained-like" table so that sigma varies
+    pipe = NGPPipeline(max_rays=n_rays, capacity=1 << 18, params=params, **over)
+    orc = NGPOracle({k: v.numpy() for k, v in params.items()}, cfg)
+    vol = synth.occupancy_volume(occupancy, n=cfg['n_grid'], seed=3)
+    pipe.set_occupancy(vol); orc.set_occupancy(vol)
+    o, d = synth.train_ray_batch(n_rays, seed=seed + 1)
+    rng = np.random.RandomState(seed + 2)
+    tgt = rng.uniform(0, 1, (n_rays, 3)).astype(np.float32)
+    bkg = rng.uniform(0, 1, (n_rays, 3)).astype(np.float32)
+    return pipe, orc, o, d, tgt, bkg
+
+
+def dev(a):
+    return torch.from_numpy(a).cuda()
+
+
+def test_forward_matches_oracle():
+    pipe, orc, o, d, tgt, bkg = setup(700, 0)
+    rgb, depth, acc = pipe.forward(dev(o), dev(d), dev(bkg))
+    res = orc.forward(o, d, bkg)
+    counts = pipe.counts[:700].cpu().numpy()
+    assert np.array_equal(counts, res['counts'])                              # bit-exact sample counts
+    total = int(pipe.meta[0]); assert total == counts.sum() and int(pipe.meta[1]) == counts.max()
+    assert np.array_equal(pipe.t[:total].cpu().numpy(), res['z'][res['m']])   # bit-exact sample distances
+    np.testing.assert_allclose(rgb.cpu().numpy(), res['rgb'].numpy(), atol=2e-3, rtol=0)
+    np.testing.assert_allclose(acc.cpu().numpy(), res['mask'].numpy(), atol=2e-3, rtol=0)
+    np.testing.assert_allclose(depth.cpu().numpy(), res['depth'].numpy(), atol=1e-2, rtol=0)
+    empty = counts == 0
+    assert empty.any()
+    np.testing.assert_array_equal(rgb.cpu().numpy()[empty], bkg[empty])
+
+
+def test_training_step_gradients_and_adam():
+    pipe, orc, o, d, tgt, bkg = setup(600, 5, lr=1e-2)
+    loss = pipe.train_step(dev(o), dev(d), dev(tgt), dev(bkg), optimize=False)
+    lo, grads, res = orc.loss_and_grads(o, d, tgt, bkg)
+    assert abs(float(loss) - lo) <= 2e-3 * abs(lo)
+    for name, g in (('rad', pipe.g_rad), ('geo', pipe.g_geo), ('table', pipe.g_table)):
+        a, b = g.cpu().numpy(), grads[name]
+        scale = np.abs(b).max()
+        assert scale > 0
+        err = np.abs(a - b)
+        assert err.max() <= 2e-2 * scale, (name, err.max(), scale)
+    # the table gradient touches exactly the entries the oracle touches
+    assert np.array_equal(pipe.g_table.cpu().numpy() != 0, grads['table'] != 0) or \
+        (np.logical_xor(pipe.g_table.cpu().numpy() != 0, grads['table'] != 0).mean() < 1e-4)
+    # Adam: apply the step on both sides, several steps, compare parameters
+    pipe.optimizer_step()
+    assert float(pipe.g_table.abs().max()) == 0.0 and float(pipe.g_rad.abs().max()) == 0.0
+    orc2 = NGPOracle(dict(table=orc.table, geo=orc.geo_p, rad=orc.rad_p), orc.cfg); orc2.set_occupancy(orc.volume)
+    orc2.train_step(o, d, tgt, bkg)
+    for a, b in ((pipe.rad_p, orc2.rad_p), (pipe.geo_p, orc2.geo_p), (pipe.table, orc2.table)):
+        # first Adam step moves every touched parameter by ~lr: compare the update direction and size
+        np.testing.assert_allclose(a.cpu().numpy(), b, atol=2.5e-3, rtol=0)
+    assert torch.equal(pipe.table_h, pipe.table.half())
+    for _ in range(3):
+        l1 = float(pipe.train_step(dev(o), dev(d), dev(tgt), dev(bkg)))
+    assert np.isfinite(l1) and l1 < float(loss)          # the loss goes down on a repeated batch
+
+
+def test_render_chunks_and_capacity_clamp():
+    pipe, orc, o, d, tgt, bkg = setup(512, 9)
+    o2, d2 = synth.camera_rays(64, 48, synth.sphere_poses(1, seed=4)[0])
+    b1 = torch.ones((1, 3), device='cuda')
+    rgb, depth, acc = pipe.render(dev(o2), dev(d2), b1, chunk=512)
+    assert rgb.shape == (64 * 48, 3) and torch.isfinite(rgb).all()
+    # chunked == the same chunks run by hand with the same generator states
+    pipe.rng = type(pipe.rng)()
+    r2 = [pipe.forward(dev(o2[s:s + 512]), dev(d2[s:s + 512]), b1)[0].clone() for s in range(0, 64 * 48, 512)]
+    pipe.rng = type(pipe.rng)()
+    r3, _, _ = pipe.render(dev(o2), dev(d2), b1, chunk=512)
+    assert torch.equal(torch.cat(r2), r3)
+    # a capacity smaller than the sample count drops the overflow without touching memory out of bounds
+    small = NGPPipeline(max_rays=512, capacity=4096, params=dict(table=pipe.table.cpu(), geo=pipe.geo_p.cpu(), rad=pipe.rad_p.cpu()))
+    small.set_occupancy(synth.occupancy_volume('full'))
+    rgb_s, _, _ = small.forward(dev(o[:512]), dev(d[:512]), None)
+    assert int(small.meta[0]) > 4096 and torch.isfinite(rgb_s).all()
+    l = small.train_step(dev(o[:512]), dev(d[:512]), dev(tgt[:512]))
+    assert torch.isfinite(l).all()
