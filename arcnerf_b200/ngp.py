@@ -63,6 +63,25 @@ def init_params(cfg, seed=1337, grid_scale=1e-4, device='cpu'):
     return dict(table=table.to(device), geo=geo.to(device), rad=rad.to(device))
 
 
+class StageTimer:
+    """CUDA-event timing of named pipeline stages on the current stream (used by bench.py's roofline pass)."""
+
+    def __init__(self):
+        self.records = {}
+
+    def run(self, name, fn):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        out = fn()
+        b.record()
+        self.records.setdefault(name, []).append((a, b))
+        return out
+
+    def summary(self):
+        """name -> (mean ms, launches recorded); call after a synchronize"""
+        return {k: (sum(a.elapsed_time(b) for a, b in v) / len(v), len(v)) for k, v in self.records.items()}
+
+
 class NGPPipeline:
     def __init__(self, max_rays=4096, capacity=1 << 19, device='cuda:0', seed=1337, grid_scale=1e-4, params=None,
                  world_size=1, **overrides):
@@ -104,7 +123,11 @@ class NGPPipeline:
         self.volume = torch.ones((n, n, n), dtype=torch.bool, device=dev)
         self.dt = float(np.float32(cfg['side'] * math.sqrt(3.0)) / np.float32(cfg['n_sample']))   # diag / n_sample
         self.rng = _lib.Rng()
+        self.timer = None
         self._alloc()
+
+    def _run(self, name, fn):
+        return fn() if self.timer is None else self.timer.run(name, fn)
 
     # ------------------------------------------------------------------------------------------ buffers
     def _alloc(self):
@@ -142,33 +165,37 @@ class NGPPipeline:
         R = rays_o.shape[0]
         assert R <= self.max_rays
         st = _lib.current_stream()
-        _lib.call('arcb200_aabb_intersection', rays_o.data_ptr(), rays_d.data_ptr(), self.aabb.data_ptr(),
-                  self.near.data_ptr(), self.far.data_ptr(), None, self.hit.data_ptr(), R, 1, st)
-        _lib.call('arcb200_march_packed', 0, rays_o.data_ptr(), rays_d.data_ptr(), self.near.data_ptr(),
-                  self.far.data_ptr(), cfg['n_sample'], self.dt, self.aabb.data_ptr(), cfg['n_grid'],
-                  self.volume.data_ptr(), cfg['near_distance'], R, self.rng.state, self.rng.inc,
-                  self.scratch.data_ptr(), self.counts.data_ptr(), self.offsets.data_ptr(), self.meta.data_ptr(),
-                  self.capacity, self.t.data_ptr(), None, self.ray_id.data_ptr(), self.unit.data_ptr(), st)
+        self._run('aabb', lambda: _lib.call(
+            'arcb200_aabb_intersection', rays_o.data_ptr(), rays_d.data_ptr(), self.aabb.data_ptr(),
+            self.near.data_ptr(), self.far.data_ptr(), None, self.hit.data_ptr(), R, 1, st))
+        self._run('march_packed', lambda: _lib.call(
+            'arcb200_march_packed', 0, rays_o.data_ptr(), rays_d.data_ptr(), self.near.data_ptr(),
+            self.far.data_ptr(), cfg['n_sample'], self.dt, self.aabb.data_ptr(), cfg['n_grid'],
+            self.volume.data_ptr(), cfg['near_distance'], R, self.rng.state, self.rng.inc,
+            self.scratch.data_ptr(), self.counts.data_ptr(), self.offsets.data_ptr(), self.meta.data_ptr(),
+            self.capacity, self.t.data_ptr(), None, self.ray_id.data_ptr(), self.unit.data_ptr(), st))
         self.rng.advance()
 
     def field_forward(self, rays_d):
         """encode -> geometry head -> density | [feat, SH] -> radiance head, on the packed samples"""
         C, nd = self.capacity, self.n_dev
-        F.grid_forward(self.unit, self.table_h, self.geom, n_dev=nd, out=self.enc)
+        self._run('grid_fwd', lambda: F.grid_forward(self.unit, self.table_h, self.geom, n_dev=nd, out=self.enc))
         # geometry head writes its W_feat outputs straight into the radiance input row; SH fills the rest
-        F.mlp_forward(self.enc, self.geo_blob, self.geo_spec, out=self.rad_in, out_col=0, n_dev=nd)
-        F.sh_forward(rays_d, self.cfg['sh_degree'], index=self.ray_id, remap=True, out=self.rad_in,
-                     out_col=self.cfg['w_feat'], n_dev=nd)
-        _lib.call('arcb200_trunc_exp_fwd', self.rad_in.data_ptr(), 1, self.rad_in.stride(0), self.sigma.data_ptr(), C,
-                  nd.data_ptr(), _lib.current_stream())
-        F.mlp_forward(self.rad_in, self.rad_blob, self.rad_spec, out=self.rgb_s, n_dev=nd)
+        self._run('mlp_geo_fwd', lambda: F.mlp_forward(self.enc, self.geo_blob, self.geo_spec, out=self.rad_in, out_col=0, n_dev=nd))
+        self._run('sh_fwd', lambda: F.sh_forward(rays_d, self.cfg['sh_degree'], index=self.ray_id, remap=True, out=self.rad_in,
+                                                 out_col=self.cfg['w_feat'], n_dev=nd))
+        self._run('trunc_exp_fwd', lambda: _lib.call(
+            'arcb200_trunc_exp_fwd', self.rad_in.data_ptr(), 1, self.rad_in.stride(0), self.sigma.data_ptr(), C,
+            nd.data_ptr(), _lib.current_stream()))
+        self._run('mlp_rad_fwd', lambda: F.mlp_forward(self.rad_in, self.rad_blob, self.rad_spec, out=self.rgb_s, n_dev=nd))
 
     def composite(self, R, bkg):
         bkg_per_ray = int(bkg is not None and bkg.shape[0] == R and R > 1)
-        _lib.call('arcb200_composite_fwd', self.offsets.data_ptr(), 0, self.capacity, self.pmax.data_ptr(),
-                  self.sigma.data_ptr(), 0, self.rgb_s.data_ptr(), self.t.data_ptr(), None, 0, 0, _lib.ptr(bkg),
-                  bkg_per_ray, self.rgb.data_ptr(), self.depth.data_ptr(), self.acc.data_ptr(), None, None, None, R,
-                  _lib.current_stream())
+        self._run('composite_fwd', lambda: _lib.call(
+            'arcb200_composite_fwd', self.offsets.data_ptr(), 0, self.capacity, self.pmax.data_ptr(),
+            self.sigma.data_ptr(), 0, self.rgb_s.data_ptr(), self.t.data_ptr(), None, 0, 0, _lib.ptr(bkg),
+            bkg_per_ray, self.rgb.data_ptr(), self.depth.data_ptr(), self.acc.data_ptr(), None, None, None, R,
+            _lib.current_stream()))
 
     def forward(self, rays_o, rays_d, bkg=None):
         """-> rgb (R,3), depth (R,), mask (R,) views of the pipeline's output buffers"""
@@ -181,27 +208,35 @@ class NGPPipeline:
     def backward(self, rays_d, R, bkg):
         cfg, C, nd, st = self.cfg, self.capacity, self.n_dev, _lib.current_stream()
         bkg_per_ray = int(bkg is not None and bkg.shape[0] == R and R > 1)
-        _lib.call('arcb200_composite_bwd', self.offsets.data_ptr(), 0, C, self.pmax.data_ptr(), self.sigma.data_ptr(), 0,
-                  self.rgb_s.data_ptr(), self.t.data_ptr(), None, 0, 0, _lib.ptr(bkg), bkg_per_ray,
-                  self.g_rgb.data_ptr(), None, None, None, self.d_sigma.data_ptr(), self.d_rgb_s.data_ptr(),
-                  cfg['n_sample'], R, st)
-        F.mlp_backward(self.rad_in, self.rad_blob, self.rad_spec, self.d_rgb_s, dW=self.g_rad, dx=self.d_rad_in, n_dev=nd)
-        _lib.call('arcb200_geo_head_grad', self.rad_in.data_ptr(), 1, self.rad_in.stride(0), self.d_sigma.data_ptr(),
-                  cfg['trunc_exp_clip'], self.d_rad_in.data_ptr(), 0, self.d_rad_in.stride(0), cfg['w_feat'],
-                  self.d_geo_out.data_ptr(), C, nd.data_ptr(), st)
-        F.mlp_backward(self.enc, self.geo_blob, self.geo_spec, self.d_geo_out, dW=self.g_geo, dx=self.d_enc, n_dev=nd)
-        F.grid_backward(self.unit, self.d_enc, self.geom, grad_table=self.g_table, n_dev=nd)
+        self._run('composite_bwd', lambda: _lib.call(
+            'arcb200_composite_bwd', self.offsets.data_ptr(), 0, C, self.pmax.data_ptr(), self.sigma.data_ptr(), 0,
+            self.rgb_s.data_ptr(), self.t.data_ptr(), None, 0, 0, _lib.ptr(bkg), bkg_per_ray,
+            self.g_rgb.data_ptr(), None, None, None, self.d_sigma.data_ptr(), self.d_rgb_s.data_ptr(),
+            cfg['n_sample'], R, st))
+        self._run('mlp_rad_bwd', lambda: F.mlp_backward(self.rad_in, self.rad_blob, self.rad_spec, self.d_rgb_s,
+                                                        dW=self.g_rad, dx=self.d_rad_in, n_dev=nd))
+        self._run('geo_head_grad', lambda: _lib.call(
+            'arcb200_geo_head_grad', self.rad_in.data_ptr(), 1, self.rad_in.stride(0), self.d_sigma.data_ptr(),
+            cfg['trunc_exp_clip'], self.d_rad_in.data_ptr(), 0, self.d_rad_in.stride(0), cfg['w_feat'],
+            self.d_geo_out.data_ptr(), C, nd.data_ptr(), st))
+        self._run('mlp_geo_bwd', lambda: F.mlp_backward(self.enc, self.geo_blob, self.geo_spec, self.d_geo_out,
+                                                        dW=self.g_geo, dx=self.d_enc, n_dev=nd))
+        self._run('grid_bwd', lambda: F.grid_backward(self.unit, self.d_enc, self.geom, grad_table=self.g_table, n_dev=nd))
 
     def optimizer_step(self):
         cfg = self.cfg
         self.step_count += 1
         gs = 1.0 / self.world_size
         kw = dict(beta1=cfg['beta1'], beta2=cfg['beta2'], eps=cfg['eps'], weight_decay=cfg['weight_decay'], grad_scale=gs)
-        F.adam_step(self.table, self.m_table, self.v_table, self.g_table, self.step_count, cfg['lr'], p_half=self.table_h, **kw)
-        F.adam_step(self.geo_p, self.m_geo, self.v_geo, self.g_geo, self.step_count, cfg['lr'], **kw)
-        F.adam_step(self.rad_p, self.m_rad, self.v_rad, self.g_rad, self.step_count, cfg['lr'], **kw)
-        F.mlp_pack(self.geo_p, self.geo_spec, self.geo_blob)
-        F.mlp_pack(self.rad_p, self.rad_spec, self.rad_blob)
+        self._run('adam_table', lambda: F.adam_step(self.table, self.m_table, self.v_table, self.g_table, self.step_count,
+                                                    cfg['lr'], p_half=self.table_h, **kw))
+
+        def mlp_update():
+            F.adam_step(self.geo_p, self.m_geo, self.v_geo, self.g_geo, self.step_count, cfg['lr'], **kw)
+            F.adam_step(self.rad_p, self.m_rad, self.v_rad, self.g_rad, self.step_count, cfg['lr'], **kw)
+            F.mlp_pack(self.geo_p, self.geo_spec, self.geo_blob)
+            F.mlp_pack(self.rad_p, self.rad_spec, self.rad_blob)
+        self._run('adam_mlp+pack', mlp_update)
 
     def all_reduce_grads(self):
         """Data-parallel exchange: sum of the hash-table and MLP gradients over ranks (NCCL over NVLink); the
@@ -217,11 +252,12 @@ class NGPPipeline:
         R = rays_o.shape[0]
         self.forward(rays_o, rays_d, bkg)
         self.loss.zero_()
-        _lib.call('arcb200_huber_loss', self.rgb.data_ptr(), target.data_ptr(), self.cfg['huber_delta'],
-                  self.cfg['loss_weight'], self.g_rgb.data_ptr(), self.loss.data_ptr(), R, _lib.current_stream())
+        self._run('huber_loss', lambda: _lib.call(
+            'arcb200_huber_loss', self.rgb.data_ptr(), target.data_ptr(), self.cfg['huber_delta'],
+            self.cfg['loss_weight'], self.g_rgb.data_ptr(), self.loss.data_ptr(), R, _lib.current_stream()))
         self.backward(rays_d, R, bkg)
         if optimize:
-            self.all_reduce_grads()
+            self._run('all_reduce', self.all_reduce_grads)
             self.optimizer_step()
         return self.loss
 

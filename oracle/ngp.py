@@ -197,7 +197,7 @@ class NGPOracle:
         res = self.forward(o, d, bkg, keep=True)
         loss = render.huber_loss(res['rgb'], torch.from_numpy(target), cfg['huber_delta'], cfg['loss_weight'])
         if res['sigma_v'].numel() == 0:
-            return float(loss), dict(table=np.zeros_like(self.table), geo=np.zeros_like(self.geo_p), rad=np.zeros_like(self.rad_p)), res
+            return float(loss.detach()), dict(table=np.zeros_like(self.table), geo=np.zeros_like(self.geo_p), rad=np.zeros_like(self.rad_p)), res
         loss.backward()
         ctx = res['ctx']
         d_sigma, d_rgb = res['sigma_v'].grad, res['rgb_v'].grad
@@ -206,7 +206,7 @@ class NGPOracle:
         d_geo[:, 0] += d_sigma * torch.exp(ctx['geo_out'][:, 0].clamp(-cfg['trunc_exp_clip'], cfg['trunc_exp_clip']))
         d_enc, dw_geo = mlp_backward_t(ctx['geo_acts'], ctx['geo_y'], ctx['geo_mats'], d_geo, False, self.enc_dim)
         g_table = self.tg.backward(torch.from_numpy(ctx['pts_unit']), d_enc, self.table.size // self.F, self.F)
-        return float(loss), dict(table=g_table.reshape(-1).numpy(), geo=dw_geo.numpy(), rad=dw_rad.numpy()), res
+        return float(loss.detach()), dict(table=g_table.reshape(-1).numpy(), geo=dw_geo.numpy(), rad=dw_rad.numpy()), res
 
     def train_step(self, o, d, target, bkg=None):
         cfg = self.cfg

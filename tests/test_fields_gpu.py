@@ -148,8 +148,12 @@ def close_but(actual, desired, rtol, atol, bad_frac=2e-5, hard=10.0):
     assert np.all(err <= hard * lim), 'entry far out of tolerance: %g' % (err / lim).max()
 
 
-def rand_params(rng, n, scale=0.35):
-    return rng.uniform(-scale, scale, n).astype(np.float32)
+def rand_params(rng, n, scale=0.35, cfg=None):
+    """uniform weights; with cfg, xavier-uniform per matrix like the reference's initialiser"""
+    if cfg is None:
+        return rng.uniform(-scale, scale, n).astype(np.float32)
+    shapes, _, _ = fields.mlp_shapes(*cfg[:4])
+    return np.concatenate([rng.uniform(-1, 1, o * i) * np.sqrt(6.0 / (o + i)) for o, i in shapes]).astype(np.float32)
 
 
 @pytest.mark.parametrize('cfg', MLP_CFGS)
@@ -158,7 +162,7 @@ def test_mlp_forward(cuda, cfg, n):
     in_dim, width, n_hidden, out_dim, ha, oa = cfg
     spec = F.MlpSpec(in_dim, width, n_hidden, out_dim, ha, oa)
     rng = np.random.RandomState(4)
-    params = rand_params(rng, spec.n_params)
+    params = rand_params(rng, spec.n_params, cfg=cfg if oa == 'exp' else None)
     x = rng.uniform(-1, 1, (n, in_dim)).astype(np.float32)
     blob = F.mlp_pack(T(params, cuda), spec)
     ref = fields.mlp_forward(x, params, in_dim, width, n_hidden, out_dim, ha, oa)
@@ -175,7 +179,7 @@ def test_mlp_backward(cuda, cfg, n):
     in_dim, width, n_hidden, out_dim, ha, oa = cfg
     spec = F.MlpSpec(in_dim, width, n_hidden, out_dim, ha, oa)
     rng = np.random.RandomState(5)
-    params = rand_params(rng, spec.n_params)
+    params = rand_params(rng, spec.n_params, cfg=cfg if oa == 'exp' else None)
     x = rng.uniform(-1, 1, (n, in_dim)).astype(np.float32)
     dy = (rng.normal(size=(n, out_dim)) * 1e-2).astype(np.float32)
     blob = F.mlp_pack(T(params, cuda), spec)

@@ -175,11 +175,12 @@ def test_march_packed_matches_dense(cuda, orc):
         t = torch.full((cap,), -1.0, device=cuda)
         xyz = torch.zeros((cap, 3), device=cuda)
         rid = torch.full((cap,), -1, dtype=torch.int32, device=cuda)
+        unit = torch.zeros((cap, 3), device=cuda)
         r = _lib.Rng()
         _lib.call('arcb200_march_packed', 0, o.data_ptr(), d.data_ptr(), near.data_ptr(), far.data_ptr(), c['n_pts'],
                   float(c['dt']), aabb23.data_ptr(), c['n_grid'], vol.data_ptr(), float(c['near_distance']), n,
                   r.state, r.inc, scratch.data_ptr(), counts.data_ptr(), offsets.data_ptr(), meta.data_ptr(), cap,
-                  t.data_ptr(), xyz.data_ptr(), rid.data_ptr(), _lib.current_stream())
+                  t.data_ptr(), xyz.data_ptr(), rid.data_ptr(), unit.data_ptr(), _lib.current_stream())
         cnt = m.sum(1).to(torch.int32)
         assert torch.equal(counts, cnt)
         total = int(cnt.sum().item())
@@ -196,3 +197,5 @@ def test_march_packed_matches_dense(cuda, orc):
             oo, dd, tt = c['o'][rid_exp.cpu().numpy()], c['d'][rid_exp.cpu().numpy()], t[:total].cpu().numpy()
             exp = (oo + (dd * tt[:, None]).astype(np.float32)).astype(np.float32)
             assert np.array_equal(xyz[:total].cpu().numpy(), exp)
+            lo, hi = c['aabb'][0], c['aabb'][1]
+            assert np.array_equal(unit[:total].cpu().numpy(), ((exp - lo) / (hi - lo)).astype(np.float32))
