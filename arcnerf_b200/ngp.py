@@ -242,10 +242,8 @@ class NGPPipeline:
         """Data-parallel exchange: sum of the hash-table and MLP gradients over ranks (NCCL over NVLink); the
         reference gets the same from DDP's bucketed all-reduce (basic_trainer.py:192-202)."""
         if self.world_size > 1:
-            import torch.distributed as dist
-            dist.all_reduce(self.g_table)
-            dist.all_reduce(self.g_geo)
-            dist.all_reduce(self.g_rad)
+            from .dist import all_reduce_sum_
+            all_reduce_sum_([self.g_table, self.g_geo, self.g_rad])
 
     def train_step(self, rays_o, rays_d, target, bkg=None, optimize=True):
         """One optimisation step on a ray batch; returns the (device) loss tensor.  No host synchronisation."""

@@ -50,7 +50,7 @@ def test_forward_matches_oracle():
 
 def test_training_step_gradients_and_adam():
     pipe, orc, o, d, tgt, bkg = setup(600, 5, lr=1e-2)
-    loss = pipe.train_step(dev(o), dev(d), dev(tgt), dev(bkg), optimize=False)
+    loss = float(pipe.train_step(dev(o), dev(d), dev(tgt), dev(bkg), optimize=False))
     lo, grads, res = orc.loss_and_grads(o, d, tgt, bkg)
     assert abs(float(loss) - lo) <= 2e-3 * abs(lo)
     for name, g in (('rad', pipe.g_rad), ('geo', pipe.g_geo), ('table', pipe.g_table)):
