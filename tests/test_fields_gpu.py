@@ -227,5 +227,5 @@ def test_adam_and_huber(cuda):
     rt = torch.tensor(rgb, requires_grad=True)
     lo = render.huber_loss(rt, torch.tensor(tgt)); lo.backward()
     ls, gr = F.huber_loss(T(rgb, cuda), T(tgt, cuda))
-    np.testing.assert_allclose(float(ls), float(lo), rtol=1e-5)
+    np.testing.assert_allclose(float(ls), float(lo.detach()), rtol=1e-5)
     np.testing.assert_allclose(gr.cpu().numpy(), rt.grad.numpy(), rtol=1e-5, atol=1e-7)

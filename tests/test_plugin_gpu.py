@@ -170,6 +170,7 @@ def test_neus_functions(cuda):
     np.testing.assert_allclose(float(s.grad), float(GOLD['sdf_ds']), rtol=1e-3)
     c = render_cases.pdf_case()
     smp = ray_helper.sample_pdf(dev(c['bins']), dev(c['weights']), c['n_sample'], det=True)
-    np.testing.assert_allclose(smp.cpu().numpy(), GOLD['pdf_samples'], atol=2e-5)
+    # the cdf comes from a GPU cumsum here (different summation order than the CPU golden): 1e-4 on values in [2, 6]
+    np.testing.assert_allclose(smp.cpu().numpy(), GOLD['pdf_samples'], atol=1e-4)
     rnd = ray_helper.sample_pdf(dev(c['bins']), dev(c['weights']), 64, det=False)
     assert rnd.shape == (c['bins'].shape[0], 64) and bool((rnd[:, 1:] >= rnd[:, :-1]).all())
