@@ -36,6 +36,8 @@ _SIGS = {
     'arcb200_generate_grid_samples_multivol': [P, I, L, P, I, I, F, I, P, P, U64, U64, P],
     'arcb200_march_packed_scratch_bytes': [L, I],
     'arcb200_march_packed': [I, P, P, P, P, I, F, P, I, P, F, L, U64, U64, P, P, P, P, L, P, P, P, P, P],
+    'arcb200_march_packed_static_max_slots': [],
+    'arcb200_march_packed_static': [I, P, P, P, P, I, F, P, I, P, F, L, U64, U64, P, P, P, L, P, P, P, P, P],
     'arcb200_grid_geometry': [I, I, I, F, P, P, P],
     'arcb200_cast_f32_to_f16': [P, P, L, P],
     'arcb200_grid_fwd': [P, P, I, I, P, P, P, P, P, L, P, P],
@@ -64,6 +66,7 @@ _RESTYPE = {
     'arcb200_rng_init': None,
     'arcb200_rng_advance': None,
     'arcb200_march_packed_scratch_bytes': L,
+    'arcb200_march_packed_static_max_slots': L,
     'arcb200_grid_geometry': L,
 }
 

@@ -28,7 +28,7 @@ SOURCES = {
     'mlp_tc.cu': [],
     'optim.cu': [],
     'glue.cu': [],
-    'noalloc.cu': ['-fmad=false'],
+    'noalloc.cu': [],
 }
 
 

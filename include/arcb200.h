@@ -147,6 +147,23 @@ int arcb200_march_packed(int bit, const float *rays_o, const float *rays_d, cons
                          float *t_out, float *xyz_out, int32_t *ray_id_out, float *unit_out, void *stream);
 
 
+/* No counterpart in the reference.  arcb200_march_packed for hosts that cannot bring scratch memory: a sampler
+ * called from another engine's per-frame callback (a cudaMalloc there would synchronise the whole device and stall
+ * the engine's other streams), or a plug-in inside a host that owns all device memory through its own arena and
+ * passes in nothing but the call's input and output buffers.  The scratch is a fixed device array inside the
+ * library: 16 MiB + 4 KiB of device memory on every GPU that loads the library, until the process exits.  Same
+ * arguments (minus `scratch`) and same outputs as arcb200_march_packed.  Limits: n_rays * n_pts <= 4 194 304
+ * (arcb200_march_packed_static_max_slots) and n_rays <= 262 144; larger requests return ARCB200_ERR_LIMIT.
+ * The call allocates nothing.  Its first use on a device looks up the array's device address; make that first call
+ * before any stream capture begins.  All calls on a device share the array (stale contents are harmless, nothing
+ * in it needs clearing), so calls whose kernels could overlap on the GPU race: keep them ordered. */
+int64_t arcb200_march_packed_static_max_slots(void);
+int arcb200_march_packed_static(int bit, const float *rays_o, const float *rays_d, const float *near, const float *far,
+                                int n_pts, float dt, const float *aabb, int n_grid, const uint8_t *field,
+                                float near_distance, int64_t n_rays, uint64_t rng_state, uint64_t rng_inc,
+                                int32_t *counts, int32_t *offsets, int32_t *meta, int64_t capacity, float *t_out,
+                                float *xyz_out, int32_t *ray_id_out, float *unit_out, void *stream);
+
 /* Row counts on the device: the entry points below that take `n_dev` (device int32 or NULL) process only
  * min(n, *n_dev) rows, so the sample count produced by arcb200_march_packed (meta[0]) never has to travel to
  * the host between the sampler and the field kernels. */
