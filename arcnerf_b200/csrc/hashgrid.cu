@@ -97,12 +97,11 @@ grid_fwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__re
                 const __half *__restrict__ table, GridGeom geom, __half *__restrict__ out, float *__restrict__ dy_dx) {
     extern __shared__ __half tile[];   // [32][L*F + 2]
     if (n_dev) n = min(n, (uint32_t)max(*n_dev, 0));
-    if (blockIdx.x * kTileSamples >= n) return;
     const uint32_t L = geom.n_levels;
     const uint32_t row = L * F;
     const uint32_t pitch = row + 2;
     const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
-    const uint32_t base = blockIdx.x * kTileSamples;
+    for (uint32_t base = blockIdx.x * kTileSamples; base < n; base += gridDim.x * kTileSamples) {
     const uint32_t i = base + lane;
     const bool valid = i < n;
     float x = 0.f, y = 0.f, z = 0.f;
@@ -164,6 +163,8 @@ grid_fwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__re
             out[(size_t)base * row + k] = tile[r * pitch + cidx];
         }
     }
+    __syncthreads();   // the tile is reused by the next iteration
+    }
 }
 
 template <typename T> __device__ __forceinline__ float to_f32(T v);
@@ -194,12 +195,11 @@ grid_bwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__re
                 const float *__restrict__ v_in) {
     extern __shared__ float gtile[];   // [32][L*F + 1]
     if (n_dev) n = min(n, (uint32_t)max(*n_dev, 0));
-    if (blockIdx.x * kTileSamples >= n) return;
     const uint32_t L = geom.n_levels;
     const uint32_t row = L * F;
     const uint32_t pitch = row + 1;
     const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
-    const uint32_t base = blockIdx.x * kTileSamples;
+    for (uint32_t base = blockIdx.x * kTileSamples; base < n; base += gridDim.x * kTileSamples) {
     const uint32_t i = base + lane;
     const bool valid = i < n;
     const uint32_t n_rows = min((uint32_t)kTileSamples, n - base);
@@ -213,8 +213,7 @@ grid_bwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__re
         if (SECOND) { vx = __ldg(v_in + 3 * (size_t)i); vy = __ldg(v_in + 3 * (size_t)i + 1); vz = __ldg(v_in + 3 * (size_t)i + 2); }
     }
     __syncthreads();
-    if (!valid) return;
-    for (uint32_t level = w; level < L; level += kFwdWarps) {
+    for (uint32_t level = w; valid && level < L; level += kFwdWarps) {
         const GridLevel g = geom.lv[level];
         float *lg = grad_table + (size_t)g.offset * F;
         const Cell c = locate(g, x, y, z);
@@ -237,6 +236,8 @@ grid_bwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__re
             const uint32_t idx = entry_index(g, c.gx + cx, c.gy + cy, c.gz + cz);
             add_entry<F>(lg, idx, gr, wgt);
         }
+    }
+    __syncthreads();   // the staged gradients are reused by the next iteration
     }
 }
 
@@ -330,6 +331,12 @@ __global__ void cast_f32_f16_kernel(size_t n, const float *__restrict__ src, __h
     for (size_t k = n4 * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n; k += stride) dst[k] = __float2half_rn(src[k]);
 }
 
+unsigned tile_blocks(int64_t n) {
+    long long want = (n + kTileSamples - 1) / kTileSamples;
+    const long long cap = (long long)arc_sm_count() * 16;
+    return (unsigned)(want < cap ? (want > 0 ? want : 1) : cap);
+}
+
 int pack_geom(GridGeom &geom, int n_levels, const uint32_t *offsets, const float *scales, const uint32_t *resolutions) {
     if (n_levels < 1 || n_levels > kMaxLevels) return -1;
     geom.n_levels = (uint32_t)n_levels;
@@ -421,7 +428,7 @@ int arcb200_grid_fwd(const float *xyz, const void *table_half, int n_levels, int
     ARC_REQUIRE(xyz && table_half && out_half && offsets && scales && resolutions, "grid_fwd: null pointer");
     GridGeom geom;
     ARC_REQUIRE(pack_geom(geom, n_levels, offsets, scales, resolutions) == 0, "grid_fwd: bad level geometry");
-    const unsigned blocks = arc_blocks(n, kTileSamples);
+    const unsigned blocks = tile_blocks(n);
     const size_t smem = (size_t)kTileSamples * (n_levels * n_features + 2) * sizeof(__half);
     cudaStream_t st = (cudaStream_t)stream;
     GRID_DISPATCH_F(n_features,
@@ -444,7 +451,7 @@ int arcb200_grid_bwd(const float *xyz, const void *dL_dy, int dy_is_half, float 
     ARC_REQUIRE(xyz && dL_dy && grad_table && offsets && scales && resolutions, "grid_bwd: null pointer");
     GridGeom geom;
     ARC_REQUIRE(pack_geom(geom, n_levels, offsets, scales, resolutions) == 0, "grid_bwd: bad level geometry");
-    const unsigned blocks = arc_blocks(n, kTileSamples);
+    const unsigned blocks = tile_blocks(n);
     const size_t smem = (size_t)kTileSamples * (n_levels * n_features + 1) * sizeof(float);
     cudaStream_t st = (cudaStream_t)stream;
     GRID_DISPATCH_F(n_features,
@@ -487,7 +494,7 @@ int arcb200_grid_bwd_bwd_input(const float *xyz, const void *table_half, const v
     ARC_REQUIRE(pack_geom(geom, n_levels, offsets, scales, resolutions) == 0, "grid_bwd_bwd_input: bad level geometry");
     cudaStream_t st = (cudaStream_t)stream;
     if (grad_table) {
-        const unsigned blocks = arc_blocks(n, kTileSamples);
+        const unsigned blocks = tile_blocks(n);
         const size_t smem = (size_t)kTileSamples * (n_levels * n_features + 1) * sizeof(float);
         GRID_DISPATCH_F(n_features,
             if (dy_is_half) grid_bwd_kernel<F, __half, true><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(

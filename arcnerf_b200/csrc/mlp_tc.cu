@@ -42,24 +42,60 @@ struct MlpCfg {
     uint32_t p_off[kMaxMM];   // element offset of layer l in the flat parameter vector
 };
 
-__device__ __forceinline__ float act_fwd(int a, float x) {
+// 16 values at a time with the activation chosen once (uniform branch), not per element
+__device__ __forceinline__ void act16_fwd(int a, const uint32_t (&r)[16], float (&v)[16]) {
     switch (a) {
-        case ACT_RELU: return x > 0.f ? x : 0.f;
-        case ACT_SIGMOID: return 1.0f / (1.0f + __expf(-x));
-        case ACT_SOFTPLUS: return __logf(__expf(x * 10.0f) + 1.0f) / 10.0f;
-        case ACT_EXP: return __expf(x);
-        default: return x;
+        case ACT_RELU:
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] = fmaxf(__uint_as_float(r[k]), 0.f);
+            break;
+        case ACT_SIGMOID:
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] = 1.0f / (1.0f + __expf(-__uint_as_float(r[k])));
+            break;
+        case ACT_SOFTPLUS:
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] = __logf(__expf(__uint_as_float(r[k]) * 10.0f) + 1.0f) / 10.0f;
+            break;
+        case ACT_EXP:
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] = __expf(__uint_as_float(r[k]));
+            break;
+        default:
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] = __uint_as_float(r[k]);
     }
 }
-// derivative expressed through the activation OUTPUT y (as the reference does, common_device.h:180-225)
-__device__ __forceinline__ float act_bwd(int a, float y) {
+// v[k] *= act'(.) expressed through the activation output y[k]
+__device__ __forceinline__ void act16_bwd_mul(int a, float (&v)[16], const float (&y)[16]) {
     switch (a) {
-        case ACT_RELU: return y > 0.f ? 1.f : 0.f;
-        case ACT_SIGMOID: return y * (1.0f - y);
-        case ACT_SOFTPLUS: return 1.0f - __expf(-y * 10.0f);
-        case ACT_EXP: return y;
-        default: return 1.f;
+        case ACT_RELU:
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] = y[k] > 0.f ? v[k] : 0.f;
+            break;
+        case ACT_SIGMOID:
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] *= y[k] * (1.0f - y[k]);
+            break;
+        case ACT_SOFTPLUS:
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] *= 1.0f - __expf(-y[k] * 10.0f);
+            break;
+        case ACT_EXP:
+            #pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] *= y[k];
+            break;
+        default: break;
     }
+}
+
+// up to four 16-column accumulator blocks of this thread's row in flight, then one wait
+__device__ __forceinline__ void tmem_ld_blocks(uint32_t taddr, int nb, uint32_t (&r)[4][16]) {
+    tc05::tmem_ld16(taddr, r[0]);
+    if (nb > 1) tc05::tmem_ld16(taddr + 16, r[1]);
+    if (nb > 2) tc05::tmem_ld16(taddr + 32, r[2]);
+    if (nb > 3) tc05::tmem_ld16(taddr + 48, r[3]);
+    tc05::tmem_ld_wait();
 }
 
 template <typename T> __device__ __forceinline__ float ld_f32(const T *p);
@@ -74,22 +110,66 @@ __device__ __forceinline__ uint4 *tile_word(uint8_t *tile, int r, int cg) {
     return reinterpret_cast<uint4 *>(tile + (size_t)cg * kTileLBO + (size_t)r * 16);
 }
 
-// Row `grow` of X (fp32 or fp16, leading dimension ldx) -> fp16 row r of the tile; columns >= in_dim are 1.0
-// (the reference's identity-encoding padding), rows beyond n are zero.
+// Rows [row0, row0+128) of X (fp32 or fp16, leading dimension ldx) -> fp16 operand tile.  Columns >= in_dim are 1.0
+// (the reference's identity-encoding padding), rows beyond n are zero.  The whole CTA cooperates: 16-byte chunks
+// are visited in (row, column-group) order, i.e. in the order they lie in global memory, so a warp reads
+// consecutive addresses; `vec` (set by the host: in_dim and ldx multiples of 8, 16-byte aligned base) selects the
+// vector path, otherwise every element is loaded on its own.
 template <typename TIN>
-__device__ __forceinline__ void load_input_row(uint8_t *tile, int r, const TIN *__restrict__ X, int64_t ldx, int64_t grow,
-                                               int64_t n, int in_dim, int in_pad) {
-    for (int cg = 0; cg < in_pad / 8; ++cg) {
-        float v[8];
-        #pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const int c = cg * 8 + k;
-            v[k] = (grow < n) ? (c < in_dim ? ld_f32<TIN>(X + grow * ldx + c) : 1.0f) : 0.0f;
-        }
+__device__ __forceinline__ void load_input_tile(uint8_t *tile, const TIN *__restrict__ X, int64_t ldx, int64_t row0,
+                                                int64_t n, int in_dim, int in_pad, bool vec, int tid) {
+    const int ncg = in_pad >> 3;
+    for (int q = tid; q < kRows * ncg; q += kRows) {
+        const int r = q / ncg, cg = q - r * ncg;
+        const int64_t grow = row0 + r;
+        const int c0 = cg * 8;
         uint4 w;
-        w.x = tc05::pack_half2(v[0], v[1]); w.y = tc05::pack_half2(v[2], v[3]);
-        w.z = tc05::pack_half2(v[4], v[5]); w.w = tc05::pack_half2(v[6], v[7]);
+        if (grow >= n) {
+            w = make_uint4(0u, 0u, 0u, 0u);
+        } else if (c0 >= in_dim) {
+            w = make_uint4(0x3C003C00u, 0x3C003C00u, 0x3C003C00u, 0x3C003C00u);   // eight fp16 ones
+        } else if (vec) {
+            if (sizeof(TIN) == 2) {
+                w = __ldg(reinterpret_cast<const uint4 *>(X + grow * ldx + c0));
+            } else {
+                const float4 a = __ldg(reinterpret_cast<const float4 *>(X + grow * ldx + c0));
+                const float4 b = __ldg(reinterpret_cast<const float4 *>(X + grow * ldx + c0) + 1);
+                w.x = tc05::pack_half2(a.x, a.y); w.y = tc05::pack_half2(a.z, a.w);
+                w.z = tc05::pack_half2(b.x, b.y); w.w = tc05::pack_half2(b.z, b.w);
+            }
+        } else {
+            float v[8];
+            #pragma unroll
+            for (int k = 0; k < 8; ++k) v[k] = (c0 + k < in_dim) ? ld_f32<TIN>(X + grow * ldx + c0 + k) : 1.0f;
+            w.x = tc05::pack_half2(v[0], v[1]); w.y = tc05::pack_half2(v[2], v[3]);
+            w.z = tc05::pack_half2(v[4], v[5]); w.w = tc05::pack_half2(v[6], v[7]);
+        }
         *tile_word(tile, r, cg) = w;
+    }
+}
+
+// 16 consecutive outputs of one row -> global memory (fp32 or fp16), vector stores when the host vouches for
+// alignment (`vec`: ld and column offset keep 16-byte alignment), masked scalar stores otherwise.
+template <typename TOUT>
+__device__ __forceinline__ void store_out16(TOUT *__restrict__ dst, const float (&v)[16], int c0, int n_cols, bool vec) {
+    if (vec && c0 + 16 <= n_cols) {
+        if (sizeof(TOUT) == 2) {
+            uint4 w0, w1;
+            w0.x = tc05::pack_half2(v[0], v[1]);   w0.y = tc05::pack_half2(v[2], v[3]);
+            w0.z = tc05::pack_half2(v[4], v[5]);   w0.w = tc05::pack_half2(v[6], v[7]);
+            w1.x = tc05::pack_half2(v[8], v[9]);   w1.y = tc05::pack_half2(v[10], v[11]);
+            w1.z = tc05::pack_half2(v[12], v[13]); w1.w = tc05::pack_half2(v[14], v[15]);
+            reinterpret_cast<uint4 *>(dst + c0)[0] = w0;
+            reinterpret_cast<uint4 *>(dst + c0)[1] = w1;
+        } else {
+            #pragma unroll
+            for (int k = 0; k < 4; ++k)
+                reinterpret_cast<float4 *>(dst + c0)[k] = make_float4(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3]);
+        }
+    } else {
+        #pragma unroll
+        for (int k = 0; k < 16; ++k)
+            if (c0 + k < n_cols) st_val<TOUT>(dst + c0 + k, v[k]);
     }
 }
 
@@ -134,7 +214,8 @@ struct Shared {
 template <typename TIN, typename TOUT, uint32_t TMEM_COLS>
 __global__ void __launch_bounds__(kRows)
 mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restrict__ X, int64_t ldx,
-               const uint8_t *__restrict__ blob, MlpCfg cfg, TOUT *__restrict__ Y, int64_t ldy) {
+               const uint8_t *__restrict__ blob, const __grid_constant__ MlpCfg cfg, TOUT *__restrict__ Y, int64_t ldy,
+               int io_vec) {
     extern __shared__ __align__(128) uint8_t smem[];
     if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     Shared *sh = reinterpret_cast<Shared *>(smem);
@@ -164,7 +245,7 @@ mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
     const int64_t n_tiles = (n + kRows - 1) / kRows;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int64_t grow = tile * kRows + tid;
-        load_input_row<TIN>(a_s, tid, X, ldx, grow, n, cfg.in_dim, cfg.in_pad);
+        load_input_tile<TIN>(a_s, X, ldx, tile * kRows, n, cfg.in_dim, cfg.in_pad, (io_vec & 1) != 0, tid);
         if (!weights_ready) { tc05::mbar_wait(&sh->mbar_w, 0); weights_ready = true; }
         for (int l = 0; l < cfg.n_mm; ++l) {
             tc05::fence_proxy_async();
@@ -180,26 +261,27 @@ mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
             tc05::fence_after_sync();
             const bool last = (l == cfg.n_mm - 1);
             const int act = last ? cfg.out_act : cfg.hidden_act;
-            for (int cb = 0; cb < cfg.N[l] / 16; ++cb) {
-                uint32_t r[16];
-                tc05::tmem_ld16(my_tmem + (uint32_t)cb * 16, r);
-                tc05::tmem_ld_wait();
-                float v[16];
+            const int nblk = cfg.N[l] / 16;
+            for (int cb0 = 0; cb0 < nblk; cb0 += 4) {
+                const int nb = min(4, nblk - cb0);
+                uint32_t r[4][16];
+                tmem_ld_blocks(my_tmem + (uint32_t)cb0 * 16, nb, r);
                 #pragma unroll
-                for (int k = 0; k < 16; ++k) v[k] = act_fwd(act, __uint_as_float(r[k]));
-                if (!last) {
-                    uint4 w0, w1;
-                    w0.x = tc05::pack_half2(v[0], v[1]);   w0.y = tc05::pack_half2(v[2], v[3]);
-                    w0.z = tc05::pack_half2(v[4], v[5]);   w0.w = tc05::pack_half2(v[6], v[7]);
-                    w1.x = tc05::pack_half2(v[8], v[9]);   w1.y = tc05::pack_half2(v[10], v[11]);
-                    w1.z = tc05::pack_half2(v[12], v[13]); w1.w = tc05::pack_half2(v[14], v[15]);
-                    *tile_word(a_s, tid, 2 * cb) = w0;
-                    *tile_word(a_s, tid, 2 * cb + 1) = w1;
-                } else if (grow < n) {
-                    #pragma unroll
-                    for (int k = 0; k < 16; ++k) {
-                        const int c = cb * 16 + k;
-                        if (c < cfg.out_dim) st_val<TOUT>(Y + grow * ldy + c, v[k]);
+                for (int j = 0; j < 4; ++j) {
+                    if (j >= nb) break;
+                    const int cb = cb0 + j;
+                    float v[16];
+                    act16_fwd(act, r[j], v);
+                    if (!last) {
+                        uint4 w0, w1;
+                        w0.x = tc05::pack_half2(v[0], v[1]);   w0.y = tc05::pack_half2(v[2], v[3]);
+                        w0.z = tc05::pack_half2(v[4], v[5]);   w0.w = tc05::pack_half2(v[6], v[7]);
+                        w1.x = tc05::pack_half2(v[8], v[9]);   w1.y = tc05::pack_half2(v[10], v[11]);
+                        w1.z = tc05::pack_half2(v[12], v[13]); w1.w = tc05::pack_half2(v[14], v[15]);
+                        *tile_word(a_s, tid, 2 * cb) = w0;
+                        *tile_word(a_s, tid, 2 * cb + 1) = w1;
+                    } else if (grow < n) {
+                        store_out16<TOUT>(Y + grow * ldy, v, cb * 16, cfg.out_dim, (io_vec & 2) != 0);
                     }
                 }
             }
@@ -222,8 +304,9 @@ struct BwdPlan {
 template <typename TIN, typename TGX, uint32_t TMEM_COLS>
 __global__ void __launch_bounds__(kRows)
 mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restrict__ X, int64_t ldx,
-               const uint8_t *__restrict__ blob, MlpCfg cfg, BwdPlan plan, const float *__restrict__ dY, int64_t ldy,
-               float loss_scale, TGX *__restrict__ dX, int64_t ldgx, float *__restrict__ dW) {
+               const uint8_t *__restrict__ blob, const __grid_constant__ MlpCfg cfg, const __grid_constant__ BwdPlan plan,
+               const float *__restrict__ dY, int64_t ldy, float loss_scale, TGX *__restrict__ dX, int64_t ldgx,
+               float *__restrict__ dW, int io_vec) {
     extern __shared__ __align__(128) uint8_t smem[];
     if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     Shared *sh = reinterpret_cast<Shared *>(smem);
@@ -281,7 +364,7 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
     const int64_t n_tiles = (n + kRows - 1) / kRows;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         const int64_t grow = tile * kRows + tid;
-        load_input_row<TIN>(x_s, tid, X, ldx, grow, n, cfg.in_dim, cfg.in_pad);
+        load_input_tile<TIN>(x_s, X, ldx, tile * kRows, n, cfg.in_dim, cfg.in_pad, (io_vec & 1) != 0, tid);
         if (!weights_ready) { tc05::mbar_wait(&sh->mbar_w, 0); weights_ready = true; }
 
         // ---- forward re-computation; hidden activations stay in shared memory
@@ -289,25 +372,41 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
             const uint32_t a_tile = l == 0 ? x_addr : h_addr + (uint32_t)((l - 1) * h_bytes);
             sync_issue_wait([&] { issue_forward_mm(tmem, a_tile, w_addr + cfg.w_off[l], cfg.K[l], cfg.N[l]); });
             const bool last = (l == cfg.n_mm - 1);
-            for (int cb = 0; cb < cfg.N[l] / 16; ++cb) {
-                uint32_t r[16];
-                tc05::tmem_ld16(my_tmem + (uint32_t)cb * 16, r);
-                tc05::tmem_ld_wait();
-                float v[16];
-                if (!last) {
-                    #pragma unroll
-                    for (int k = 0; k < 16; ++k) v[k] = act_fwd(cfg.hidden_act, __uint_as_float(r[k]));
-                    store16(h_s + (size_t)l * h_bytes, cb, v);
-                } else {
-                    // gradient w.r.t. the last pre-activation, scaled; padded outputs and rows carry none
-                    #pragma unroll
-                    for (int k = 0; k < 16; ++k) {
-                        const int c = cb * 16 + k;
-                        const float y = act_fwd(cfg.out_act, __uint_as_float(r[k]));
-                        const float g = (grow < n && c < cfg.out_dim) ? __ldg(dY + grow * ldy + c) : 0.0f;
-                        v[k] = g * act_bwd(cfg.out_act, y) * loss_scale;
+            const int nblk = cfg.N[l] / 16;
+            for (int cb0 = 0; cb0 < nblk; cb0 += 4) {
+                const int nb = min(4, nblk - cb0);
+                uint32_t r[4][16];
+                tmem_ld_blocks(my_tmem + (uint32_t)cb0 * 16, nb, r);
+                #pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (j >= nb) break;
+                    const int cb = cb0 + j;
+                    float v[16];
+                    if (!last) {
+                        act16_fwd(cfg.hidden_act, r[j], v);
+                        store16(h_s + (size_t)l * h_bytes, cb, v);
+                    } else {
+                        // gradient w.r.t. the last pre-activation, scaled; padded outputs and rows carry none
+                        float g[16], y[16];
+                        if ((io_vec & 4) && grow < n && cb * 16 + 16 <= cfg.out_dim) {
+                            #pragma unroll
+                            for (int k = 0; k < 4; ++k) {
+                                const float4 q = __ldg(reinterpret_cast<const float4 *>(dY + grow * ldy + cb * 16) + k);
+                                g[4 * k] = q.x; g[4 * k + 1] = q.y; g[4 * k + 2] = q.z; g[4 * k + 3] = q.w;
+                            }
+                        } else {
+                            #pragma unroll
+                            for (int k = 0; k < 16; ++k) {
+                                const int c = cb * 16 + k;
+                                g[k] = (grow < n && c < cfg.out_dim) ? __ldg(dY + grow * ldy + c) : 0.0f;
+                            }
+                        }
+                        act16_fwd(cfg.out_act, r[j], y);
+                        #pragma unroll
+                        for (int k = 0; k < 16; ++k) v[k] = g[k] * loss_scale;
+                        act16_bwd_mul(cfg.out_act, v, y);
+                        store16(g_s, cb, v);
                     }
-                    store16(g_s, cb, v);
                 }
             }
         }
@@ -322,29 +421,35 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
                 if (need_dgrad) issue_dgrad_mm(tmem, g_addr, w_addr + cfg.w_off[l], cfg.K[l], cfg.N[l]);
             });
             if (!need_dgrad) continue;
-            for (int cb = 0; cb < cfg.K[l] / 16; ++cb) {
-                uint32_t r[16];
-                tc05::tmem_ld16(my_tmem + (uint32_t)cb * 16, r);
-                tc05::tmem_ld_wait();
-                float v[16];
-                if (l > 0) {
-                    // through the hidden activation of layer l-1 (derivative from its stored output)
-                    const uint8_t *hp = h_s + (size_t)(l - 1) * h_bytes;
-                    const uint4 a = *tile_word(const_cast<uint8_t *>(hp), tid, 2 * cb);
-                    const uint4 b = *tile_word(const_cast<uint8_t *>(hp), tid, 2 * cb + 1);
-                    const uint32_t hw[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-                    #pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        const float2 h2 = __half22float2(*reinterpret_cast<const __half2 *>(&hw[k]));
-                        v[2 * k] = __uint_as_float(r[2 * k]) * act_bwd(cfg.hidden_act, h2.x);
-                        v[2 * k + 1] = __uint_as_float(r[2 * k + 1]) * act_bwd(cfg.hidden_act, h2.y);
-                    }
-                    store16(g_s, cb, v);
-                } else if (grow < n) {
-                    #pragma unroll
-                    for (int k = 0; k < 16; ++k) {
-                        const int c = cb * 16 + k;
-                        if (c < cfg.in_dim) st_val<TGX>(dX + grow * ldgx + c, __uint_as_float(r[k]) * inv_scale);
+            const int nblk = cfg.K[l] / 16;
+            for (int cb0 = 0; cb0 < nblk; cb0 += 4) {
+                const int nb = min(4, nblk - cb0);
+                uint32_t r[4][16];
+                tmem_ld_blocks(my_tmem + (uint32_t)cb0 * 16, nb, r);
+                #pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (j >= nb) break;
+                    const int cb = cb0 + j;
+                    float v[16];
+                    if (l > 0) {
+                        // through the hidden activation of layer l-1 (derivative from its stored output)
+                        uint8_t *hp = h_s + (size_t)(l - 1) * h_bytes;
+                        const uint4 a = *tile_word(hp, tid, 2 * cb);
+                        const uint4 b = *tile_word(hp, tid, 2 * cb + 1);
+                        const uint32_t hw[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+                        float y[16];
+                        #pragma unroll
+                        for (int k = 0; k < 8; ++k) {
+                            const float2 h2 = __half22float2(*reinterpret_cast<const __half2 *>(&hw[k]));
+                            y[2 * k] = h2.x; y[2 * k + 1] = h2.y;
+                            v[2 * k] = __uint_as_float(r[j][2 * k]); v[2 * k + 1] = __uint_as_float(r[j][2 * k + 1]);
+                        }
+                        act16_bwd_mul(cfg.hidden_act, v, y);
+                        store16(g_s, cb, v);
+                    } else if (grow < n) {
+                        #pragma unroll
+                        for (int k = 0; k < 16; ++k) v[k] = __uint_as_float(r[j][k]) * inv_scale;
+                        store_out16<TGX>(dX + grow * ldgx, v, cb * 16, cfg.in_dim, (io_vec & 2) != 0);
                     }
                 }
             }
@@ -368,13 +473,20 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
                 tc05::tmem_ld16(my_tmem + plan.wg_col[l] + (uint32_t)cb * 16, r);
                 tc05::tmem_ld_wait();
                 if (!owner) continue;
-                #pragma unroll
-                for (int k = 0; k < 16; ++k) {
-                    const int col = cb * 16 + k;
-                    const float g = __uint_as_float(r[k]) * inv_scale;
-                    // plain: acc[out][in]; transposed: acc[in][out]; parameters are (out x in) row-major
-                    const int o = plan.wg_t[l] ? col : row, i = plan.wg_t[l] ? row : col;
-                    if (g != 0.0f) atomicAdd(dst + (size_t)o * cfg.K[l] + i, g);
+                if (!plan.wg_t[l]) {
+                    // acc[out = row][in = col]: 16 consecutive parameters -> four 16-byte vector atomics
+                    float4 *d4 = reinterpret_cast<float4 *>(dst + (size_t)row * cfg.K[l] + cb * 16);
+                    #pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        atomicAdd(d4 + k, make_float4(__uint_as_float(r[4 * k]) * inv_scale, __uint_as_float(r[4 * k + 1]) * inv_scale,
+                                                      __uint_as_float(r[4 * k + 2]) * inv_scale, __uint_as_float(r[4 * k + 3]) * inv_scale));
+                } else {
+                    // acc[in = row][out = col]; parameters are (out x in) row-major
+                    #pragma unroll
+                    for (int k = 0; k < 16; ++k) {
+                        const float g = __uint_as_float(r[k]) * inv_scale;
+                        if (g != 0.0f) atomicAdd(dst + (size_t)(cb * 16 + k) * cfg.K[l] + row, g);
+                    }
                 }
             }
         }
@@ -512,13 +624,20 @@ int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob,
     ARC_REQUIRE(ldx >= in_dim && ldy >= out_dim, "mlp_fwd: leading dimension too small");
     const size_t smem = fwd_smem(c);
     cudaStream_t st = (cudaStream_t)stream;
+    // vector I/O when rows keep 16-byte alignment: bit 0 input, bit 1 output
+    int io_vec = 0;
+    if (in_dim % 8 == 0 && ldx % 8 == 0 && ((uintptr_t)X & 15u) == 0) io_vec |= 1;
+    {
+        const int esz = y_is_half ? 2 : 4;
+        if ((ldy * esz) % 16 == 0 && ((uintptr_t)Y & 15u) == 0) io_vec |= 2;
+    }
     constexpr uint32_t COLS = 128;
     const unsigned grid = mlp_grid(n, smem, COLS);
 #define LAUNCH_FWD(TI, TO)                                                                                  \
     do {                                                                                                    \
         int rc = set_smem(mlp_fwd_kernel<TI, TO, COLS>, smem);                                              \
         if (rc != ARCB200_OK) return rc;                                                                    \
-        mlp_fwd_kernel<TI, TO, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, (TO *)Y, ldy); \
+        mlp_fwd_kernel<TI, TO, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, (TO *)Y, ldy, io_vec); \
     } while (0)
     if (x_is_half) { if (y_is_half) LAUNCH_FWD(__half, __half); else LAUNCH_FWD(__half, float); }
     else { if (y_is_half) LAUNCH_FWD(float, __half); else LAUNCH_FWD(float, float); }
@@ -548,13 +667,18 @@ int arcb200_mlp_bwd(const void *X, int x_is_half, int64_t ldx, const void *blob,
     if (cols > 512) { arcb200_set_error("mlp_bwd: %d TMEM columns needed, 512 available", cols); return ARCB200_ERR_LIMIT; }
     const size_t smem = bwd_smem(c);
     cudaStream_t st = (cudaStream_t)stream;
+    // vector I/O flags: bit 0 input X, bit 1 output dX, bit 2 dY
+    int io_vec = 0;
+    if (in_dim % 8 == 0 && ldx % 8 == 0 && ((uintptr_t)X & 15u) == 0) io_vec |= 1;
+    if (dX && (ldgx * (dx_is_half ? 2 : 4)) % 16 == 0 && ((uintptr_t)dX & 15u) == 0) io_vec |= 2;
+    if (ldy % 4 == 0 && ((uintptr_t)dY & 15u) == 0) io_vec |= 4;
 #define LAUNCH_BWD(TI, TG, COLS)                                                                            \
     do {                                                                                                    \
         int rc = set_smem(mlp_bwd_kernel<TI, TG, COLS>, smem);                                              \
         if (rc != ARCB200_OK) return rc;                                                                    \
         const unsigned grid = mlp_grid(n, smem, COLS);                                                      \
         mlp_bwd_kernel<TI, TG, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, plan, dY, \
-                                                               ldy, loss_scale, (TG *)dX, ldgx, dW);        \
+                                                               ldy, loss_scale, (TG *)dX, ldgx, dW, io_vec); \
     } while (0)
 #define LAUNCH_BWD_T(COLS)                                                                                  \
     do {                                                                                                    \

@@ -48,25 +48,38 @@ __device__ __forceinline__ void sh_basis(float x, float y, float z, int degree, 
     o[24] = -3.7550144126950569f * x2 * y2 + 0.62583573544917614f * x4 + 0.62583573544917614f * y4;
 }
 
-// One thread per direction; dirs may be indexed through `index` (e.g. the ray id of a packed sample, so
-// that per-ray directions need not be repeated per sample as fg_model.py:289 does).
+// One thread per direction (grid-stride); dirs may be indexed through `index` (e.g. the ray id of a packed sample,
+// so that per-ray directions need not be repeated per sample as fg_model.py:289 does).  fp16 rows whose start is
+// 16-byte aligned are written with 16-byte stores.
 template <typename OUT>
 __global__ void sh_fwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__restrict__ dirs,
                               const int32_t *__restrict__ index, int degree, int remap, OUT *__restrict__ out,
-                              uint32_t out_stride) {
+                              uint32_t out_stride, int vec) {
     if (n_dev) n = min(n, (uint32_t)max(*n_dev, 0));
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const size_t src = index ? (size_t)index[i] : (size_t)i;
-    float x = __ldg(dirs + 3 * src), y = __ldg(dirs + 3 * src + 1), z = __ldg(dirs + 3 * src + 2);
-    if (remap) { x = (x + 1.0f) / 2.0f; y = (y + 1.0f) / 2.0f; z = (z + 1.0f) / 2.0f; }
-    x = fmaf(x, 2.f, -1.f); y = fmaf(y, 2.f, -1.f); z = fmaf(z, 2.f, -1.f);
-    float o[25];
-    sh_basis(x, y, z, degree, o);
-    OUT *dst = out + (size_t)i * out_stride;
     const int nd = degree * degree;
-    #pragma unroll
-    for (int k = 0; k < 25; ++k) if (k < nd) dst[k] = cvt<OUT>(o[k]);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const size_t src = index ? (size_t)index[i] : (size_t)i;
+        float x = __ldg(dirs + 3 * src), y = __ldg(dirs + 3 * src + 1), z = __ldg(dirs + 3 * src + 2);
+        if (remap) { x = (x + 1.0f) / 2.0f; y = (y + 1.0f) / 2.0f; z = (z + 1.0f) / 2.0f; }
+        x = fmaf(x, 2.f, -1.f); y = fmaf(y, 2.f, -1.f); z = fmaf(z, 2.f, -1.f);
+        float o[32];
+        sh_basis(x, y, z, degree, o);
+        OUT *dst = out + (size_t)i * out_stride;
+        if (sizeof(OUT) == 2 && vec && nd == 16) {
+            uint4 w[2];
+            uint32_t *pw = reinterpret_cast<uint32_t *>(w);
+            #pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                __half2 h = __floats2half2_rn(o[2 * k], o[2 * k + 1]);
+                pw[k] = *reinterpret_cast<uint32_t *>(&h);
+            }
+            reinterpret_cast<uint4 *>(dst)[0] = w[0];
+            reinterpret_cast<uint4 *>(dst)[1] = w[1];
+        } else {
+            #pragma unroll
+            for (int k = 0; k < 25; ++k) if (k < nd) dst[k] = cvt<OUT>(o[k]);
+        }
+    }
 }
 
 }  // namespace
@@ -84,12 +97,16 @@ int arcb200_sh_fwd(const float *dirs, const int32_t *index, int degree, int rema
     ARC_REQUIRE(dirs && out, "sh_fwd: null pointer");
     ARC_REQUIRE(degree >= 1 && degree <= 5, "sh_fwd: degree must be 1..5");
     ARC_REQUIRE(out_stride >= degree * degree, "sh_fwd: out_stride smaller than degree^2");
+    long long blocks = (n + 255) / 256;
+    const long long cap = (long long)arc_sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    const int vec = out_is_half && (((uintptr_t)out & 15u) == 0) && ((out_stride * 2) % 16 == 0);
     if (out_is_half)
-        sh_fwd_kernel<__half><<<arc_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>((uint32_t)n, n_dev, dirs, index, degree, remap,
-                                                                                   (__half *)out, (uint32_t)out_stride);
+        sh_fwd_kernel<__half><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((uint32_t)n, n_dev, dirs, index, degree, remap,
+                                                                                (__half *)out, (uint32_t)out_stride, vec);
     else
-        sh_fwd_kernel<float><<<arc_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>((uint32_t)n, n_dev, dirs, index, degree, remap,
-                                                                                  (float *)out, (uint32_t)out_stride);
+        sh_fwd_kernel<float><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((uint32_t)n, n_dev, dirs, index, degree, remap,
+                                                                               (float *)out, (uint32_t)out_stride, 0);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
