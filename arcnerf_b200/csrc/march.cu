@@ -95,8 +95,13 @@ march_warp_kernel(uint32_t n_rays, const float *__restrict__ rays_o, const float
     float reach = -CUDART_INF_F;  // ... whose chain value is >= reach
     float last_t = 0.0f;
     bool done = false;
+    const uint32_t lane_lt = (1u << lane) - 1u;
 
+    uint32_t chunks = 0;
     while (!done) {
+        // a step too small to move t (t + dt == t) would never terminate, here as in the reference: give up after
+        // 4 Mi links instead of hanging the device
+        if (++chunks > (1u << 17)) break;
         // 32 consecutive links of the chain; every lane runs the same 32 dependent adds.
         float mine = chain;
         #pragma unroll
@@ -113,30 +118,62 @@ march_warp_kernel(uint32_t n_rays, const float *__restrict__ rays_o, const float
         const uint32_t live_mask = __ballot_sync(ARC_FULL_MASK, live);
         const uint32_t occ_mask = __ballot_sync(ARC_FULL_MASK, occ);
 
-        for (;;) {
-            const uint32_t cand = __ballot_sync(ARC_FULL_MASK, lane >= first_lane && mine >= reach);
-            if (cand == 0) { first_lane = 0; break; }             // next visit lies in a later chunk
-            const uint32_t v = __ffs(cand) - 1;
-            if (!((live_mask >> v) & 1u)) { done = true; break; }  // past far / outside the box
-            if ((occ_mask >> v) & 1u) {
-                const uint32_t rest = ~(occ_mask >> v);
-                uint32_t run = rest ? (uint32_t)(__ffs(rest) - 1) : 32u;   // consecutive occupied links from v
-                if (run > n_pts - emitted) run = n_pts - emitted;
-                if (lane >= v && lane < v + run) {
-                    z_row[emitted + (lane - v)] = mine;
-                    if (m_row) m_row[emitted + (lane - v)] = 1;
-                }
-                last_t = __shfl_sync(ARC_FULL_MASK, mine, (v + run - 1) & 31u);
-                emitted += run;
-                if (emitted >= n_pts) { done = true; break; }
-                first_lane = v + run;
-                reach = -CUDART_INF_F;
-                if (first_lane >= 32) { first_lane = 0; break; }
-            } else {
-                reach = __shfl_sync(ARC_FULL_MASK, skip_to, v);
-                first_lane = v + 1;   // do-while: at least one link
-                if (first_lane >= 32) { first_lane = 0; break; }
+        // entry link of this chunk
+        // (`!(c < reach)` rather than `c >= reach`: a NaN target ends the reference's do-while after one step)
+        const uint32_t cand = __ballot_sync(ARC_FULL_MASK, lane >= first_lane && !(mine < reach));
+        if (cand == 0) { first_lane = 0; continue; }                 // the next visit lies in a later chunk
+        const uint32_t entry = __ffs(cand) - 1;
+
+        // successor of every link inside the chunk (32 = leaves the chunk): an occupied link steps to the next
+        // one, an empty link to the first link whose chain value reaches its skip target (at least one step,
+        // the reference's do-while).  The chain is non-decreasing over lanes: lower bound by 5 shuffles.
+        uint32_t hop;
+        {
+            uint32_t lo = 0;
+            #pragma unroll
+            for (uint32_t step = 16; step >= 1; step >>= 1) {
+                const float probe = __shfl_sync(ARC_FULL_MASK, mine, lo + step - 1);
+                if (probe < skip_to) lo += step;
             }
+            const float c31 = __shfl_sync(ARC_FULL_MASK, mine, 31);
+            if (lo == 31 && c31 < skip_to) lo = 32;
+            hop = occ ? lane + 1 : max(lane + 1, lo);
+        }
+        // links visited from the entry: reachability by pointer doubling (5 rounds cover 31 hops)
+        uint32_t visited = 1u << entry;
+        #pragma unroll
+        for (int r = 0; r < 5; ++r) {
+            const uint32_t add = (((visited >> lane) & 1u) && hop < 32) ? (1u << hop) : 0u;
+            visited |= __reduce_or_sync(ARC_FULL_MASK, add);
+            const uint32_t hop2 = __shfl_sync(ARC_FULL_MASK, hop, hop & 31u);
+            hop = hop < 32 ? hop2 : 32u;
+        }
+        // the walk ends at the first visited link that is past `far` or outside the box
+        const uint32_t stop = visited & ~live_mask;
+        uint32_t valid = visited;
+        if (stop) { valid &= (1u << (__ffs(stop) - 1)) - 1u; done = true; }
+        // warp-level compaction of the occupied visited links: rank inside the set + running count = slot
+        const uint32_t emit = valid & occ_mask;
+        const uint32_t room = n_pts - emitted;
+        const uint32_t rank = __popc(emit & lane_lt);
+        const bool write = ((emit >> lane) & 1u) && rank < room;
+        if (write) {
+            z_row[emitted + rank] = mine;
+            if (m_row) m_row[emitted + rank] = 1;
+        }
+        const uint32_t wrote = __ballot_sync(ARC_FULL_MASK, write);
+        if (wrote) {
+            last_t = __shfl_sync(ARC_FULL_MASK, mine, 31 - __clz(wrote));
+            emitted += __popc(wrote);
+        }
+        if (emitted >= n_pts) done = true;
+        if (!done) {
+            // leave the chunk through the last visited link: an occupied one continues with the very next link,
+            // an empty one carries its skip target into the next chunk
+            const uint32_t last = 31 - __clz(valid);
+            const float carry = __shfl_sync(ARC_FULL_MASK, skip_to, last);
+            reach = ((occ_mask >> last) & 1u) ? -CUDART_INF_F : carry;
+            first_lane = 0;
         }
     }
 
