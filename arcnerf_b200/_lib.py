@@ -58,7 +58,8 @@ _SIGS = {
     'arcb200_trunc_exp_fwd': [P, I, L, P, L, P, P],
     'arcb200_trunc_exp_bwd': [P, I, L, P, F, P, L, P, P],
     'arcb200_geo_head_grad': [P, I, L, P, F, P, I, L, I, P, L, P, P],
-    'arcb200_adam_step': [P, P, P, P, P, L, I, F, F, F, F, F, F, I, P],
+    'arcb200_adam_step': [P, P, P, P, P, L, I, F, F, F, F, F, F, I, P, P],
+    'arcb200_counter_add': [P, I, P],
     'arcb200_huber_loss': [P, P, F, F, P, P, L, P],
 }
 _RESTYPE = {

@@ -89,13 +89,27 @@ __device__ __forceinline__ void act16_bwd_mul(int a, float (&v)[16], const float
     }
 }
 
-// up to four 16-column accumulator blocks of this thread's row in flight, then one wait
-__device__ __forceinline__ void tmem_ld_blocks(uint32_t taddr, int nb, uint32_t (&r)[4][16]) {
-    tc05::tmem_ld16(taddr, r[0]);
-    if (nb > 1) tc05::tmem_ld16(taddr + 16, r[1]);
-    if (nb > 2) tc05::tmem_ld16(taddr + 32, r[2]);
-    if (nb > 3) tc05::tmem_ld16(taddr + 48, r[3]);
-    tc05::tmem_ld_wait();
+// Visit this thread's accumulator row in 16-column blocks: fn(block index, 16 raw fp32 words).  Four blocks are
+// handled per trip; the TMEM loads of the second pair are in flight while the first pair is being processed.
+template <class Fn>
+__device__ __forceinline__ void for_each_acc_block(uint32_t taddr, int nblk, Fn fn) {
+    for (int cb0 = 0; cb0 < nblk; cb0 += 4) {
+        const int nb = min(4, nblk - cb0);
+        uint32_t r0[16], r1[16], r2[16], r3[16];
+        const uint32_t a = taddr + (uint32_t)cb0 * 16;
+        tc05::tmem_ld16(a, r0);
+        if (nb > 1) tc05::tmem_ld16(a + 16, r1);
+        tc05::tmem_ld_wait();
+        if (nb > 2) tc05::tmem_ld16(a + 32, r2);
+        if (nb > 3) tc05::tmem_ld16(a + 48, r3);
+        fn(cb0, r0);
+        if (nb > 1) fn(cb0 + 1, r1);
+        if (nb > 2) {
+            tc05::tmem_ld_wait();
+            fn(cb0 + 2, r2);
+            if (nb > 3) fn(cb0 + 3, r3);
+        }
+    }
 }
 
 template <typename T> __device__ __forceinline__ float ld_f32(const T *p);
@@ -212,7 +226,7 @@ struct Shared {
 
 // ---------------------------------------------------------------------------------------------- forward
 template <typename TIN, typename TOUT, uint32_t TMEM_COLS>
-__global__ void __launch_bounds__(kRows)
+__global__ void __launch_bounds__(kRows, TMEM_COLS == 64 ? 7 : 4)
 mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restrict__ X, int64_t ldx,
                const uint8_t *__restrict__ blob, const __grid_constant__ MlpCfg cfg, TOUT *__restrict__ Y, int64_t ldy,
                int io_vec) {
@@ -261,30 +275,21 @@ mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
             tc05::fence_after_sync();
             const bool last = (l == cfg.n_mm - 1);
             const int act = last ? cfg.out_act : cfg.hidden_act;
-            const int nblk = cfg.N[l] / 16;
-            for (int cb0 = 0; cb0 < nblk; cb0 += 4) {
-                const int nb = min(4, nblk - cb0);
-                uint32_t r[4][16];
-                tmem_ld_blocks(my_tmem + (uint32_t)cb0 * 16, nb, r);
-                #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    if (j >= nb) break;
-                    const int cb = cb0 + j;
-                    float v[16];
-                    act16_fwd(act, r[j], v);
-                    if (!last) {
-                        uint4 w0, w1;
-                        w0.x = tc05::pack_half2(v[0], v[1]);   w0.y = tc05::pack_half2(v[2], v[3]);
-                        w0.z = tc05::pack_half2(v[4], v[5]);   w0.w = tc05::pack_half2(v[6], v[7]);
-                        w1.x = tc05::pack_half2(v[8], v[9]);   w1.y = tc05::pack_half2(v[10], v[11]);
-                        w1.z = tc05::pack_half2(v[12], v[13]); w1.w = tc05::pack_half2(v[14], v[15]);
-                        *tile_word(a_s, tid, 2 * cb) = w0;
-                        *tile_word(a_s, tid, 2 * cb + 1) = w1;
-                    } else if (grow < n) {
-                        store_out16<TOUT>(Y + grow * ldy, v, cb * 16, cfg.out_dim, (io_vec & 2) != 0);
-                    }
+            for_each_acc_block(my_tmem, cfg.N[l] / 16, [&](int cb, const uint32_t (&rr)[16]) {
+                float v[16];
+                act16_fwd(act, rr, v);
+                if (!last) {
+                    uint4 w0, w1;
+                    w0.x = tc05::pack_half2(v[0], v[1]);   w0.y = tc05::pack_half2(v[2], v[3]);
+                    w0.z = tc05::pack_half2(v[4], v[5]);   w0.w = tc05::pack_half2(v[6], v[7]);
+                    w1.x = tc05::pack_half2(v[8], v[9]);   w1.y = tc05::pack_half2(v[10], v[11]);
+                    w1.z = tc05::pack_half2(v[12], v[13]); w1.w = tc05::pack_half2(v[14], v[15]);
+                    *tile_word(a_s, tid, 2 * cb) = w0;
+                    *tile_word(a_s, tid, 2 * cb + 1) = w1;
+                } else if (grow < n) {
+                    store_out16<TOUT>(Y + grow * ldy, v, cb * 16, cfg.out_dim, (io_vec & 2) != 0);
                 }
-            }
+            });
         }
     }
     tc05::fence_before_sync();
@@ -372,43 +377,34 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
             const uint32_t a_tile = l == 0 ? x_addr : h_addr + (uint32_t)((l - 1) * h_bytes);
             sync_issue_wait([&] { issue_forward_mm(tmem, a_tile, w_addr + cfg.w_off[l], cfg.K[l], cfg.N[l]); });
             const bool last = (l == cfg.n_mm - 1);
-            const int nblk = cfg.N[l] / 16;
-            for (int cb0 = 0; cb0 < nblk; cb0 += 4) {
-                const int nb = min(4, nblk - cb0);
-                uint32_t r[4][16];
-                tmem_ld_blocks(my_tmem + (uint32_t)cb0 * 16, nb, r);
-                #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    if (j >= nb) break;
-                    const int cb = cb0 + j;
-                    float v[16];
-                    if (!last) {
-                        act16_fwd(cfg.hidden_act, r[j], v);
-                        store16(h_s + (size_t)l * h_bytes, cb, v);
-                    } else {
-                        // gradient w.r.t. the last pre-activation, scaled; padded outputs and rows carry none
-                        float g[16], y[16];
-                        if ((io_vec & 4) && grow < n && cb * 16 + 16 <= cfg.out_dim) {
-                            #pragma unroll
-                            for (int k = 0; k < 4; ++k) {
-                                const float4 q = __ldg(reinterpret_cast<const float4 *>(dY + grow * ldy + cb * 16) + k);
-                                g[4 * k] = q.x; g[4 * k + 1] = q.y; g[4 * k + 2] = q.z; g[4 * k + 3] = q.w;
-                            }
-                        } else {
-                            #pragma unroll
-                            for (int k = 0; k < 16; ++k) {
-                                const int c = cb * 16 + k;
-                                g[k] = (grow < n && c < cfg.out_dim) ? __ldg(dY + grow * ldy + c) : 0.0f;
-                            }
-                        }
-                        act16_fwd(cfg.out_act, r[j], y);
+            for_each_acc_block(my_tmem, cfg.N[l] / 16, [&](int cb, const uint32_t (&rr)[16]) {
+                float v[16];
+                if (!last) {
+                    act16_fwd(cfg.hidden_act, rr, v);
+                    store16(h_s + (size_t)l * h_bytes, cb, v);
+                } else {
+                    // gradient w.r.t. the last pre-activation, scaled; padded outputs and rows carry none
+                    float g[16], y[16];
+                    if ((io_vec & 4) && grow < n && cb * 16 + 16 <= cfg.out_dim) {
                         #pragma unroll
-                        for (int k = 0; k < 16; ++k) v[k] = g[k] * loss_scale;
-                        act16_bwd_mul(cfg.out_act, v, y);
-                        store16(g_s, cb, v);
+                        for (int k = 0; k < 4; ++k) {
+                            const float4 q = __ldg(reinterpret_cast<const float4 *>(dY + grow * ldy + cb * 16) + k);
+                            g[4 * k] = q.x; g[4 * k + 1] = q.y; g[4 * k + 2] = q.z; g[4 * k + 3] = q.w;
+                        }
+                    } else {
+                        #pragma unroll
+                        for (int k = 0; k < 16; ++k) {
+                            const int c = cb * 16 + k;
+                            g[k] = (grow < n && c < cfg.out_dim) ? __ldg(dY + grow * ldy + c) : 0.0f;
+                        }
                     }
+                    act16_fwd(cfg.out_act, rr, y);
+                    #pragma unroll
+                    for (int k = 0; k < 16; ++k) v[k] = g[k] * loss_scale;
+                    act16_bwd_mul(cfg.out_act, v, y);
+                    store16(g_s, cb, v);
                 }
-            }
+            });
         }
 
         // ---- backward chain
@@ -421,38 +417,29 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
                 if (need_dgrad) issue_dgrad_mm(tmem, g_addr, w_addr + cfg.w_off[l], cfg.K[l], cfg.N[l]);
             });
             if (!need_dgrad) continue;
-            const int nblk = cfg.K[l] / 16;
-            for (int cb0 = 0; cb0 < nblk; cb0 += 4) {
-                const int nb = min(4, nblk - cb0);
-                uint32_t r[4][16];
-                tmem_ld_blocks(my_tmem + (uint32_t)cb0 * 16, nb, r);
-                #pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    if (j >= nb) break;
-                    const int cb = cb0 + j;
-                    float v[16];
-                    if (l > 0) {
-                        // through the hidden activation of layer l-1 (derivative from its stored output)
-                        uint8_t *hp = h_s + (size_t)(l - 1) * h_bytes;
-                        const uint4 a = *tile_word(hp, tid, 2 * cb);
-                        const uint4 b = *tile_word(hp, tid, 2 * cb + 1);
-                        const uint32_t hw[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-                        float y[16];
-                        #pragma unroll
-                        for (int k = 0; k < 8; ++k) {
-                            const float2 h2 = __half22float2(*reinterpret_cast<const __half2 *>(&hw[k]));
-                            y[2 * k] = h2.x; y[2 * k + 1] = h2.y;
-                            v[2 * k] = __uint_as_float(r[j][2 * k]); v[2 * k + 1] = __uint_as_float(r[j][2 * k + 1]);
-                        }
-                        act16_bwd_mul(cfg.hidden_act, v, y);
-                        store16(g_s, cb, v);
-                    } else if (grow < n) {
-                        #pragma unroll
-                        for (int k = 0; k < 16; ++k) v[k] = __uint_as_float(r[j][k]) * inv_scale;
-                        store_out16<TGX>(dX + grow * ldgx, v, cb * 16, cfg.in_dim, (io_vec & 2) != 0);
+            for_each_acc_block(my_tmem, cfg.K[l] / 16, [&](int cb, const uint32_t (&rr)[16]) {
+                float v[16];
+                if (l > 0) {
+                    // through the hidden activation of layer l-1 (derivative from its stored output)
+                    uint8_t *hp = h_s + (size_t)(l - 1) * h_bytes;
+                    const uint4 a = *tile_word(hp, tid, 2 * cb);
+                    const uint4 b = *tile_word(hp, tid, 2 * cb + 1);
+                    const uint32_t hw[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+                    float y[16];
+                    #pragma unroll
+                    for (int k = 0; k < 8; ++k) {
+                        const float2 h2 = __half22float2(*reinterpret_cast<const __half2 *>(&hw[k]));
+                        y[2 * k] = h2.x; y[2 * k + 1] = h2.y;
+                        v[2 * k] = __uint_as_float(rr[2 * k]); v[2 * k + 1] = __uint_as_float(rr[2 * k + 1]);
                     }
+                    act16_bwd_mul(cfg.hidden_act, v, y);
+                    store16(g_s, cb, v);
+                } else if (grow < n) {
+                    #pragma unroll
+                    for (int k = 0; k < 16; ++k) v[k] = __uint_as_float(rr[k]) * inv_scale;
+                    store_out16<TGX>(dX + grow * ldgx, v, cb * 16, cfg.in_dim, (io_vec & 2) != 0);
                 }
-            }
+            });
         }
         first_tile = false;
     }
@@ -631,17 +618,20 @@ int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob,
         const int esz = y_is_half ? 2 : 4;
         if ((ldy * esz) % 16 == 0 && ((uintptr_t)Y & 15u) == 0) io_vec |= 2;
     }
-    constexpr uint32_t COLS = 128;
-    const unsigned grid = mlp_grid(n, smem, COLS);
-#define LAUNCH_FWD(TI, TO)                                                                                  \
+    // accumulator columns: the widest layer output; 64 columns let eight CTAs share an SM's tensor memory
+    const bool narrow = c.width <= 64 && c.out_pad <= 64;
+#define LAUNCH_FWD2(TI, TO, COLS)                                                                           \
     do {                                                                                                    \
         int rc = set_smem(mlp_fwd_kernel<TI, TO, COLS>, smem);                                              \
         if (rc != ARCB200_OK) return rc;                                                                    \
+        const unsigned grid = mlp_grid(n, smem, COLS);                                                      \
         mlp_fwd_kernel<TI, TO, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, (TO *)Y, ldy, io_vec); \
     } while (0)
+#define LAUNCH_FWD(TI, TO) do { if (narrow) LAUNCH_FWD2(TI, TO, 64); else LAUNCH_FWD2(TI, TO, 128); } while (0)
     if (x_is_half) { if (y_is_half) LAUNCH_FWD(__half, __half); else LAUNCH_FWD(__half, float); }
     else { if (y_is_half) LAUNCH_FWD(float, __half); else LAUNCH_FWD(float, float); }
 #undef LAUNCH_FWD
+#undef LAUNCH_FWD2
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }

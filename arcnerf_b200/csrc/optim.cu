@@ -13,6 +13,11 @@ struct AdamHyper {
     float grad_scale;          // multiplies the incoming gradient (e.g. 1/world_size after an all-reduce sum)
 };
 
+__device__ __forceinline__ void bias_from_step(AdamHyper &h, int step) {
+    h.bias1 = (float)(1.0 - pow((double)h.beta1, (double)step));
+    h.bias2_sqrt = (float)sqrt(1.0 - pow((double)h.beta2, (double)step));
+}
+
 __device__ __forceinline__ void adam_one(float &p, float &m, float &v, float g, const AdamHyper &h) {
     g = g * h.grad_scale + h.weight_decay * p;
     m = h.beta1 * m + (1.0f - h.beta1) * g;
@@ -22,7 +27,9 @@ __device__ __forceinline__ void adam_one(float &p, float &m, float &v, float g, 
 }
 
 __global__ void adam_kernel(size_t n, float *__restrict__ p, float *__restrict__ m, float *__restrict__ v,
-                            float *__restrict__ g, __half *__restrict__ p_half, AdamHyper h, int zero_grad) {
+                            float *__restrict__ g, __half *__restrict__ p_half, AdamHyper h, int zero_grad,
+                            const int32_t *__restrict__ step_dev) {
+    if (step_dev) bias_from_step(h, max(*step_dev, 1));    // step count kept on the device (replayable launches)
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     const size_t n4 = n / 4;
     for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n4; k += stride) {
@@ -50,6 +57,8 @@ __global__ void adam_kernel(size_t n, float *__restrict__ p, float *__restrict__
         if (p_half) p_half[k] = __float2half_rn(pp);
     }
 }
+
+__global__ void counter_add_kernel(int32_t *c, int32_t v) { if (threadIdx.x == 0 && blockIdx.x == 0) *c += v; }
 
 // loss_sum[0] += weight/(3R) * sum huber(rgb - target);  g_rgb = d loss / d rgb
 __global__ void huber_kernel(uint32_t n_elem, const float *__restrict__ rgb, const float *__restrict__ target,
@@ -83,14 +92,17 @@ extern "C" {
 // One Adam step over a flat fp32 parameter vector (torch.optim.Adam arithmetic: L2 weight decay added to the
 // gradient, bias correction by step count `step` >= 1).  p_half (optional): fp16 copy of the updated
 // parameters, written in the same pass.  zero_grad != 0 clears g after use.  All buffers 16-byte aligned.
+// step_dev (device int32, optional) overrides `step`: the bias corrections are then derived on the device, so the
+// launch can be replayed (CUDA graph) while a counter kernel advances the step.
 // The reference runs torch.optim.Adam (common/trainer/optimizer.py) and re-casts fp32->fp16 at every forward
 // (tinycudann/modules.py:156).
 int arcb200_adam_step(float *p, float *m, float *v, float *g, void *p_half, int64_t n, int step, float lr,
                       float beta1, float beta2, float eps, float weight_decay, float grad_scale, int zero_grad,
-                      void *stream) {
+                      const int32_t *step_dev, void *stream) {
     ARC_REQUIRE(n >= 0, "adam_step: negative n");
     if (n == 0) return ARCB200_OK;
-    ARC_REQUIRE(p && m && v && g && step >= 1, "adam_step: null pointer or step < 1");
+    ARC_REQUIRE(p && m && v && g && (step >= 1 || step_dev), "adam_step: null pointer or step < 1");
+    if (step < 1) step = 1;
     ARC_REQUIRE((((uintptr_t)p | (uintptr_t)m | (uintptr_t)v | (uintptr_t)g) & 15u) == 0 && ((uintptr_t)p_half & 7u) == 0,
                 "adam_step: misaligned buffer");
     AdamHyper h;
@@ -102,7 +114,15 @@ int arcb200_adam_step(float *p, float *m, float *v, float *g, void *p_half, int6
     const long long cap = (long long)arc_sm_count() * 16;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    adam_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((size_t)n, p, m, v, g, (__half *)p_half, h, zero_grad);
+    adam_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((size_t)n, p, m, v, g, (__half *)p_half, h, zero_grad, step_dev);
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// counter[0] += value on the stream (device-resident step counter for replayed launch sequences)
+int arcb200_counter_add(int32_t *counter, int value, void *stream) {
+    ARC_REQUIRE(counter != nullptr, "counter_add: null pointer");
+    counter_add_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(counter, value);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }

@@ -271,10 +271,11 @@ def sample_cdf_gather(bins, cdf, u, eps=1e-5):
 
 # ---------------------------------------------------------------------------------------------- step helpers
 def adam_step(p, m, v, g, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0, p_half=None, grad_scale=1.0,
-              zero_grad=True):
+              zero_grad=True, step_dev=None):
+    """step_dev: device int32 tensor holding the step count (takes precedence over `step`; replayable launches)"""
     _lib.call('arcb200_adam_step', p.data_ptr(), m.data_ptr(), v.data_ptr(), g.data_ptr(), _lib.ptr(p_half), p.numel(),
               int(step), float(lr), float(beta1), float(beta2), float(eps), float(weight_decay), float(grad_scale),
-              int(bool(zero_grad)), _stream())
+              int(bool(zero_grad)), _lib.ptr(step_dev), _stream())
 
 
 def huber_loss(rgb, target, delta=0.1, weight=3000.0, loss_sum=None, want_grad=True):

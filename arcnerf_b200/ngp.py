@@ -82,6 +82,24 @@ class StageTimer:
         return {k: (sum(a.elapsed_time(b) for a, b in v) / len(v), len(v)) for k, v in self.records.items()}
 
 
+class SampleSet:
+    """Everything the sampler produces for one ray batch (packed layout).  The pipeline owns two of them
+    so that the march of the next batch can run on a side stream while the current batch is in the field kernels."""
+
+    def __init__(self, max_rays, capacity, n_sample, dev):
+        f32, i32 = torch.float32, torch.int32
+        e = lambda shape, dt: torch.empty(shape, dtype=dt, device=dev)
+        R, C = max_rays, capacity
+        self.near, self.far, self.hit = e((R, 1), f32), e((R, 1), f32), e((R, 1), torch.uint8)
+        self.counts, self.offsets = e((R,), i32), e((R + 1,), i32)
+        self.meta = torch.zeros(2, dtype=i32, device=dev)
+        self.scratch = e((_lib.load().arcb200_march_packed_scratch_bytes(R, n_sample),), torch.uint8)
+        self.t, self.unit, self.ray_id = e((C,), f32), e((C, 3), f32), e((C,), i32)
+        self.n_dev, self.pmax = self.meta[0:1], self.meta[1:2]
+        self.ready = None        # event recorded after the sampler kernels (side stream) or None
+        self.key = None          # (rays_o.data_ptr(), rays_d.data_ptr(), n_rays) the set was filled for
+
+
 class NGPPipeline:
     def __init__(self, max_rays=4096, capacity=1 << 19, device='cuda:0', seed=1337, grid_scale=1e-4, params=None,
                  world_size=1, **overrides):
@@ -116,6 +134,7 @@ class NGPPipeline:
         self.g_geo, self.m_geo, self.v_geo = z(self.geo_p), z(self.geo_p), z(self.geo_p)
         self.g_rad, self.m_rad, self.v_rad = z(self.rad_p), z(self.rad_p), z(self.rad_p)
         self.step_count = 0
+        self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)     # same count, device resident (graph replays)
         # occupancy + box
         n = cfg['n_grid']
         half = cfg['side'] / 2.0
@@ -134,11 +153,9 @@ class NGPPipeline:
         dev, R, C = self.dev, self.max_rays, self.capacity
         f32, i32, f16 = torch.float32, torch.int32, torch.float16
         e = lambda shape, dt: torch.empty(shape, dtype=dt, device=dev)
-        self.near, self.far, self.hit = e((R, 1), f32), e((R, 1), f32), e((R, 1), torch.uint8)
-        self.counts, self.offsets, self.meta = e((R,), i32), e((R + 1,), i32), torch.zeros(2, dtype=i32, device=dev)
-        nbytes = _lib.load().arcb200_march_packed_scratch_bytes(R, self.cfg['n_sample'])
-        self.scratch = e((nbytes,), torch.uint8)
-        self.t, self.unit, self.ray_id = e((C,), f32), e((C, 3), f32), e((C,), i32)
+        self.sets = [SampleSet(R, C, self.cfg['n_sample'], dev), SampleSet(R, C, self.cfg['n_sample'], dev)]
+        self.cur = 0
+        self.side_stream = torch.cuda.Stream(device=dev)
         self.enc = e((C, self.enc_dim), f16)
         self.rad_in = torch.zeros((C, self.rad_in_dim), dtype=f16, device=dev)
         self.sigma, self.rgb_s = e((C,), f32), e((C, 3), f32)
@@ -149,8 +166,19 @@ class NGPPipeline:
         self.d_geo_out = e((C, self.cfg['w_feat']), f32)
         self.d_enc = e((C, self.enc_dim), f32)
         self.loss = torch.zeros(1, dtype=f32, device=dev)
-        self.n_dev = self.meta[0:1]
-        self.pmax = self.meta[1:2]
+
+    # the sampler outputs of the batch currently in the field kernels
+    near = property(lambda self: self.sets[self.cur].near)
+    far = property(lambda self: self.sets[self.cur].far)
+    hit = property(lambda self: self.sets[self.cur].hit)
+    counts = property(lambda self: self.sets[self.cur].counts)
+    offsets = property(lambda self: self.sets[self.cur].offsets)
+    meta = property(lambda self: self.sets[self.cur].meta)
+    t = property(lambda self: self.sets[self.cur].t)
+    unit = property(lambda self: self.sets[self.cur].unit)
+    ray_id = property(lambda self: self.sets[self.cur].ray_id)
+    n_dev = property(lambda self: self.sets[self.cur].n_dev)
+    pmax = property(lambda self: self.sets[self.cur].pmax)
 
     def set_occupancy(self, volume_bool):
         """(n,n,n) bool occupancy (numpy or tensor), the VolumeBound bitfield."""
@@ -159,22 +187,51 @@ class NGPPipeline:
         self.volume.copy_(v)
 
     # ------------------------------------------------------------------------------------------ stages
-    def sample(self, rays_o, rays_d):
-        """slab test + packed occupancy march; everything stays on the device"""
+    def _sample_into(self, ss, rays_o, rays_d):
+        """slab test + packed occupancy march into sample set `ss` on the current stream; stays on the device"""
         cfg = self.cfg
         R = rays_o.shape[0]
         assert R <= self.max_rays
         st = _lib.current_stream()
         self._run('aabb', lambda: _lib.call(
             'arcb200_aabb_intersection', rays_o.data_ptr(), rays_d.data_ptr(), self.aabb.data_ptr(),
-            self.near.data_ptr(), self.far.data_ptr(), None, self.hit.data_ptr(), R, 1, st))
+            ss.near.data_ptr(), ss.far.data_ptr(), None, ss.hit.data_ptr(), R, 1, st))
         self._run('march_packed', lambda: _lib.call(
-            'arcb200_march_packed', 0, rays_o.data_ptr(), rays_d.data_ptr(), self.near.data_ptr(),
-            self.far.data_ptr(), cfg['n_sample'], self.dt, self.aabb.data_ptr(), cfg['n_grid'],
+            'arcb200_march_packed', 0, rays_o.data_ptr(), rays_d.data_ptr(), ss.near.data_ptr(),
+            ss.far.data_ptr(), cfg['n_sample'], self.dt, self.aabb.data_ptr(), cfg['n_grid'],
             self.volume.data_ptr(), cfg['near_distance'], R, self.rng.state, self.rng.inc,
-            self.scratch.data_ptr(), self.counts.data_ptr(), self.offsets.data_ptr(), self.meta.data_ptr(),
-            self.capacity, self.t.data_ptr(), None, self.ray_id.data_ptr(), self.unit.data_ptr(), st))
+            ss.scratch.data_ptr(), ss.counts.data_ptr(), ss.offsets.data_ptr(), ss.meta.data_ptr(),
+            self.capacity, ss.t.data_ptr(), None, ss.ray_id.data_ptr(), ss.unit.data_ptr(), st))
         self.rng.advance()
+        ss.key = (rays_o.data_ptr(), rays_d.data_ptr(), R)
+
+    def sample(self, rays_o, rays_d):
+        """Make the samples of this ray batch current: take the set a prefetch() filled for exactly these tensors (the
+        main stream then only waits for its event), otherwise march now on the main stream."""
+        key = (rays_o.data_ptr(), rays_d.data_ptr(), rays_o.shape[0])
+        other = self.sets[1 - self.cur]
+        if other.ready is not None and other.key == key:
+            torch.cuda.current_stream().wait_event(other.ready)
+            other.ready = None
+        else:
+            if other.ready is not None:                 # a prefetch for other rays is still writing this set
+                torch.cuda.current_stream().wait_event(other.ready)
+                other.ready = None
+            self._sample_into(other, rays_o, rays_d)
+        self.cur = 1 - self.cur
+
+    def prefetch(self, rays_o, rays_d):
+        """Sample the NEXT ray batch on the side stream while the current one is in the field kernels.  The set being
+        overwritten was last read by the step before the current one; an event on the main stream orders that.
+        The caller keeps rays_o / rays_d alive and unchanged until the batch has been consumed."""
+        nxt = self.sets[1 - self.cur]
+        gate = torch.cuda.Event()
+        gate.record()                                  # everything enqueued so far on the main stream
+        with torch.cuda.stream(self.side_stream):
+            self.side_stream.wait_event(gate)
+            self._sample_into(nxt, rays_o, rays_d)
+            nxt.ready = torch.cuda.Event()
+            nxt.ready.record()
 
     def field_forward(self, rays_d):
         """encode -> geometry head -> density | [feat, SH] -> radiance head, on the packed samples"""
@@ -197,10 +254,13 @@ class NGPPipeline:
             bkg_per_ray, self.rgb.data_ptr(), self.depth.data_ptr(), self.acc.data_ptr(), None, None, None, R,
             _lib.current_stream()))
 
-    def forward(self, rays_o, rays_d, bkg=None):
-        """-> rgb (R,3), depth (R,), mask (R,) views of the pipeline's output buffers"""
+    def forward(self, rays_o, rays_d, bkg=None, next_rays=None):
+        """-> rgb (R,3), depth (R,), mask (R,) views of the pipeline's output buffers.
+        next_rays = (rays_o, rays_d) of the batch that follows: its march is started on the side stream."""
         R = rays_o.shape[0]
         self.sample(rays_o, rays_d)
+        if next_rays is not None:
+            self.prefetch(*next_rays)
         self.field_forward(rays_d)
         self.composite(R, bkg)
         return self.rgb[:R], self.depth[:R], self.acc[:R]
@@ -227,7 +287,9 @@ class NGPPipeline:
         cfg = self.cfg
         self.step_count += 1
         gs = 1.0 / self.world_size
-        kw = dict(beta1=cfg['beta1'], beta2=cfg['beta2'], eps=cfg['eps'], weight_decay=cfg['weight_decay'], grad_scale=gs)
+        _lib.call('arcb200_counter_add', self.step_dev.data_ptr(), 1, _lib.current_stream())
+        kw = dict(beta1=cfg['beta1'], beta2=cfg['beta2'], eps=cfg['eps'], weight_decay=cfg['weight_decay'], grad_scale=gs,
+                  step_dev=self.step_dev)
         self._run('adam_table', lambda: F.adam_step(self.table, self.m_table, self.v_table, self.g_table, self.step_count,
                                                     cfg['lr'], p_half=self.table_h, **kw))
 
@@ -245,10 +307,12 @@ class NGPPipeline:
             from .dist import all_reduce_sum_
             all_reduce_sum_([self.g_table, self.g_geo, self.g_rad])
 
-    def train_step(self, rays_o, rays_d, target, bkg=None, optimize=True):
-        """One optimisation step on a ray batch; returns the (device) loss tensor.  No host synchronisation."""
+    def train_step(self, rays_o, rays_d, target, bkg=None, optimize=True, next_rays=None):
+        """One optimisation step on a ray batch; returns the (device) loss tensor.  No host synchronisation.
+        next_rays = (rays_o, rays_d) of the following batch, if known: it is sampled on the side stream meanwhile
+        (the sampler does not depend on the parameters being updated)."""
         R = rays_o.shape[0]
-        self.forward(rays_o, rays_d, bkg)
+        self.forward(rays_o, rays_d, bkg, next_rays=next_rays)
         self.loss.zero_()
         self._run('huber_loss', lambda: _lib.call(
             'arcb200_huber_loss', self.rgb.data_ptr(), target.data_ptr(), self.cfg['huber_delta'],
@@ -257,6 +321,99 @@ class NGPPipeline:
         if optimize:
             self._run('all_reduce', self.all_reduce_grads)
             self.optimizer_step()
+        return self.loss
+
+    # ------------------------------------------------------------------------------------------ replayed step
+    def _step_body(self, R, rays_d, target, bkg):
+        """everything of a training step after the sampler, on the current sample set and the current stream"""
+        self.field_forward(rays_d)
+        self.composite(R, bkg)
+        self.loss.zero_()
+        self._run('huber_loss', lambda: _lib.call(
+            'arcb200_huber_loss', self.rgb.data_ptr(), target.data_ptr(), self.cfg['huber_delta'],
+            self.cfg['loss_weight'], self.g_rgb.data_ptr(), self.loss.data_ptr(), R, _lib.current_stream()))
+        self.backward(rays_d, R, bkg)
+        self.optimizer_step()
+
+    def enable_graphs(self, n_rays):
+        """Static input slots + one CUDA graph per sample-set parity for the post-sampler part of a step (20 launches
+        replayed as one).  The sampler itself stays a normal launch on the side stream: its jitter generator state is
+        a by-value argument that changes every call.  Single-GPU only (the gradient exchange is not captured)."""
+        assert self.world_size == 1, 'graph replay is implemented for the single-GPU step'
+        dev, f32 = self.dev, torch.float32
+        self.static_in = [tuple(torch.empty((n_rays, 3), dtype=f32, device=dev) for _ in range(4)) for _ in range(2)]
+        self.graph_rays = n_rays
+        self.graphs = [None, None]
+        rng_state = (self.rng.state, self.rng.inc)       # the warm-up marches must not consume the jitter stream
+        # warm up outside capture (lazy module loading, function attributes), on both parities
+        for _ in range(2):
+            for x in self.static_in[1 - self.cur]:
+                x.zero_()
+            o, d, t, b = self.static_in[1 - self.cur]
+            d[:, 2] = 1.0
+            self.train_step(o, d, t, b, optimize=False)
+        torch.cuda.synchronize()
+        self.g_table.zero_(); self.g_geo.zero_(); self.g_rad.zero_()
+        count0, step0 = self.step_count, self.step_dev.clone()
+        keep = (self.table.clone(), self.geo_p.clone(), self.rad_p.clone(), self.m_table.clone(), self.v_table.clone(),
+                self.m_geo.clone(), self.v_geo.clone(), self.m_rad.clone(), self.v_rad.clone())
+        saved_cur = self.cur
+        for p in range(2):
+            self.cur = p
+            o, d, t, b = self.static_in[p]
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                self._step_body(n_rays, d, t, b)
+            self.graphs[p] = g
+        self.cur = saved_cur
+        # capture does not execute, but restore the optimiser state anyway in case of eager fall-backs above
+        for dst, src in zip((self.table, self.geo_p, self.rad_p, self.m_table, self.v_table, self.m_geo, self.v_geo,
+                             self.m_rad, self.v_rad), keep):
+            dst.copy_(src)
+        self.step_count = count0
+        self.step_dev.copy_(step0)
+        self.rng.state, self.rng.inc = rng_state
+        for ss in self.sets:
+            ss.ready, ss.key = None, None
+        self.table_h.copy_(self.table.half())
+        F.mlp_pack(self.geo_p, self.geo_spec, self.geo_blob)
+        F.mlp_pack(self.rad_p, self.rad_spec, self.rad_blob)
+        torch.cuda.synchronize()
+
+    def _upload_and_sample(self, slot, batch):
+        """batch (rays_o, rays_d, target, bkg) host-pinned or device tensors -> static slot, then march (current stream)"""
+        for dst, src in zip(self.static_in[slot], batch):
+            dst.copy_(src, non_blocking=True)
+        ss = self.sets[slot]
+        self._sample_into(ss, self.static_in[slot][0], self.static_in[slot][1])
+
+    def train_step_graphed(self, batch, next_batch=None):
+        """One optimisation step from a (host or device) batch through the static slots and the captured graph.
+        next_batch, if given, is uploaded and sampled on the side stream while this step runs.  Returns the device
+        loss tensor."""
+        p = 1 - self.cur
+        ss = self.sets[p]
+        main = torch.cuda.current_stream()
+        if ss.ready is not None and ss.key == ('slot', p, id(batch[0])):
+            main.wait_event(ss.ready)
+        else:
+            if ss.ready is not None:
+                main.wait_event(ss.ready)
+            self._upload_and_sample(p, batch)
+        ss.ready = None
+        self.cur = p
+        if next_batch is not None:
+            q = 1 - p
+            gate = torch.cuda.Event()
+            gate.record()
+            with torch.cuda.stream(self.side_stream):
+                self.side_stream.wait_event(gate)
+                self._upload_and_sample(q, next_batch)
+                self.sets[q].key = ('slot', q, id(next_batch[0]))
+                self.sets[q].ready = torch.cuda.Event()
+                self.sets[q].ready.record()
+        self.step_count += 1
+        self.graphs[p].replay()
         return self.loss
 
     @torch.no_grad()
@@ -271,10 +428,11 @@ class NGPPipeline:
         for s in range(0, N, chunk):
             e = min(N, s + chunk)
             b = None if bkg is None else (bkg if bkg.shape[0] == 1 else bkg[s:e])
-            r, d, a = self.forward(rays_o[s:e], rays_d[s:e], b)
+            nxt = (rays_o[e:min(N, e + chunk)], rays_d[e:min(N, e + chunk)]) if e < N else None
+            r, d, a = self.forward(rays_o[s:e], rays_d[s:e], b, next_rays=nxt)
             rgb[s:e].copy_(r); depth[s:e].copy_(d); acc[s:e].copy_(a)
         return rgb, depth, acc
 
     # number of library kernels one train_step enqueues (for bench.py's gpu_launches)
     LAUNCHES_FORWARD = 1 + 4 + 1 + 1 + 1 + 1 + 1 + 1      # aabb, march(4), grid, geo mlp, sh, exp, rad mlp, composite
-    LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1 + 1 + 3 + 2   # huber, comp bwd, rad bwd, glue, geo bwd, grid bwd, adam x3, pack x2
+    LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1 + 1 + 1 + 3 + 2   # huber, comp bwd, rad bwd, glue, geo bwd, grid bwd, step counter, adam x3, pack x2

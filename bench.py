@@ -235,7 +235,8 @@ def main():
     e0.record()
     for i in range(K):
         o, d, t, b = resident[W + i]
-        pipe.train_step(o, d, t, b)
+        nxt = resident[W + i + 1][:2] if i + 1 < K else None      # the trainer knows its next batch: sample it meanwhile
+        pipe.train_step(o, d, t, b, next_rays=nxt)
     e1.record()
     barrier()
     ms_total = max_over_ranks(e0.elapsed_time(e1))
@@ -243,18 +244,39 @@ def main():
     value = N_RAYS * world * K / (ms_total * 1e-3)
 
     # ---- timed: end to end from host buffers (H2D rays + targets, D2H loss, every step)
-    dbuf = [torch.empty_like(x, device=dev) for x in host[0]]
     loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
-    barrier()
-    e0.record()
-    for i in range(K):
-        for dst, src in zip(dbuf, host[W + i]):
+    if world == 1:
+        # single GPU: static input slots + CUDA-graph replay of the post-sampler part of the step
+        pipe.enable_graphs(N_RAYS)
+        for i in range(3):
+            pipe.train_step_graphed(host[i], next_batch=host[i + 1])
+        barrier()
+        e0.record()
+        for i in range(K):
+            nb = host[W + i + 1] if i + 1 < K else None
+            loss = pipe.train_step_graphed(host[W + i], next_batch=nb)     # H2D of rays/targets inside
+            loss_host.copy_(loss, non_blocking=True)
+            torch.cuda.current_stream().synchronize()      # the caller reads the loss every step
+        e1.record()
+        barrier()
+        e2e_mode = 'host pinned buffers -> static device slots (H2D per step) -> sampler on side stream + CUDA graph replay -> loss D2H + sync per step'
+    else:
+        dbufs = [[torch.empty_like(x, device=dev) for x in host[0]] for _ in range(2)]   # current / next batch
+        barrier()
+        e0.record()
+        for dst, src in zip(dbufs[0], host[W]):
             dst.copy_(src, non_blocking=True)
-        loss = pipe.train_step(*dbuf)
-        loss_host.copy_(loss, non_blocking=True)
-        torch.cuda.current_stream().synchronize()      # the caller reads the loss every step
-    e1.record()
-    barrier()
+        for i in range(K):
+            cur, nxt = dbufs[i % 2], dbufs[(i + 1) % 2]
+            if i + 1 < K:                                   # upload the next batch, then let the sampler run ahead on it
+                for dst, src in zip(nxt, host[W + i + 1]):
+                    dst.copy_(src, non_blocking=True)
+            loss = pipe.train_step(*cur, next_rays=(nxt[0], nxt[1]) if i + 1 < K else None)
+            loss_host.copy_(loss, non_blocking=True)
+            torch.cuda.current_stream().synchronize()      # the caller reads the loss every step
+        e1.record()
+        barrier()
+        e2e_mode = 'host pinned buffers -> H2D per step -> eager launches (gradient all-reduce is not graph captured) -> loss D2H + sync per step'
     ms_e2e = max_over_ranks(e0.elapsed_time(e1))
     e2e_value = N_RAYS * world * K / (ms_e2e * 1e-3)
     h2d = sum(x.numel() * x.element_size() for x in host[0])
@@ -356,7 +378,7 @@ def main():
                         l2='per-step working set (fp32 table + Adam moments + gradients + fp16 copy, 0.27 GB) exceeds the '
                            '126 MB L2 and every step draws a different ray batch; the Adam sweep evicts L2 between steps',
                         parallelism='dp%d' % world),
-            e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=4, ms_per_step=ms_e2e / K),
+            e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=4, ms_per_step=ms_e2e / K, path=e2e_mode),
             gpu_launches=NGPPipeline.LAUNCHES_TRAIN * K,
             clocks=clock_info, roofline=roofline, cpu_baseline=cpu_baseline,
             render_ms_800x800=render_ms,

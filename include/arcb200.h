@@ -296,10 +296,13 @@ int arcb200_geo_head_grad(const void *x0, int x_is_half, int64_t ldx, const floa
 
 /* ---------------------------------------------------------------- training-step helpers ----------------
  * torch.optim.Adam arithmetic (common/trainer/optimizer.py -> torch) in one pass that also writes the fp16
- * working copy (p_half, optional) and clears the gradient (zero_grad).  step >= 1. */
+ * working copy (p_half, optional) and clears the gradient (zero_grad).  step >= 1.
+ * step_dev (device int32 or NULL) overrides `step` so that the launch can be replayed from a CUDA graph;
+ * arcb200_counter_add advances such a counter on the stream. */
 int arcb200_adam_step(float *p, float *m, float *v, float *g, void *p_half, int64_t n, int step, float lr,
                       float beta1, float beta2, float eps, float weight_decay, float grad_scale, int zero_grad,
-                      void *stream);
+                      const int32_t *step_dev, void *stream);
+int arcb200_counter_add(int32_t *counter, int value, void *stream);
 /* ImgLoss with HuberLoss (arcnerf/loss/img_loss.py:48-98): loss_sum[0] += weight * mean(huber), g_rgb = gradient. */
 int arcb200_huber_loss(const float *rgb, const float *target, float delta, float weight, float *g_rgb,
                        float *loss_sum, int64_t n_rays, void *stream);
