@@ -49,6 +49,9 @@ _SIGS = {
     'arcb200_mlp_blob_bytes': [I, I, I, I],
     'arcb200_mlp_pack_weights': [P, P, I, I, I, I, P],
     'arcb200_mlp_fwd': [P, I, L, P, I, I, I, I, I, I, P, I, L, L, P, P],
+    'arcb200_mlp_act_save_bytes': [L, I, I],
+    'arcb200_mlp_fwd_ex': [P, I, L, P, I, I, I, I, I, I, P, I, L, P, P, L, P, P],
+    'arcb200_mlp_bwd_ex': [P, I, L, P, I, I, I, I, I, I, P, L, F, P, I, L, P, P, P, I, L, P, P, I, L, F, L, P, P],
     'arcb200_mlp_bwd': [P, I, L, P, I, I, I, I, I, I, P, L, F, P, I, L, P, L, P, P],
     'arcb200_composite_fwd': [P, I, L, P, P, I, P, P, P, I, I, P, I, P, P, P, P, P, P, L, P],
     'arcb200_composite_bwd': [P, I, L, P, P, I, P, P, P, I, I, P, I, P, P, P, P, P, P, I, L, P],
@@ -69,6 +72,7 @@ _RESTYPE = {
     'arcb200_march_packed_scratch_bytes': L,
     'arcb200_march_packed_static_max_slots': L,
     'arcb200_grid_geometry': L,
+    'arcb200_mlp_act_save_bytes': L,
 }
 
 _lib = None

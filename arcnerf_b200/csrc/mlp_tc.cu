@@ -220,16 +220,37 @@ __device__ __forceinline__ void issue_wgrad_mm(uint32_t tmem_d, uint32_t p_tile,
 struct Shared {
     uint64_t mbar_w;
     uint64_t mbar_mma;
+    uint64_t mbar_h;      // saved hidden activations of the current tile have landed (backward, bulk copies)
     uint32_t tmem_base;
     uint32_t pad;
 };
 
+// Optional extras of the forward: hidden activations saved for the backward (operand-tile layout, per 128-row tile)
+// and exp() of output channel 0 (the density head's TruncExp).
+struct FwdExtra {
+    uint8_t *act_save;
+    float *exp0_out;
+};
+// Optional extras of the backward: saved hidden activations / outputs instead of re-computation, and an extra
+// gradient on output channel 0 that arrives through exp(): g0[row] * exp(clamp(x0[row], +-clip)).
+struct BwdExtra {
+    const uint8_t *act_saved;
+    const void *y_saved;
+    int64_t ldys;
+    int y_is_half;
+    const float *g0;
+    const void *x0;
+    int64_t ldx0;
+    int x0_is_half;
+    float clip;
+};
+
 // ---------------------------------------------------------------------------------------------- forward
 template <typename TIN, typename TOUT, uint32_t TMEM_COLS>
-__global__ void __launch_bounds__(kRows, TMEM_COLS == 64 ? 7 : 4)
+__global__ void __launch_bounds__(kRows, TMEM_COLS == 64 ? 5 : 4)
 mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restrict__ X, int64_t ldx,
                const uint8_t *__restrict__ blob, const __grid_constant__ MlpCfg cfg, TOUT *__restrict__ Y, int64_t ldy,
-               int io_vec) {
+               int io_vec, FwdExtra ex) {
     extern __shared__ __align__(128) uint8_t smem[];
     if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     Shared *sh = reinterpret_cast<Shared *>(smem);
@@ -240,6 +261,7 @@ mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
     if (tid == 32) {
         tc05::mbar_init(&sh->mbar_w, 1);
         tc05::mbar_init(&sh->mbar_mma, 1);
+        tc05::mbar_init(&sh->mbar_h, 1);
         tc05::fence_mbar_init();
     }
     if (warp == 0) tc05::tmem_alloc<TMEM_COLS>(&sh->tmem_base);
@@ -286,8 +308,15 @@ mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
                     w1.z = tc05::pack_half2(v[12], v[13]); w1.w = tc05::pack_half2(v[14], v[15]);
                     *tile_word(a_s, tid, 2 * cb) = w0;
                     *tile_word(a_s, tid, 2 * cb + 1) = w1;
+                    if (ex.act_save) {   // same tile layout in global memory: consecutive threads, consecutive 16-byte words
+                        uint8_t *gt = ex.act_save + ((size_t)tile * (cfg.n_mm - 1) + l) * ((size_t)kRows * cfg.width * 2);
+                        *tile_word(gt, tid, 2 * cb) = w0;
+                        *tile_word(gt, tid, 2 * cb + 1) = w1;
+                    }
                 } else if (grow < n) {
                     store_out16<TOUT>(Y + grow * ldy, v, cb * 16, cfg.out_dim, (io_vec & 2) != 0);
+                    if (ex.exp0_out && cb == 0)
+                        ex.exp0_out[grow] = expf(sizeof(TOUT) == 2 ? __half2float(__float2half_rn(v[0])) : v[0]);
                 }
             });
         }
@@ -311,7 +340,7 @@ __global__ void __launch_bounds__(kRows)
 mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restrict__ X, int64_t ldx,
                const uint8_t *__restrict__ blob, const __grid_constant__ MlpCfg cfg, const __grid_constant__ BwdPlan plan,
                const float *__restrict__ dY, int64_t ldy, float loss_scale, TGX *__restrict__ dX, int64_t ldgx,
-               float *__restrict__ dW, int io_vec) {
+               float *__restrict__ dW, int io_vec, BwdExtra ex) {
     extern __shared__ __align__(128) uint8_t smem[];
     if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     Shared *sh = reinterpret_cast<Shared *>(smem);
@@ -325,6 +354,7 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
     if (tid == 32) {
         tc05::mbar_init(&sh->mbar_w, 1);
         tc05::mbar_init(&sh->mbar_mma, 1);
+        tc05::mbar_init(&sh->mbar_h, 1);
         tc05::fence_mbar_init();
     }
     if (warp == 0) tc05::tmem_alloc<TMEM_COLS>(&sh->tmem_base);
@@ -339,7 +369,7 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
     const uint32_t w_addr = tc05::smem_u32(w_s), x_addr = tc05::smem_u32(x_s), h_addr = tc05::smem_u32(h_s),
                    g_addr = tc05::smem_u32(g_s);
     const uint32_t my_tmem = tmem + ((uint32_t)(warp * 32) << 16);
-    uint32_t phase = 0;
+    uint32_t phase = 0, hphase = 0;
     bool weights_ready = false, first_tile = true;
     const float inv_scale = 1.0f / loss_scale;
 
@@ -372,6 +402,60 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
         load_input_tile<TIN>(x_s, X, ldx, tile * kRows, n, cfg.in_dim, cfg.in_pad, (io_vec & 1) != 0, tid);
         if (!weights_ready) { tc05::mbar_wait(&sh->mbar_w, 0); weights_ready = true; }
 
+        // gradient at the network output for 16 columns of this thread's row (+ the exp-channel extra on column 0)
+        auto load_dy16 = [&](int cb, float (&g)[16]) {
+            if ((io_vec & 4) && grow < n && cb * 16 + 16 <= cfg.out_dim) {
+                #pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const float4 q = __ldg(reinterpret_cast<const float4 *>(dY + grow * ldy + cb * 16) + k);
+                    g[4 * k] = q.x; g[4 * k + 1] = q.y; g[4 * k + 2] = q.z; g[4 * k + 3] = q.w;
+                }
+            } else {
+                #pragma unroll
+                for (int k = 0; k < 16; ++k) {
+                    const int c = cb * 16 + k;
+                    g[k] = (grow < n && c < cfg.out_dim) ? __ldg(dY + grow * ldy + c) : 0.0f;
+                }
+            }
+            if (ex.g0 && cb == 0 && grow < n) {
+                const float x0 = ex.x0_is_half ? __half2float(__ldg(reinterpret_cast<const __half *>(ex.x0) + grow * ex.ldx0))
+                                               : __ldg(reinterpret_cast<const float *>(ex.x0) + grow * ex.ldx0);
+                g[0] += __ldg(ex.g0 + grow) * expf(fminf(fmaxf(x0, -ex.clip), ex.clip));
+            }
+        };
+
+        if (ex.act_saved) {
+            // ---- saved activations: bulk copies (TMA engine) straight into the operand tiles, no re-computation
+            __syncthreads();                               // every reader of the previous tile's h_s / g_s is done
+            const uint32_t hb = (uint32_t)h_bytes * (uint32_t)(cfg.n_mm - 1);
+            if (tid == 0 && hb) {
+                tc05::mbar_expect_tx(&sh->mbar_h, hb);
+                for (int l = 0; l + 1 < cfg.n_mm; ++l)
+                    tc05::bulk_g2s(h_s + (size_t)l * h_bytes,
+                                   ex.act_saved + ((size_t)tile * (cfg.n_mm - 1) + l) * h_bytes, (uint32_t)h_bytes, &sh->mbar_h);
+            }
+            for (int cb = 0; cb < cfg.out_pad / 16; ++cb) {
+                float g[16], v[16];
+                load_dy16(cb, g);
+                #pragma unroll
+                for (int k = 0; k < 16; ++k) v[k] = g[k] * loss_scale;
+                if (cfg.out_act != ACT_NONE) {
+                    float y[16];
+                    #pragma unroll
+                    for (int k = 0; k < 16; ++k) {
+                        const int c = cb * 16 + k;
+                        y[k] = 0.f;
+                        if (grow < n && c < cfg.out_dim)
+                            y[k] = ex.y_is_half ? __half2float(__ldg(reinterpret_cast<const __half *>(ex.y_saved) + grow * ex.ldys + c))
+                                                : __ldg(reinterpret_cast<const float *>(ex.y_saved) + grow * ex.ldys + c);
+                    }
+                    act16_bwd_mul(cfg.out_act, v, y);
+                }
+                store16(g_s, cb, v);
+            }
+            if (hb) tc05::mbar_wait(&sh->mbar_h, hphase);
+            hphase ^= 1u;
+        } else {
         // ---- forward re-computation; hidden activations stay in shared memory
         for (int l = 0; l < cfg.n_mm; ++l) {
             const uint32_t a_tile = l == 0 ? x_addr : h_addr + (uint32_t)((l - 1) * h_bytes);
@@ -385,19 +469,7 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
                 } else {
                     // gradient w.r.t. the last pre-activation, scaled; padded outputs and rows carry none
                     float g[16], y[16];
-                    if ((io_vec & 4) && grow < n && cb * 16 + 16 <= cfg.out_dim) {
-                        #pragma unroll
-                        for (int k = 0; k < 4; ++k) {
-                            const float4 q = __ldg(reinterpret_cast<const float4 *>(dY + grow * ldy + cb * 16) + k);
-                            g[4 * k] = q.x; g[4 * k + 1] = q.y; g[4 * k + 2] = q.z; g[4 * k + 3] = q.w;
-                        }
-                    } else {
-                        #pragma unroll
-                        for (int k = 0; k < 16; ++k) {
-                            const int c = cb * 16 + k;
-                            g[k] = (grow < n && c < cfg.out_dim) ? __ldg(dY + grow * ldy + c) : 0.0f;
-                        }
-                    }
+                    load_dy16(cb, g);
                     act16_fwd(cfg.out_act, rr, y);
                     #pragma unroll
                     for (int k = 0; k < 16; ++k) v[k] = g[k] * loss_scale;
@@ -405,6 +477,7 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
                     store16(g_s, cb, v);
                 }
             });
+        }
         }
 
         // ---- backward chain
@@ -599,10 +672,35 @@ int arcb200_mlp_pack_weights(const float *params, void *blob, int in_dim, int wi
 // Forward.  X (n, in_dim) fp32 or fp16 (x_is_half), leading dimension ldx elements; Y (n, out_dim) fp32 or fp16,
 // leading dimension ldy.  Activation codes: 0 none, 1 ReLU, 2 sigmoid, 3 softplus (tcnn, beta 10), 4 exp.
 // Replaces tcnn Module.fwd for a FullyFusedMLP network (bindings.cpp:78-109 -> fully_fused_mlp.cu:499-700).
+// Bytes of the activation-save buffer of arcb200_mlp_fwd_ex for n rows (hidden activations of every 128-row tile).
+int64_t arcb200_mlp_act_save_bytes(int64_t n, int width, int n_hidden) {
+    if (n < 0 || width < 16 || n_hidden < 1) return ARCB200_ERR_ARG;
+    const int64_t tiles = (n + kRows - 1) / kRows;
+    return tiles * n_hidden * (int64_t)kRows * width * 2;
+}
+
+int arcb200_mlp_fwd_ex(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                       int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, void *act_save,
+                       float *exp0_out, int64_t n, const int32_t *n_dev, void *stream);
+
 int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
                     int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, int64_t n,
                     const int32_t *n_dev, void *stream) {
+    return arcb200_mlp_fwd_ex(X, x_is_half, ldx, blob, in_dim, width, n_hidden, out_dim, hidden_act, out_act, Y, y_is_half,
+                              ldy, nullptr, nullptr, n, n_dev, stream);
+}
+
+// As arcb200_mlp_fwd, plus: act_save (optional, arcb200_mlp_act_save_bytes(n,...) bytes, 16-byte aligned) receives the
+// hidden activations for arcb200_mlp_bwd_ex; exp0_out (optional, n floats) receives exp(output channel 0), taken from
+// the value as stored in Y (the density head's TruncExp forward, arcnerf/ops/trunc_exp.py:10-24).
+int arcb200_mlp_fwd_ex(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                       int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, void *act_save,
+                       float *exp0_out, int64_t n, const int32_t *n_dev, void *stream) {
     ARC_REQUIRE(n >= 0, "mlp_fwd: negative n");
+    ARC_REQUIRE(((uintptr_t)act_save & 15u) == 0, "mlp_fwd: act_save must be 16-byte aligned");
+    FwdExtra fex;
+    fex.act_save = (uint8_t *)act_save;
+    fex.exp0_out = exp0_out;
     if (n == 0) return ARCB200_OK;
     MlpCfg c;
     ARC_REQUIRE(make_cfg(c, in_dim, width, n_hidden, out_dim, hidden_act, out_act) >= 0, "mlp_fwd: unsupported shape");
@@ -625,7 +723,7 @@ int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob,
         int rc = set_smem(mlp_fwd_kernel<TI, TO, COLS>, smem);                                              \
         if (rc != ARCB200_OK) return rc;                                                                    \
         const unsigned grid = mlp_grid(n, smem, COLS);                                                      \
-        mlp_fwd_kernel<TI, TO, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, (TO *)Y, ldy, io_vec); \
+        mlp_fwd_kernel<TI, TO, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, (TO *)Y, ldy, io_vec, fex); \
     } while (0)
 #define LAUNCH_FWD(TI, TO) do { if (narrow) LAUNCH_FWD2(TI, TO, 64); else LAUNCH_FWD2(TI, TO, 128); } while (0)
     if (x_is_half) { if (y_is_half) LAUNCH_FWD(__half, __half); else LAUNCH_FWD(__half, float); }
@@ -641,10 +739,38 @@ int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob,
 // loss_scale (128 in the reference, tinycudann/modules.py:141) and are unscaled on the way out.
 // width must be 64 or 128.  Replaces tcnn Module.bwd for a FullyFusedMLP (bindings.cpp:111-170 ->
 // fully_fused_mlp.cu:702-857).
+int arcb200_mlp_bwd_ex(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                       int out_dim, int hidden_act, int out_act, const float *dY, int64_t ldy, float loss_scale,
+                       void *dX, int dx_is_half, int64_t ldgx, float *dW, const void *act_saved, const void *y_saved,
+                       int ys_is_half, int64_t ldys, const float *g0, const void *x0, int x0_is_half, int64_t ldx0,
+                       float clip, int64_t n, const int32_t *n_dev, void *stream);
+
 int arcb200_mlp_bwd(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
                     int out_dim, int hidden_act, int out_act, const float *dY, int64_t ldy, float loss_scale,
                     void *dX, int dx_is_half, int64_t ldgx, float *dW, int64_t n, const int32_t *n_dev, void *stream) {
+    return arcb200_mlp_bwd_ex(X, x_is_half, ldx, blob, in_dim, width, n_hidden, out_dim, hidden_act, out_act, dY, ldy,
+                              loss_scale, dX, dx_is_half, ldgx, dW, nullptr, nullptr, 0, 0, nullptr, nullptr, 0, 0, 0.f, n,
+                              n_dev, stream);
+}
+
+// As arcb200_mlp_bwd, plus:
+//   act_saved : hidden activations written by arcb200_mlp_fwd_ex for the same X / weights / n (skips the forward
+//               re-computation); then y_saved (n,out_dim; fp16 or fp32, leading dimension ldys) must hold the network
+//               outputs whenever the output activation is not "none";
+//   g0, x0    : extra gradient on output channel 0 arriving through exp(): dY[:,0] += g0[row]*exp(clamp(x0[row*ldx0],
+//               +-clip)) - the density head (TruncExp backward, arcnerf/ops/trunc_exp.py:26-37) without a separate pass.
+int arcb200_mlp_bwd_ex(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                       int out_dim, int hidden_act, int out_act, const float *dY, int64_t ldy, float loss_scale,
+                       void *dX, int dx_is_half, int64_t ldgx, float *dW, const void *act_saved, const void *y_saved,
+                       int ys_is_half, int64_t ldys, const float *g0, const void *x0, int x0_is_half, int64_t ldx0,
+                       float clip, int64_t n, const int32_t *n_dev, void *stream) {
     ARC_REQUIRE(n >= 0, "mlp_bwd: negative n");
+    ARC_REQUIRE(!act_saved || out_act == 0 || y_saved, "mlp_bwd: saved activations need the saved outputs when the output activation is not none");
+    ARC_REQUIRE(((uintptr_t)act_saved & 15u) == 0, "mlp_bwd: act_saved must be 16-byte aligned");
+    ARC_REQUIRE(!g0 || x0, "mlp_bwd: g0 given without x0");
+    BwdExtra bex;
+    bex.act_saved = (const uint8_t *)act_saved; bex.y_saved = y_saved; bex.ldys = ldys; bex.y_is_half = ys_is_half;
+    bex.g0 = g0; bex.x0 = x0; bex.ldx0 = ldx0; bex.x0_is_half = x0_is_half; bex.clip = clip;
     if (n == 0) return ARCB200_OK;
     MlpCfg c;
     ARC_REQUIRE(make_cfg(c, in_dim, width, n_hidden, out_dim, hidden_act, out_act) >= 0, "mlp_bwd: unsupported shape");
@@ -668,7 +794,7 @@ int arcb200_mlp_bwd(const void *X, int x_is_half, int64_t ldx, const void *blob,
         if (rc != ARCB200_OK) return rc;                                                                    \
         const unsigned grid = mlp_grid(n, smem, COLS);                                                      \
         mlp_bwd_kernel<TI, TG, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, plan, dY, \
-                                                               ldy, loss_scale, (TG *)dX, ldgx, dW, io_vec); \
+                                                               ldy, loss_scale, (TG *)dX, ldgx, dW, io_vec, bex); \
     } while (0)
 #define LAUNCH_BWD_T(COLS)                                                                                  \
     do {                                                                                                    \

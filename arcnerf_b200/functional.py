@@ -162,33 +162,45 @@ def mlp_pack(params, spec, blob=None):
     return blob
 
 
-def mlp_forward(x, blob, spec, out_dtype=torch.float32, out=None, out_col=0, n_dev=None):
+def mlp_act_save_buffer(n, spec, device):
+    """scratch for the hidden activations of n rows (forward -> backward hand-over)"""
+    nbytes = _lib.load().arcb200_mlp_act_save_bytes(int(n), spec.width, spec.n_hidden)
+    return torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+
+
+def mlp_forward(x, blob, spec, out_dtype=torch.float32, out=None, out_col=0, n_dev=None, act_save=None, exp0_out=None):
     _cuda(x, 'x'), _cuda(blob, 'blob')
     if x.dtype not in (torch.float16, torch.float32) or x.dim() != 2 or x.shape[1] < spec.in_dim or x.stride(1) != 1:
         raise RuntimeError('x must be (N, >=%d) float16/float32 with unit column stride' % spec.in_dim)
     n = x.shape[0]
     if out is None:
         out = torch.empty((n, spec.out_dim), dtype=out_dtype, device=x.device)
-    _lib.call('arcb200_mlp_fwd', x.data_ptr(), int(x.dtype == torch.float16), x.stride(0), blob.data_ptr(), *spec.dims(),
+    _lib.call('arcb200_mlp_fwd_ex', x.data_ptr(), int(x.dtype == torch.float16), x.stride(0), blob.data_ptr(), *spec.dims(),
               spec.hidden_act, spec.out_act, out.data_ptr() + out_col * out.element_size(),
-              int(out.dtype == torch.float16), out.stride(0), n, _lib.ptr(n_dev), _stream())
+              int(out.dtype == torch.float16), out.stride(0), _lib.ptr(act_save), _lib.ptr(exp0_out), n, _lib.ptr(n_dev),
+              _stream())
     return out
 
 
 def mlp_backward(x, blob, spec, dy, dW=None, want_dx=True, dx_dtype=torch.float32, loss_scale=128.0, n_dev=None,
-                 dx=None):
-    """-> (dX (N,in_dim) | None, dW flat fp32 accumulated)"""
+                 dx=None, act_saved=None, y_saved=None, g0=None, x0=None, clip=15.0):
+    """-> (dX (N,in_dim) | None, dW flat fp32 accumulated).  act_saved / y_saved: hand-over from mlp_forward(act_save=..)
+    (no forward re-computation); g0 (N,) with x0 (N-row strided view, fp16/fp32): extra gradient on output channel 0
+    through exp(clamp(x0))."""
     _cuda(x, 'x'), _cuda(blob, 'blob'), _cuda(dy, 'dy')
-    if dy.dtype != torch.float32 or dy.shape != (x.shape[0], spec.out_dim):
-        raise RuntimeError('dy must be (N, %d) float32' % spec.out_dim)
+    if dy.dtype != torch.float32 or dy.shape[0] != x.shape[0] or dy.shape[1] < spec.out_dim or dy.stride(1) != 1:
+        raise RuntimeError('dy must be (N, >=%d) float32 with unit column stride' % spec.out_dim)
     n = x.shape[0]
     if dW is None:
         dW = torch.zeros(spec.n_params, dtype=torch.float32, device=x.device)
     if dx is None and want_dx:
         dx = torch.empty((n, spec.in_dim), dtype=dx_dtype, device=x.device)
-    _lib.call('arcb200_mlp_bwd', x.data_ptr(), int(x.dtype == torch.float16), x.stride(0), blob.data_ptr(), *spec.dims(),
+    _lib.call('arcb200_mlp_bwd_ex', x.data_ptr(), int(x.dtype == torch.float16), x.stride(0), blob.data_ptr(), *spec.dims(),
               spec.hidden_act, spec.out_act, dy.data_ptr(), dy.stride(0), float(loss_scale), _lib.ptr(dx),
-              int(dx is not None and dx.dtype == torch.float16), dx.stride(0) if dx is not None else 0, dW.data_ptr(), n,
+              int(dx is not None and dx.dtype == torch.float16), dx.stride(0) if dx is not None else 0, dW.data_ptr(),
+              _lib.ptr(act_saved), _lib.ptr(y_saved), int(y_saved is not None and y_saved.dtype == torch.float16),
+              y_saved.stride(0) if y_saved is not None else 0, _lib.ptr(g0), _lib.ptr(x0),
+              int(x0 is not None and x0.dtype == torch.float16), x0.stride(0) if x0 is not None else 0, float(clip), n,
               _lib.ptr(n_dev), _stream())
     return dx, dW
 

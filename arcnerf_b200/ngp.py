@@ -163,7 +163,10 @@ class NGPPipeline:
         self.g_rgb = e((R, 3), f32)
         self.d_sigma, self.d_rgb_s = torch.zeros((C,), dtype=f32, device=dev), torch.zeros((C, 3), dtype=f32, device=dev)
         self.d_rad_in = e((C, self.rad_in_dim), f32)
-        self.d_geo_out = e((C, self.cfg['w_feat']), f32)
+        # hidden activations handed from the forward to the backward kernels (operand-tile layout)
+        self.geo_act = F.mlp_act_save_buffer(C, self.geo_spec, dev)
+        self.rad_act = F.mlp_act_save_buffer(C, self.rad_spec, dev)
+        self.training = True
         self.d_enc = e((C, self.enc_dim), f32)
         self.loss = torch.zeros(1, dtype=f32, device=dev)
 
@@ -238,13 +241,14 @@ class NGPPipeline:
         C, nd = self.capacity, self.n_dev
         self._run('grid_fwd', lambda: F.grid_forward(self.unit, self.table_h, self.geom, n_dev=nd, out=self.enc))
         # geometry head writes its W_feat outputs straight into the radiance input row; SH fills the rest
-        self._run('mlp_geo_fwd', lambda: F.mlp_forward(self.enc, self.geo_blob, self.geo_spec, out=self.rad_in, out_col=0, n_dev=nd))
+        # (the density sigma = TruncExp(channel 0) comes out of the same kernel's epilogue)
+        tr = self.training
+        self._run('mlp_geo_fwd', lambda: F.mlp_forward(self.enc, self.geo_blob, self.geo_spec, out=self.rad_in, out_col=0,
+                                                       n_dev=nd, act_save=self.geo_act if tr else None, exp0_out=self.sigma))
         self._run('sh_fwd', lambda: F.sh_forward(rays_d, self.cfg['sh_degree'], index=self.ray_id, remap=True, out=self.rad_in,
                                                  out_col=self.cfg['w_feat'], n_dev=nd))
-        self._run('trunc_exp_fwd', lambda: _lib.call(
-            'arcb200_trunc_exp_fwd', self.rad_in.data_ptr(), 1, self.rad_in.stride(0), self.sigma.data_ptr(), C,
-            nd.data_ptr(), _lib.current_stream()))
-        self._run('mlp_rad_fwd', lambda: F.mlp_forward(self.rad_in, self.rad_blob, self.rad_spec, out=self.rgb_s, n_dev=nd))
+        self._run('mlp_rad_fwd', lambda: F.mlp_forward(self.rad_in, self.rad_blob, self.rad_spec, out=self.rgb_s, n_dev=nd,
+                                                       act_save=self.rad_act if tr else None))
 
     def composite(self, R, bkg):
         bkg_per_ray = int(bkg is not None and bkg.shape[0] == R and R > 1)
@@ -274,13 +278,13 @@ class NGPPipeline:
             self.g_rgb.data_ptr(), None, None, None, self.d_sigma.data_ptr(), self.d_rgb_s.data_ptr(),
             cfg['n_sample'], R, st))
         self._run('mlp_rad_bwd', lambda: F.mlp_backward(self.rad_in, self.rad_blob, self.rad_spec, self.d_rgb_s,
-                                                        dW=self.g_rad, dx=self.d_rad_in, n_dev=nd))
-        self._run('geo_head_grad', lambda: _lib.call(
-            'arcb200_geo_head_grad', self.rad_in.data_ptr(), 1, self.rad_in.stride(0), self.d_sigma.data_ptr(),
-            cfg['trunc_exp_clip'], self.d_rad_in.data_ptr(), 0, self.d_rad_in.stride(0), cfg['w_feat'],
-            self.d_geo_out.data_ptr(), C, nd.data_ptr(), st))
-        self._run('mlp_geo_bwd', lambda: F.mlp_backward(self.enc, self.geo_blob, self.geo_spec, self.d_geo_out,
-                                                        dW=self.g_geo, dx=self.d_enc, n_dev=nd))
+                                                        dW=self.g_rad, dx=self.d_rad_in, n_dev=nd,
+                                                        act_saved=self.rad_act, y_saved=self.rgb_s))
+        # geometry head: feature gradient = first W_feat columns of d_rad_in; the density gradient joins channel 0
+        # through TruncExp inside the kernel (no separate merge pass)
+        self._run('mlp_geo_bwd', lambda: F.mlp_backward(self.enc, self.geo_blob, self.geo_spec, self.d_rad_in,
+                                                        dW=self.g_geo, dx=self.d_enc, n_dev=nd, act_saved=self.geo_act,
+                                                        g0=self.d_sigma, x0=self.rad_in, clip=cfg['trunc_exp_clip']))
         self._run('grid_bwd', lambda: F.grid_backward(self.unit, self.d_enc, self.geom, grad_table=self.g_table, n_dev=nd))
 
     def optimizer_step(self):
@@ -420,6 +424,13 @@ class NGPPipeline:
     def render(self, rays_o, rays_d, bkg=None, chunk=None):
         """Full-frame forward in chunks of `max_rays` rays (the reference chunks by chunk_rays=32768,
         full_model.py:415-457); returns rgb (N,3), depth (N,), mask (N,)."""
+        was_training, self.training = self.training, False      # inference: no activations kept for a backward
+        try:
+            return self._render(rays_o, rays_d, bkg, chunk)
+        finally:
+            self.training = was_training
+
+    def _render(self, rays_o, rays_d, bkg, chunk):
         N = rays_o.shape[0]
         chunk = chunk or self.max_rays
         rgb = torch.empty((N, 3), dtype=torch.float32, device=self.dev)
@@ -434,5 +445,5 @@ class NGPPipeline:
         return rgb, depth, acc
 
     # number of library kernels one train_step enqueues (for bench.py's gpu_launches)
-    LAUNCHES_FORWARD = 1 + 4 + 1 + 1 + 1 + 1 + 1 + 1      # aabb, march(4), grid, geo mlp, sh, exp, rad mlp, composite
-    LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1 + 1 + 1 + 3 + 2   # huber, comp bwd, rad bwd, glue, geo bwd, grid bwd, step counter, adam x3, pack x2
+    LAUNCHES_FORWARD = 1 + 4 + 1 + 1 + 1 + 1 + 1      # aabb, march(4), grid, geo mlp (+density), sh, rad mlp, composite
+    LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1 + 1 + 3 + 2   # huber, comp bwd, rad bwd, geo bwd, grid bwd, step counter, adam x3, pack x2

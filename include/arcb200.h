@@ -236,6 +236,25 @@ int arcb200_mlp_pack_weights(const float *params, void *blob, int in_dim, int wi
 int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
                     int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, int64_t n,
                     const int32_t *n_dev, void *stream);
+/* Forward with extras.  act_save (optional; arcb200_mlp_act_save_bytes(n, width, n_hidden) bytes, 16-byte aligned)
+ * receives the hidden activations for arcb200_mlp_bwd_ex, as tcnn keeps them in training mode
+ * (fully_fused_mlp.cu:702-760, `forward.hidden`); exp0_out (optional, n floats) receives exp(output channel 0) taken
+ * from the value as stored in Y: FusedMLPGeoNet's TruncExp density (tcnn_fusedmlp_module.py:99-111,
+ * arcnerf/ops/trunc_exp.py:10-24) without a separate pass. */
+int64_t arcb200_mlp_act_save_bytes(int64_t n, int width, int n_hidden);
+int arcb200_mlp_fwd_ex(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                       int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, void *act_save,
+                       float *exp0_out, int64_t n, const int32_t *n_dev, void *stream);
+/* Backward with extras.  act_saved: buffer written by arcb200_mlp_fwd_ex for the same X / weights / n - the forward is
+ * then not re-computed, and y_saved (n,out_dim; fp16 if ys_is_half else fp32; leading dimension ldys) must hold the
+ * network outputs whenever out_act != 0.  g0/x0: extra gradient on output channel 0 that arrives through exp():
+ * dY[:,0] += g0[row] * exp(clamp(x0[row*ldx0], +-clip))  (TruncExp backward, trunc_exp.py:26-37, fused). */
+int arcb200_mlp_bwd_ex(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                       int out_dim, int hidden_act, int out_act, const float *dY, int64_t ldy, float loss_scale,
+                       void *dX, int dx_is_half, int64_t ldgx, float *dW, const void *act_saved, const void *y_saved,
+                       int ys_is_half, int64_t ldys, const float *g0, const void *x0, int x0_is_half, int64_t ldx0,
+                       float clip, int64_t n, const int32_t *n_dev, void *stream);
+
 /* Replaces tcnn Module.bwd for a FullyFusedMLP (bindings.cpp:111-170 -> fully_fused_mlp.cu:150-259,702-857).
  * dY (n,out_dim) fp32; dX (n,in_dim) fp32/fp16 or NULL; dW flat fp32 in the parameter layout, ACCUMULATED.
  * loss_scale: internal fp16 gradient scale (128 in the reference, modules.py:141).  width must be 64 or 128. */

@@ -229,3 +229,39 @@ def test_adam_and_huber(cuda):
     ls, gr = F.huber_loss(T(rgb, cuda), T(tgt, cuda))
     np.testing.assert_allclose(float(ls), float(lo.detach()), rtol=1e-5)
     np.testing.assert_allclose(gr.cpu().numpy(), rt.grad.numpy(), rtol=1e-5, atol=1e-7)
+
+
+@pytest.mark.parametrize('cfg', [MLP_CFGS[0], MLP_CFGS[1], MLP_CFGS[2]])
+@pytest.mark.parametrize('n', [1, 300, 20000])
+def test_mlp_saved_activations_and_density_extras(cuda, cfg, n):
+    """The forward's activation hand-over + the backward that skips re-computation give the re-computing backward's
+    results; exp0_out / (g0, x0) reproduce TruncExp forward / backward on output channel 0."""
+    in_dim, width, n_hidden, out_dim, ha, oa = cfg
+    spec = F.MlpSpec(in_dim, width, n_hidden, out_dim, ha, oa)
+    rng = np.random.RandomState(7)
+    params = rand_params(rng, spec.n_params)
+    x = T(rng.uniform(-1, 1, (n, in_dim)).astype(np.float32), cuda, torch.float16)
+    dy = T((rng.normal(size=(n, out_dim)) * 1e-2).astype(np.float32), cuda)
+    blob = F.mlp_pack(T(params, cuda), spec)
+    save = F.mlp_act_save_buffer(n, spec, cuda)
+    exp0 = torch.empty(n, device=cuda)
+    y16 = torch.empty((n, out_dim), dtype=torch.float16, device=cuda)
+    F.mlp_forward(x, blob, spec, out=y16, act_save=save, exp0_out=exp0)
+    y_plain = F.mlp_forward(x, blob, spec, out_dtype=torch.float16)
+    assert torch.equal(y16, y_plain)
+    np.testing.assert_allclose(exp0.cpu().numpy(), np.exp(y16[:, 0].float().cpu().numpy()), rtol=1e-6)
+    dx0, dw0 = F.mlp_backward(x, blob, spec, dy)
+    dx1, dw1 = F.mlp_backward(x, blob, spec, dy, act_saved=save, y_saved=y16)
+    np.testing.assert_allclose(dx1.cpu().numpy(), dx0.cpu().numpy(), rtol=2e-3, atol=2e-3 * float(dx0.abs().max()))
+    np.testing.assert_allclose(dw1.cpu().numpy(), dw0.cpu().numpy(), rtol=2e-3, atol=2e-3 * float(dw0.abs().max()))
+    # extra gradient on channel 0 through exp(clamp(x0))
+    g0 = T((rng.normal(size=n) * 1e-2).astype(np.float32), cuda)
+    dy2 = dy.clone()
+    dy2[:, 0] += g0 * torch.exp(y16[:, 0].float().clamp(-15, 15))
+    dx2, dw2 = F.mlp_backward(x, blob, spec, dy2, act_saved=save, y_saved=y16)
+    dx3, dw3 = F.mlp_backward(x, blob, spec, dy, act_saved=save, y_saved=y16, g0=g0, x0=y16, clip=15.0)
+    np.testing.assert_allclose(dx3.cpu().numpy(), dx2.cpu().numpy(), rtol=1e-3, atol=1e-3 * float(dx2.abs().max()))
+    np.testing.assert_allclose(dw3.cpu().numpy(), dw2.cpu().numpy(), rtol=1e-3, atol=1e-3 * float(dw2.abs().max()))
+    if oa != 'none':
+        with pytest.raises(RuntimeError):
+            F.mlp_backward(x, blob, spec, dy, act_saved=save)        # saved path needs the saved outputs
