@@ -41,15 +41,38 @@ __device__ __forceinline__ Seg segment(uint32_t ray, const int32_t *__restrict__
     return s;
 }
 
+// What one lane needs for one weighted entry.  Fetched one 32-wide chunk AHEAD of its use: the loads of chunk k+1
+// are in flight while chunk k goes through the shuffle scan, so a long ray pays the memory latency once, not per chunk.
+struct Item {
+    float geo, t0, t1, nz, r, g, b, gw;
+};
+
+template <bool IS_ALPHA, bool WITH_RAD>
+__device__ __forceinline__ Item fetch_item(const float *__restrict__ geo, const float *__restrict__ t,
+                                           const float *__restrict__ noise, const float *__restrict__ rad,
+                                           const float *__restrict__ g_w, int64_t start, int32_t i, int32_t n, int32_t m) {
+    Item it;
+    it.geo = 0.f; it.t0 = 0.f; it.t1 = 0.f; it.nz = 0.f; it.r = 0.f; it.g = 0.f; it.b = 0.f; it.gw = 0.f;
+    if (i >= 0 && i < m) {
+        const int64_t s = start + i;
+        it.geo = geo[s];
+        it.t0 = t[s];
+        if (!IS_ALPHA) {
+            it.t1 = (i < n - 1) ? t[s + 1] : 0.f;
+            if (noise) it.nz = noise[s];
+        }
+        if (WITH_RAD && rad) { it.r = rad[3 * s]; it.g = rad[3 * s + 1]; it.b = rad[3 * s + 2]; }
+        if (g_w) it.gw = g_w[s];
+    }
+    return it;
+}
+
 template <bool IS_ALPHA>
-__device__ __forceinline__ float interval_alpha(const float *__restrict__ geo, const float *__restrict__ t,
-                                                const float *__restrict__ noise, int64_t s, int32_t i, int32_t n,
-                                                float &delta, float &dens) {
-    if (IS_ALPHA) { delta = 0.f; dens = 0.f; return geo[s]; }
-    delta = (i < n - 1) ? (t[s + 1] - t[s]) : 1e10f;
+__device__ __forceinline__ float item_alpha(const Item &it, int32_t i, int32_t n, float &delta, float &dens) {
+    if (IS_ALPHA) { delta = 0.f; dens = 0.f; return it.geo; }
+    delta = (i < n - 1) ? (it.t1 - it.t0) : 1e10f;
     if (fabsf(delta) < 1e-5f) delta = 0.0f;
-    dens = geo[s] + (noise ? noise[s] : 0.0f);
-    dens = fmaxf(dens, 0.0f);
+    dens = fmaxf(it.geo + it.nz, 0.0f);
     return 1.0f - expf(-dens * delta);
 }
 
@@ -88,12 +111,14 @@ composite_fwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
 
     float carry = 1.0f, t_bkg = 1.0f;
     float ar = 0.f, ag = 0.f, ab = 0.f, ad = 0.f, aw = 0.f;
+    Item cur = fetch_item<IS_ALPHA, true>(geo, t, noise, rad, nullptr, sg.start, (int32_t)lane, n, m);
     for (int32_t base = 0; base < m; base += 32) {
         const int32_t i = base + (int32_t)lane;
         const bool on = i < m;
         const int64_t s = sg.start + i;
+        const Item nxt = fetch_item<IS_ALPHA, true>(geo, t, noise, rad, nullptr, sg.start, i + 32, n, m);
         float delta, dens;
-        const float alpha = on ? interval_alpha<IS_ALPHA>(geo, t, noise, s, i, n, delta, dens) : 0.0f;
+        const float alpha = on ? item_alpha<IS_ALPHA>(cur, i, n, delta, dens) : 0.0f;
         const float f = on ? (1.0f - alpha + 1e-10f) : 1.0f;
         const float incl = warp_prod_inclusive(f, lane);
         float excl = __shfl_up_sync(ARC_FULL_MASK, incl, 1);
@@ -101,8 +126,8 @@ composite_fwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
         const float T = carry * excl;
         const float w = alpha * T;
         if (on) {
-            if (rad) { ar = fmaf(w, rad[3 * s], ar); ag = fmaf(w, rad[3 * s + 1], ag); ab = fmaf(w, rad[3 * s + 2], ab); }
-            ad = fmaf(w, t[s], ad);
+            if (rad) { ar = fmaf(w, cur.r, ar); ag = fmaf(w, cur.g, ag); ab = fmaf(w, cur.b, ab); }
+            ad = fmaf(w, cur.t0, ad);
             aw += w;
             if (w_out) w_out[s] = w;
             if (trans_out) trans_out[s] = T;
@@ -112,6 +137,7 @@ composite_fwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
         if (k_bkg >= base && k_bkg < base + 32) t_bkg = __shfl_sync(ARC_FULL_MASK, T, k_bkg - base);
         carry *= __shfl_sync(ARC_FULL_MASK, incl, 31);
         if (k_bkg == base + 32) t_bkg = carry;
+        cur = nxt;
     }
     // the unweighted closing sample(s) of the segment
     for (int32_t i = m + (int32_t)lane; i < n; i += 32) {
@@ -175,12 +201,14 @@ composite_bwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
     #pragma unroll
     for (int q = 0; q < kMaxChunks / 32; ++q) carries[q] = 1.0f;
     float carry = 1.0f, t_bkg = 1.0f;
+    Item cur = fetch_item<IS_ALPHA, false>(geo, t, noise, nullptr, nullptr, sg.start, (int32_t)lane, n, m);
     for (int32_t c = 0; c < n_chunks; ++c) {
         const int32_t base = c << 5;
         const int32_t i = base + (int32_t)lane;
         const bool on = i < m;
+        const Item nxt = fetch_item<IS_ALPHA, false>(geo, t, noise, nullptr, nullptr, sg.start, i + 32, n, m);
         float delta, dens;
-        const float alpha = on ? interval_alpha<IS_ALPHA>(geo, t, noise, sg.start + i, i, n, delta, dens) : 0.0f;
+        const float alpha = on ? item_alpha<IS_ALPHA>(cur, i, n, delta, dens) : 0.0f;
         const float f = on ? (1.0f - alpha + 1e-10f) : 1.0f;
         const float incl = warp_prod_inclusive(f, lane);
         #pragma unroll
@@ -193,18 +221,21 @@ composite_bwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
         }
         carry *= __shfl_sync(ARC_FULL_MASK, incl, 31);
         if (k_bkg == base + 32) t_bkg = carry;
+        cur = nxt;
     }
     const float bkg_term = t_bkg * v_bkg;
 
     // pass 2 (reverse): suffix sums of w_j * v_j
     float suffix = 0.0f;
+    cur = fetch_item<IS_ALPHA, true>(geo, t, noise, rad, g_w, sg.start, ((n_chunks - 1) << 5) + (int32_t)lane, n, m);
     for (int32_t c = n_chunks - 1; c >= 0; --c) {
         const int32_t base = c << 5;
         const int32_t i = base + (int32_t)lane;
         const bool on = i < m;
         const int64_t s = sg.start + i;
+        const Item nxt = fetch_item<IS_ALPHA, true>(geo, t, noise, rad, g_w, sg.start, i - 32, n, m);
         float delta = 0.f, dens = 0.f;
-        const float alpha = on ? interval_alpha<IS_ALPHA>(geo, t, noise, s, i, n, delta, dens) : 0.0f;
+        const float alpha = on ? item_alpha<IS_ALPHA>(cur, i, n, delta, dens) : 0.0f;
         const float f = on ? (1.0f - alpha + 1e-10f) : 1.0f;
         const float incl = warp_prod_inclusive(f, lane);
         float excl = __shfl_up_sync(ARC_FULL_MASK, incl, 1);
@@ -217,8 +248,8 @@ composite_bwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
         const float w = alpha * T;
         float v = 0.f;
         if (on) {
-            if (rad) v = gr * rad[3 * s] + gg * rad[3 * s + 1] + gb * rad[3 * s + 2];
-            v += gd * t[s] + ga + (g_w ? g_w[s] : 0.f);
+            if (rad) v = gr * cur.r + gg * cur.g + gb * cur.b;
+            v += gd * cur.t0 + ga + cur.gw;
         }
         // exclusive suffix sum inside the chunk
         float wv = w * v, sfx = wv;
@@ -236,6 +267,7 @@ composite_bwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
             if (d_rad) { d_rad[3 * s] = w * gr; d_rad[3 * s + 1] = w * gg; d_rad[3 * s + 2] = w * gb; }
         }
         suffix += __shfl_sync(ARC_FULL_MASK, sfx, 0);
+        cur = nxt;
     }
     for (int32_t i = m + (int32_t)lane; i < n; i += 32) {
         const int64_t s = sg.start + i;
