@@ -130,9 +130,13 @@ class NGPPipeline:
         self.geo_blob = F.mlp_pack(self.geo_p, self.geo_spec)
         self.rad_blob = F.mlp_pack(self.rad_p, self.rad_spec)
         z = lambda t: torch.zeros_like(t)
-        self.g_table, self.m_table, self.v_table = z(self.table), z(self.table), z(self.table)
-        self.g_geo, self.m_geo, self.v_geo = z(self.geo_p), z(self.geo_p), z(self.geo_p)
-        self.g_rad, self.m_rad, self.v_rad = z(self.rad_p), z(self.rad_p), z(self.rad_p)
+        # one flat gradient buffer (hash table | geometry head | radiance head): a single collective moves it all
+        nt, ng, nr = self.table.numel(), self.geo_p.numel(), self.rad_p.numel()
+        self.g_all = torch.zeros(nt + ng + nr, dtype=torch.float32, device=dev)
+        self.g_table, self.g_geo, self.g_rad = self.g_all[:nt], self.g_all[nt:nt + ng], self.g_all[nt + ng:]
+        self.m_table, self.v_table = z(self.table), z(self.table)
+        self.m_geo, self.v_geo = z(self.geo_p), z(self.geo_p)
+        self.m_rad, self.v_rad = z(self.rad_p), z(self.rad_p)
         self.step_count = 0
         self.step_dev = torch.zeros(1, dtype=torch.int32, device=dev)     # same count, device resident (graph replays)
         # occupancy + box
@@ -304,13 +308,6 @@ class NGPPipeline:
             F.mlp_pack(self.rad_p, self.rad_spec, self.rad_blob)
         self._run('adam_mlp+pack', mlp_update)
 
-    def all_reduce_grads(self):
-        """Data-parallel exchange: sum of the hash-table and MLP gradients over ranks (NCCL over NVLink); the
-        reference gets the same from DDP's bucketed all-reduce (basic_trainer.py:192-202)."""
-        if self.world_size > 1:
-            from .dist import all_reduce_sum_
-            all_reduce_sum_([self.g_table, self.g_geo, self.g_rad])
-
     def train_step(self, rays_o, rays_d, target, bkg=None, optimize=True, next_rays=None):
         """One optimisation step on a ray batch; returns the (device) loss tensor.  No host synchronisation.
         next_rays = (rays_o, rays_d) of the following batch, if known: it is sampled on the side stream meanwhile
@@ -323,9 +320,19 @@ class NGPPipeline:
             self.cfg['loss_weight'], self.g_rgb.data_ptr(), self.loss.data_ptr(), R, _lib.current_stream()))
         self.backward(rays_d, R, bkg)
         if optimize:
-            self._run('all_reduce', self.all_reduce_grads)
-            self.optimizer_step()
+            if self.world_size > 1:
+                self.exchange_and_step()
+            else:
+                self.optimizer_step()
         return self.loss
+
+    def exchange_and_step(self):
+        """Data-parallel step: ONE sum over ranks of the flat gradient buffer (hash table + both heads, 48.8 MB; NCCL
+        over NVLink/NVSwitch), then Adam with grad_scale = 1/world - the mean gradient DDP would deliver
+        (common/trainer/basic_trainer.py:192-202)."""
+        import torch.distributed as dist
+        self._run('all_reduce', lambda: dist.all_reduce(self.g_all))
+        self.optimizer_step()
 
     # ------------------------------------------------------------------------------------------ replayed step
     def _step_body(self, R, rays_d, target, bkg):
@@ -337,13 +344,15 @@ class NGPPipeline:
             'arcb200_huber_loss', self.rgb.data_ptr(), target.data_ptr(), self.cfg['huber_delta'],
             self.cfg['loss_weight'], self.g_rgb.data_ptr(), self.loss.data_ptr(), R, _lib.current_stream()))
         self.backward(rays_d, R, bkg)
-        self.optimizer_step()
+        if self.world_size > 1:
+            self.exchange_and_step()
+        else:
+            self.optimizer_step()
 
     def enable_graphs(self, n_rays):
         """Static input slots + one CUDA graph per sample-set parity for the post-sampler part of a step (20 launches
         replayed as one).  The sampler itself stays a normal launch on the side stream: its jitter generator state is
-        a by-value argument that changes every call.  Single-GPU only (the gradient exchange is not captured)."""
-        assert self.world_size == 1, 'graph replay is implemented for the single-GPU step'
+        a by-value argument that changes every call.  With several ranks the gradient all-reduce is captured too."""
         dev, f32 = self.dev, torch.float32
         self.static_in = [tuple(torch.empty((n_rays, 3), dtype=f32, device=dev) for _ in range(4)) for _ in range(2)]
         self.graph_rays = n_rays
@@ -356,8 +365,11 @@ class NGPPipeline:
             o, d, t, b = self.static_in[1 - self.cur]
             d[:, 2] = 1.0
             self.train_step(o, d, t, b, optimize=False)
+        if self.world_size > 1:                          # communicator set-up must not happen inside the capture
+            import torch.distributed as dist
+            dist.all_reduce(self.g_all)
         torch.cuda.synchronize()
-        self.g_table.zero_(); self.g_geo.zero_(); self.g_rad.zero_()
+        self.g_all.zero_()
         count0, step0 = self.step_count, self.step_dev.clone()
         keep = (self.table.clone(), self.geo_p.clone(), self.rad_p.clone(), self.m_table.clone(), self.v_table.clone(),
                 self.m_geo.clone(), self.v_geo.clone(), self.m_rad.clone(), self.v_rad.clone())

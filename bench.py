@@ -169,6 +169,9 @@ def run_reference_arm(args, rank, world):
 
 
 def main():
+    if os.environ.get('ARCB200_BENCH_WATCHDOG'):        # debugging aid: dump every thread's stack and exit if the run hangs
+        import faulthandler
+        faulthandler.dump_traceback_later(float(os.environ['ARCB200_BENCH_WATCHDOG']), exit=True)
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
     ap.add_argument('--steps', type=int, default=50)
@@ -245,8 +248,9 @@ def main():
 
     # ---- timed: end to end from host buffers (H2D rays + targets, D2H loss, every step)
     loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
-    if world == 1:
-        # single GPU: static input slots + CUDA-graph replay of the post-sampler part of the step
+    use_graph = os.environ.get('ARCB200_BENCH_GRAPH', '1') == '1'
+    if use_graph:
+        # static input slots + CUDA-graph replay of the post-sampler part of the step (incl. the NCCL all-reduce)
         pipe.enable_graphs(N_RAYS)
         for i in range(3):
             pipe.train_step_graphed(host[i], next_batch=host[i + 1])
@@ -385,7 +389,14 @@ def main():
         )
         print(json.dumps(line))
     if dist is not None:
+        # captured graphs hold NCCL work: release them before the communicator, and never let teardown hang the job
+        sys.stdout.flush()
+        threading.Timer(20.0, lambda: os._exit(0)).start()
+        pipe.graphs = None
+        torch.cuda.synchronize()
+        dist.barrier()
         dist.destroy_process_group()
+        os._exit(0)
 
 
 if __name__ == '__main__':
