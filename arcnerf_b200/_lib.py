@@ -64,6 +64,13 @@ _SIGS = {
     'arcb200_adam_step': [P, P, P, P, P, L, I, F, F, F, F, F, F, I, P, P],
     'arcb200_counter_add': [P, I, P],
     'arcb200_huber_loss': [P, P, F, F, P, P, L, P],
+    'arcb200_mlp_adam_pack': [I, P, P, P, P, P, I, P, I, F, F, F, F, F, F, I, P, P],
+    'arcb200_peer_alloc': [L, P, P],
+    'arcb200_peer_open': [P, P],
+    'arcb200_peer_close': [P],
+    'arcb200_peer_free': [P],
+    'arcb200_peer_barrier': [P, I, I, P, P, I, P],
+    'arcb200_adam_step_peer': [P, P, I, L, L, P, P, P, I, F, F, F, F, F, F, P, P],
 }
 _RESTYPE = {
     'arcb200_last_error': C.c_char_p,

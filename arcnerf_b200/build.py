@@ -29,6 +29,7 @@ SOURCES = {
     'optim.cu': [],
     'glue.cu': [],
     'noalloc.cu': [],
+    'peer.cu': [],
 }
 
 

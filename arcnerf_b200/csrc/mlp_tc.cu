@@ -21,6 +21,8 @@
 // very same tiles), flushing them once per CTA with fp32 atomics.
 #include "common.cuh"
 #include "tc05.cuh"
+#include "adam.cuh"
+#include <string.h>
 
 namespace {
 
@@ -568,6 +570,44 @@ __global__ void pack_weights_kernel(MlpCfg cfg, const float *__restrict__ params
     }
 }
 
+// ---- optimiser step of the (small) networks: Adam on the flat fp32 parameters and the fp16 operand tiles of the
+// updated weights in the same pass, for up to kMaxJobs networks per launch (blockIdx.y = network).  The gradient is
+// the sum over `world` vectors in index order (1 = this GPU's own; several = every rank's copy through peer memory).
+constexpr int kMaxJobs = 4;
+constexpr int kMaxGradSrc = 16;
+
+struct AdamPackJob {
+    MlpCfg cfg;
+    int n_params;
+    float *p, *m, *v;
+    uint8_t *blob;
+    float *grad[kMaxGradSrc];
+};
+struct AdamPackJobs { AdamPackJob job[kMaxJobs]; };
+
+__global__ void mlp_adam_pack_kernel(const __grid_constant__ AdamPackJobs jobs, int world, AdamHyper h, int zero_grad,
+                                     const int32_t *__restrict__ step_dev) {
+    const AdamPackJob &J = jobs.job[blockIdx.y];
+    if (step_dev) bias_from_step(h, max(*step_dev, 1));
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < J.n_params; i += gridDim.x * blockDim.x) {
+        float g = __ldcg(J.grad[0] + i);
+        for (int w = 1; w < world; ++w) g += __ldcg(J.grad[w] + i);
+        float pp = J.p[i], mm = J.m[i], vv = J.v[i];
+        adam_one(pp, mm, vv, g, h);
+        J.p[i] = pp; J.m[i] = mm; J.v[i] = vv;
+        if (zero_grad) J.grad[0][i] = 0.f;
+        int l = 0;
+        #pragma unroll
+        for (int q = 1; q < kMaxMM; ++q)
+            if (q < J.cfg.n_mm && (uint32_t)i >= J.cfg.p_off[q]) l = q;
+        const int K = J.cfg.K[l], N = J.cfg.N[l];
+        const int e = i - (int)J.cfg.p_off[l];
+        const int r = e / K, c = e - r * K;
+        __half *tile = reinterpret_cast<__half *>(J.blob + J.cfg.w_off[l]);
+        tile[(size_t)(c >> 3) * (N * 8) + (size_t)r * 8 + (c & 7)] = __float2half_rn(pp);
+    }
+}
+
 int make_cfg(MlpCfg &c, int in_dim, int width, int n_hidden, int out_dim, int hidden_act, int out_act) {
     if (n_hidden < 1 || n_hidden + 1 > kMaxMM) return -1;
     if (width % 16 != 0 || width < 16 || width > 128) return -1;
@@ -665,6 +705,41 @@ int arcb200_mlp_pack_weights(const float *params, void *blob, int in_dim, int wi
     ARC_REQUIRE(make_cfg(c, in_dim, width, n_hidden, out_dim, 0, 0) >= 0, "mlp_pack_weights: unsupported shape");
     ARC_REQUIRE(params && blob && ((uintptr_t)blob & 15u) == 0, "mlp_pack_weights: null or misaligned pointer");
     pack_weights_kernel<<<dim3(8, c.n_mm), 256, 0, (cudaStream_t)stream>>>(c, params, (uint8_t *)blob);
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// Adam + re-packing of n_mlps (<= 4) small networks in ONE launch: replaces, per network, arcb200_adam_step followed by
+// arcb200_mlp_pack_weights (the reference: torch.optim.Adam on tcnn's `params`, common/trainer/optimizer.py, and
+// tcnn's own fp32->fp16 cast of the parameters at the next forward, tinycudann/modules.py:156).
+//   shapes : host int[n_mlps*4] = in_dim, width, n_hidden, out_dim of each network
+//   p, m, v, blobs : host arrays of n_mlps device pointers
+//   grads  : host array of n_mlps*world device pointers, grads[j*world + w] = rank w's gradient of network j (world = 1:
+//            the local gradient).  Summed in index order, scaled by grad_scale.  zero_grad clears grads[j*world + 0].
+int arcb200_mlp_adam_pack(int n_mlps, const int *shapes, float *const *p, float *const *m, float *const *v,
+                          void *const *grads, int world, void *const *blobs, int step, float lr, float beta1,
+                          float beta2, float eps, float weight_decay, float grad_scale, int zero_grad,
+                          const int32_t *step_dev, void *stream) {
+    ARC_REQUIRE(n_mlps >= 1 && n_mlps <= kMaxJobs, "mlp_adam_pack: 1..%d networks per call", kMaxJobs);
+    ARC_REQUIRE(world >= 1 && world <= kMaxGradSrc, "mlp_adam_pack: world %d out of range (max %d)", world, kMaxGradSrc);
+    ARC_REQUIRE(shapes && p && m && v && grads && blobs && (step >= 1 || step_dev), "mlp_adam_pack: null pointer or step < 1");
+    AdamPackJobs jobs;
+    memset(&jobs, 0, sizeof(jobs));
+    int n_max = 0;
+    for (int j = 0; j < n_mlps; ++j) {
+        AdamPackJob &J = jobs.job[j];
+        J.n_params = make_cfg(J.cfg, shapes[4 * j], shapes[4 * j + 1], shapes[4 * j + 2], shapes[4 * j + 3], 0, 0);
+        ARC_REQUIRE(J.n_params > 0, "mlp_adam_pack: unsupported shape of network %d", j);
+        J.p = p[j]; J.m = m[j]; J.v = v[j]; J.blob = (uint8_t *)blobs[j];
+        ARC_REQUIRE(J.p && J.m && J.v && J.blob, "mlp_adam_pack: null buffer of network %d", j);
+        for (int w = 0; w < world; ++w) {
+            J.grad[w] = (float *)grads[j * world + w];
+            ARC_REQUIRE(J.grad[w] != nullptr, "mlp_adam_pack: null gradient %d of network %d", w, j);
+        }
+        n_max = J.n_params > n_max ? J.n_params : n_max;
+    }
+    const AdamHyper h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, grad_scale, step < 1 ? 1 : step);
+    mlp_adam_pack_kernel<<<dim3((n_max + 255) / 256, n_mlps), 256, 0, (cudaStream_t)stream>>>(jobs, world, h, zero_grad, step_dev);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }

@@ -4,27 +4,9 @@
 // nerf_lego_nerf_ngp.yaml:192-197, arcnerf/loss/img_loss.py:80-98) with its gradient.
 // Both are pure HBM streams: Adam moves 34 B per parameter (p, m, v, g in; p, m, v, g=0, fp16 p out).
 #include "common.cuh"
+#include "adam.cuh"
 
 namespace {
-
-struct AdamHyper {
-    float lr, beta1, beta2, eps, weight_decay;
-    float bias1, bias2_sqrt;   // 1 - beta1^t, sqrt(1 - beta2^t)
-    float grad_scale;          // multiplies the incoming gradient (e.g. 1/world_size after an all-reduce sum)
-};
-
-__device__ __forceinline__ void bias_from_step(AdamHyper &h, int step) {
-    h.bias1 = (float)(1.0 - pow((double)h.beta1, (double)step));
-    h.bias2_sqrt = (float)sqrt(1.0 - pow((double)h.beta2, (double)step));
-}
-
-__device__ __forceinline__ void adam_one(float &p, float &m, float &v, float g, const AdamHyper &h) {
-    g = g * h.grad_scale + h.weight_decay * p;
-    m = h.beta1 * m + (1.0f - h.beta1) * g;
-    v = h.beta2 * v + (1.0f - h.beta2) * g * g;
-    const float denom = sqrtf(v) / h.bias2_sqrt + h.eps;
-    p -= (h.lr / h.bias1) * (m / denom);
-}
 
 __global__ void adam_kernel(size_t n, float *__restrict__ p, float *__restrict__ m, float *__restrict__ v,
                             float *__restrict__ g, __half *__restrict__ p_half, AdamHyper h, int zero_grad,
@@ -105,11 +87,7 @@ int arcb200_adam_step(float *p, float *m, float *v, float *g, void *p_half, int6
     if (step < 1) step = 1;
     ARC_REQUIRE((((uintptr_t)p | (uintptr_t)m | (uintptr_t)v | (uintptr_t)g) & 15u) == 0 && ((uintptr_t)p_half & 7u) == 0,
                 "adam_step: misaligned buffer");
-    AdamHyper h;
-    h.lr = lr; h.beta1 = beta1; h.beta2 = beta2; h.eps = eps; h.weight_decay = weight_decay;
-    h.bias1 = (float)(1.0 - pow((double)beta1, (double)step));
-    h.bias2_sqrt = (float)sqrt(1.0 - pow((double)beta2, (double)step));
-    h.grad_scale = grad_scale;
+    const AdamHyper h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, grad_scale, step);
     long long blocks = (n / 4 + 255) / 256;
     const long long cap = (long long)arc_sm_count() * 16;
     if (blocks > cap) blocks = cap;

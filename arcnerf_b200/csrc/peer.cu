@@ -1,0 +1,267 @@
+// Data-parallel optimiser step over NVLink peer memory (one process per GPU, same node).
+//
+// The reference trains data-parallel through torch DDP: every rank all-reduces the full fp32 gradient and then
+// runs the same Adam on the full parameter vector (common/trainer/basic_trainer.py:192-202,
+// common/trainer/optimizer.py).  For the NGP hot path that is 48.8 MB of hash-table gradient per step, produced by
+// the LAST backward kernel, so the exchange cannot hide behind the backward.  Here the exchange and the update are
+// one kernel: rank r owns a contiguous slice of the parameter vector, loads that slice of every rank's gradient
+// straight from the peers' HBM (NVLink loads, summed in rank order), applies Adam to its slice and stores the fp16
+// working copy of the slice into every rank's table (NVLink stores).  Per rank and step that moves (N-1)/N * 4 B
+// in and (N-1)/N * 2 B out per parameter over NVLink and 1/N of the Adam HBM stream - no NCCL on the data path.
+// Small replicated vectors (the two MLP heads) use the same kernel with the full range on every rank: each rank
+// sums all ranks' gradients in the same order, so the replicas stay bit-identical.
+//
+// Ordering between ranks is two flag barriers per step (arcb200_peer_barrier), each a 1-block kernel on the
+// step's stream: A) "my backward is complete, my gradient may be read" before the update, B) "I no longer read your
+// gradient nor write your table" after it.  Flags are epoch counters that only grow, kept in the shared arena.
+#include "adam.cuh"
+#include <string.h>
+
+namespace {
+
+constexpr int kMaxWorld = 16;
+
+struct PeerList {
+    const float *grad[kMaxWorld];   // gradient vectors of all ranks (index = rank), same layout on every rank
+    __half *half_out[kMaxWorld];    // fp16 working copies of all ranks, or all null
+};
+
+struct FlagList {
+    unsigned long long *flags[kMaxWorld];   // flags[w] = base of rank w's flag array (kMaxWorld entries)
+};
+
+__device__ __forceinline__ float4 ld_peer4(const float *p, size_t k4) {
+    // L1-bypassing 128-bit load: peer lines are never held in this SM's L1 across kernels, the home L2 is coherent
+    return __ldcg(reinterpret_cast<const float4 *>(p) + k4);
+}
+
+__device__ __forceinline__ void acc4(float4 &a, const float4 &b) { a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
+
+// W > 0: world size known at compile time (all peer loads of one element group are in flight together);
+// W == 0: run-time world size, sequential accumulation.
+template <int W>
+__global__ void adam_peer_kernel(size_t lo, size_t hi, float *__restrict__ p, float *__restrict__ m,
+                                 float *__restrict__ v, const __grid_constant__ PeerList peers, int world,
+                                 AdamHyper h, const int32_t *__restrict__ step_dev) {
+    if (step_dev) bias_from_step(h, max(*step_dev, 1));
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t k_lo = lo / 4, k_hi = hi / 4;            // lo is a multiple of 4
+    const bool want_half = peers.half_out[0] != nullptr;
+    // two element groups per trip: every load of both groups (peer and local) is issued before the first store
+    auto load_grad = [&](size_t k) {
+        float4 gg;
+        if (W > 0) {
+            float4 part[W > 0 ? W : 1];
+            #pragma unroll
+            for (int w = 0; w < W; ++w) part[w] = ld_peer4(peers.grad[w], k);
+            gg = part[0];
+            #pragma unroll
+            for (int w = 1; w < W; ++w) acc4(gg, part[w]);
+        } else {
+            gg = ld_peer4(peers.grad[0], k);
+            for (int w = 1; w < world; ++w) acc4(gg, ld_peer4(peers.grad[w], k));
+        }
+        return gg;
+    };
+    auto update = [&](size_t k, float4 gg, float4 pp, float4 mm, float4 vv) {
+        adam_one(pp.x, mm.x, vv.x, gg.x, h); adam_one(pp.y, mm.y, vv.y, gg.y, h);
+        adam_one(pp.z, mm.z, vv.z, gg.z, h); adam_one(pp.w, mm.w, vv.w, gg.w, h);
+        reinterpret_cast<float4 *>(p)[k] = pp;
+        reinterpret_cast<float4 *>(m)[k] = mm;
+        reinterpret_cast<float4 *>(v)[k] = vv;
+        if (want_half) {
+            __half2 a = __floats2half2_rn(pp.x, pp.y), b = __floats2half2_rn(pp.z, pp.w);
+            uint2 pk;
+            pk.x = *reinterpret_cast<uint32_t *>(&a);
+            pk.y = *reinterpret_cast<uint32_t *>(&b);
+            const int n = W > 0 ? W : world;
+            #pragma unroll
+            for (int w = 0; w < (W > 0 ? W : kMaxWorld); ++w)
+                if (w < n) reinterpret_cast<uint2 *>(peers.half_out[w])[k] = pk;
+        }
+    };
+    for (size_t k = k_lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < k_hi; k += 2 * stride) {
+        const size_t k2 = k + stride;
+        const bool two = k2 < k_hi;
+        const float4 g1 = load_grad(k);
+        const float4 p1 = reinterpret_cast<const float4 *>(p)[k], m1 = reinterpret_cast<const float4 *>(m)[k],
+                     v1 = reinterpret_cast<const float4 *>(v)[k];
+        float4 g2, p2, m2, v2;
+        if (two) {
+            g2 = load_grad(k2);
+            p2 = reinterpret_cast<const float4 *>(p)[k2]; m2 = reinterpret_cast<const float4 *>(m)[k2];
+            v2 = reinterpret_cast<const float4 *>(v)[k2];
+        }
+        update(k, g1, p1, m1, v1);
+        if (two) update(k2, g2, p2, m2, v2);
+    }
+    // scalar tail of the range (hi not a multiple of 4)
+    for (size_t k = k_hi * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < hi; k += stride) {
+        float g = __ldcg(peers.grad[0] + k);
+        for (int w = 1; w < world; ++w) g += __ldcg(peers.grad[w] + k);
+        float pp = p[k], mm = m[k], vv = v[k];
+        adam_one(pp, mm, vv, g, h);
+        p[k] = pp; m[k] = mm; v[k] = vv;
+        if (want_half)
+            for (int w = 0; w < world; ++w) peers.half_out[w][k] = __float2half_rn(pp);
+    }
+}
+
+__device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long *p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// One block, one thread per rank.  epoch[0] += 1; publish it into slot `rank` of every rank's flag array, then wait
+// until every slot of the own array has reached it.  A wait longer than timeout_ns gives up and raises status[0]
+// (the step's results are then invalid, but the GPU is not left spinning).
+__global__ void peer_barrier_kernel(const __grid_constant__ FlagList fl, int world, int rank,
+                                    unsigned long long *epoch, int32_t *status, unsigned long long timeout_ns) {
+    __shared__ unsigned long long target;
+    if (threadIdx.x == 0) {
+        target = *epoch + 1ull;
+        *epoch = target;
+        __threadfence_system();          // everything earlier on this stream (incl. stores to peers) before the flags
+    }
+    __syncthreads();
+    const unsigned long long e = target;
+    const int w = threadIdx.x;
+    if (w < world) {
+        st_release_sys(fl.flags[w] + rank, e);
+        const unsigned long long *mine = fl.flags[rank] + w;
+        const unsigned long long t0 = global_ns();
+        while (ld_acquire_sys(mine) < e) {
+            if (global_ns() - t0 > timeout_ns) {
+                atomicExch(status, 1);
+                break;
+            }
+            __nanosleep(64);
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) __threadfence_system();
+}
+
+template <int W>
+void launch_adam_peer(unsigned blocks, cudaStream_t st, size_t lo, size_t hi, float *p, float *m, float *v,
+                      const PeerList &pl, int world, const AdamHyper &h, const int32_t *step_dev) {
+    adam_peer_kernel<W><<<blocks, 256, 0, st>>>(lo, hi, p, m, v, pl, world, h, step_dev);
+}
+
+}  // namespace
+
+extern "C" {
+
+// Device memory that other processes on the node can map: cudaMalloc + IPC handle (64 bytes, to be sent to the
+// peers by any host channel).  No counterpart in the reference (DDP/NCCL own their buffers).
+int arcb200_peer_alloc(int64_t bytes, void **ptr_out, unsigned char *handle_out) {
+    ARC_REQUIRE(bytes > 0 && ptr_out && handle_out, "peer_alloc: bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    void *p = nullptr;
+    ARC_CUDA(cudaMalloc(&p, (size_t)bytes));
+    cudaIpcMemHandle_t hd;
+    cudaError_t e = cudaIpcGetMemHandle(&hd, p);
+    if (e != cudaSuccess) {
+        cudaFree(p);
+        arcb200_set_error("peer_alloc: cudaIpcGetMemHandle -> %s", cudaGetErrorString(e));
+        return ARCB200_ERR_CUDA;
+    }
+    ARC_CUDA(cudaMemset(p, 0, (size_t)bytes));
+    memcpy(handle_out, &hd, 64);
+    *ptr_out = p;
+    return ARCB200_OK;
+}
+
+// Map a peer's arena into this process (current device must be able to reach the owner over NVLink/PCIe P2P).
+int arcb200_peer_open(const unsigned char *handle, void **ptr_out) {
+    ARC_REQUIRE(handle && ptr_out, "peer_open: null pointer");
+    cudaIpcMemHandle_t hd;
+    memcpy(&hd, handle, 64);
+    void *p = nullptr;
+    ARC_CUDA(cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess));
+    *ptr_out = p;
+    return ARCB200_OK;
+}
+
+int arcb200_peer_close(void *ptr) {
+    if (ptr) ARC_CUDA(cudaIpcCloseMemHandle(ptr));
+    return ARCB200_OK;
+}
+
+int arcb200_peer_free(void *ptr) {
+    if (ptr) ARC_CUDA(cudaFree(ptr));
+    return ARCB200_OK;
+}
+
+// Flag barrier between the ranks of a node on `stream` (see the file header).  flags[w]: rank w's flag array
+// (>= 16 uint64, zero-initialised, in peer-mapped memory), as mapped in THIS process; epoch: this rank's device
+// counter (uint64, starts at 0, private); status: device int32 raised to 1 when a wait exceeded timeout_ms.
+int arcb200_peer_barrier(void *const *flags, int world, int rank, void *epoch, int32_t *status, int timeout_ms,
+                         void *stream) {
+    ARC_REQUIRE(flags && epoch && status, "peer_barrier: null pointer");
+    ARC_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, "peer_barrier: world %d rank %d out of range (max %d ranks)",
+                world, rank, kMaxWorld);
+    FlagList fl;
+    for (int w = 0; w < kMaxWorld; ++w) fl.flags[w] = w < world ? (unsigned long long *)flags[w] : nullptr;
+    for (int w = 0; w < world; ++w) ARC_REQUIRE(fl.flags[w] != nullptr, "peer_barrier: flags[%d] is null", w);
+    if (timeout_ms <= 0) timeout_ms = 20000;
+    peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(fl, world, rank, (unsigned long long *)epoch, status,
+                                                           (unsigned long long)timeout_ms * 1000000ull);
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// Fused gradient exchange + Adam + parameter broadcast over elements [lo, hi) of a flat parameter vector.
+//   grads[w]    : rank w's gradient vector (fp32, full length, peer-mapped); summed over w = 0..world-1 in that order
+//   p, m, v     : this rank's fp32 parameters and Adam moments (full-length vectors; only [lo, hi) is touched)
+//   half_out[w] : rank w's fp16 working copy (full length) - the updated slice is stored into every one of them -
+//                 or half_out == NULL for no fp16 copy
+// Gradients are NOT cleared (peers may still be reading them: clear after the closing barrier).  lo % 4 == 0.
+// Arithmetic = arcb200_adam_step on the summed gradient with grad_scale (1/world for DDP's mean).
+int arcb200_adam_step_peer(const void *const *grads, void *const *half_out, int world, int64_t lo, int64_t hi,
+                           float *p, float *m, float *v, int step, float lr, float beta1, float beta2, float eps,
+                           float weight_decay, float grad_scale, const int32_t *step_dev, void *stream) {
+    ARC_REQUIRE(world >= 1 && world <= kMaxWorld, "adam_step_peer: world %d out of range (max %d ranks)", world, kMaxWorld);
+    ARC_REQUIRE(lo >= 0 && hi >= lo && (lo & 3) == 0, "adam_step_peer: bad range [%lld, %lld)", (long long)lo, (long long)hi);
+    if (hi == lo) return ARCB200_OK;
+    ARC_REQUIRE(grads && p && m && v && (step >= 1 || step_dev), "adam_step_peer: null pointer or step < 1");
+    if (step < 1) step = 1;
+    ARC_REQUIRE((((uintptr_t)p | (uintptr_t)m | (uintptr_t)v) & 15u) == 0, "adam_step_peer: misaligned buffer");
+    PeerList pl;
+    for (int w = 0; w < kMaxWorld; ++w) {
+        pl.grad[w] = w < world ? (const float *)grads[w] : nullptr;
+        pl.half_out[w] = (w < world && half_out) ? (__half *)half_out[w] : nullptr;
+    }
+    for (int w = 0; w < world; ++w) {
+        ARC_REQUIRE(pl.grad[w] && ((uintptr_t)pl.grad[w] & 15u) == 0, "adam_step_peer: grads[%d] null or misaligned", w);
+        ARC_REQUIRE(!half_out || (pl.half_out[w] && ((uintptr_t)pl.half_out[w] & 7u) == 0),
+                    "adam_step_peer: half_out[%d] null or misaligned", w);
+    }
+    const AdamHyper h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, grad_scale, step);
+    const int64_t n = hi - lo;
+    long long blocks = (n / 4 + 255) / 256;
+    const long long cap = (long long)arc_sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    switch (world) {
+        case 1: launch_adam_peer<1>((unsigned)blocks, st, lo, hi, p, m, v, pl, world, h, step_dev); break;
+        case 2: launch_adam_peer<2>((unsigned)blocks, st, lo, hi, p, m, v, pl, world, h, step_dev); break;
+        case 4: launch_adam_peer<4>((unsigned)blocks, st, lo, hi, p, m, v, pl, world, h, step_dev); break;
+        case 8: launch_adam_peer<8>((unsigned)blocks, st, lo, hi, p, m, v, pl, world, h, step_dev); break;
+        default: launch_adam_peer<0>((unsigned)blocks, st, lo, hi, p, m, v, pl, world, h, step_dev); break;
+    }
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+}  // extern "C"

@@ -290,6 +290,31 @@ def adam_step(p, m, v, g, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_dec
               int(bool(zero_grad)), _lib.ptr(step_dev), _stream())
 
 
+class MlpAdamPack:
+    """Prepared argument block of arcb200_mlp_adam_pack: Adam + fp16 operand re-packing of up to 4 small networks in one
+    launch.  grads: per network either a tensor (local gradient) or a list of `world` raw device pointers (every rank's
+    gradient of that network, through peer memory), summed in list order."""
+
+    def __init__(self, specs, ps, ms, vs, grads, blobs):
+        n = len(specs)
+        self.n = n
+        self.keep = (ps, ms, vs, grads, blobs)
+        self.shapes = (C.c_int * (4 * n))(*[d for sp in specs for d in sp.dims()])
+        arr = lambda ts: (C.c_void_p * n)(*[t.data_ptr() for t in ts])
+        self.p, self.m, self.v, self.blobs = arr(ps), arr(ms), arr(vs), arr(blobs)
+        ptr_lists = [[g.data_ptr()] if torch.is_tensor(g) else [int(x) for x in g] for g in grads]
+        self.world = len(ptr_lists[0])
+        if any(len(x) != self.world for x in ptr_lists):
+            raise RuntimeError('every network needs the same number of gradient sources')
+        self.grads = (C.c_void_p * (n * self.world))(*[x for lst in ptr_lists for x in lst])
+
+    def step(self, step, lr, beta1=0.9, beta2=0.999, eps=1e-8, weight_decay=0.0, grad_scale=1.0, zero_grad=True,
+             step_dev=None):
+        _lib.call('arcb200_mlp_adam_pack', self.n, self.shapes, self.p, self.m, self.v, self.grads, self.world, self.blobs,
+                  int(step), float(lr), float(beta1), float(beta2), float(eps), float(weight_decay), float(grad_scale),
+                  int(bool(zero_grad)), _lib.ptr(step_dev), _stream())
+
+
 def huber_loss(rgb, target, delta=0.1, weight=3000.0, loss_sum=None, want_grad=True):
     """-> (loss_sum (1,) accumulated, g_rgb (R,3) | None)"""
     if loss_sum is None:

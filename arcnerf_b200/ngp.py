@@ -15,6 +15,7 @@ base_3d_model.py:233-254 -> ray_marching), with two structural differences that 
 All buffers are allocated once (sized by `capacity` samples and `max_rays` rays).
 """
 import math
+import os
 
 import numpy as np
 import torch
@@ -102,7 +103,11 @@ class SampleSet:
 
 class NGPPipeline:
     def __init__(self, max_rays=4096, capacity=1 << 19, device='cuda:0', seed=1337, grid_scale=1e-4, params=None,
-                 world_size=1, **overrides):
+                 world_size=1, rank=0, exchange='auto', **overrides):
+        """world_size > 1: data-parallel over the ranks of torch.distributed's default group.  exchange = 'peer' (the
+        gradient exchange fused into the Adam kernel over NVLink peer memory, csrc/peer.cu; ranks on one node),
+        'nccl' (one all-reduce of the flat gradient buffer, then the single-GPU Adam), or 'auto' (= 'peer' unless the
+        environment variable ARCB200_EXCHANGE says otherwise)."""
         cfg = dict(NGP_DEFAULTS)
         cfg.update(overrides)
         self.cfg = cfg
@@ -126,13 +131,37 @@ class NGPPipeline:
         self.rad_p = params['rad'].to(dev, torch.float32).contiguous()
         assert self.table.numel() == self.geom.n_params
         assert self.geo_p.numel() == self.geo_spec.n_params and self.rad_p.numel() == self.rad_spec.n_params
-        self.table_h = F.cast_f16(self.table)
+        nt, ng, nr = self.table.numel(), self.geo_p.numel(), self.rad_p.numel()
+        self.rank = int(rank)
+        if exchange == 'auto':
+            exchange = os.environ.get('ARCB200_EXCHANGE', 'peer')
+        self.exchange = exchange if self.world_size > 1 else 'none'
+        self.arena = None
+        if self.exchange == 'peer':
+            import torch.distributed as dist
+            from .peer import PeerArena, slice_bounds
+
+            def share(handle):
+                out = [None] * self.world_size
+                dist.all_gather_object(out, handle)
+                return out
+            self.rank = dist.get_rank()
+            self.arena = PeerArena({'grad': (nt + ng + nr) * 4, 'table_h': nt * 2}, dev, self.rank, self.world_size, share)
+            self.table_h = self.arena.local('table_h', torch.float16)
+            F.cast_f16(self.table, self.table_h)
+            self.slice = slice_bounds(nt, self.rank, self.world_size)
+            dist.barrier()                                  # every arena is mapped and initialised before anyone steps
+        else:
+            self.table_h = F.cast_f16(self.table)
         self.geo_blob = F.mlp_pack(self.geo_p, self.geo_spec)
         self.rad_blob = F.mlp_pack(self.rad_p, self.rad_spec)
         z = lambda t: torch.zeros_like(t)
         # one flat gradient buffer (hash table | geometry head | radiance head): a single collective moves it all
-        nt, ng, nr = self.table.numel(), self.geo_p.numel(), self.rad_p.numel()
-        self.g_all = torch.zeros(nt + ng + nr, dtype=torch.float32, device=dev)
+        if self.arena is not None:
+            self.g_all = self.arena.local('grad', torch.float32)
+            self.g_all.zero_()
+        else:
+            self.g_all = torch.zeros(nt + ng + nr, dtype=torch.float32, device=dev)
         self.g_table, self.g_geo, self.g_rad = self.g_all[:nt], self.g_all[nt:nt + ng], self.g_all[nt + ng:]
         self.m_table, self.v_table = z(self.table), z(self.table)
         self.m_geo, self.v_geo = z(self.geo_p), z(self.geo_p)
@@ -301,11 +330,12 @@ class NGPPipeline:
         self._run('adam_table', lambda: F.adam_step(self.table, self.m_table, self.v_table, self.g_table, self.step_count,
                                                     cfg['lr'], p_half=self.table_h, **kw))
 
+        if getattr(self, '_mlp_opt', None) is None:
+            self._mlp_opt = F.MlpAdamPack((self.geo_spec, self.rad_spec), (self.geo_p, self.rad_p), (self.m_geo, self.m_rad),
+                                          (self.v_geo, self.v_rad), (self.g_geo, self.g_rad), (self.geo_blob, self.rad_blob))
+
         def mlp_update():
-            F.adam_step(self.geo_p, self.m_geo, self.v_geo, self.g_geo, self.step_count, cfg['lr'], **kw)
-            F.adam_step(self.rad_p, self.m_rad, self.v_rad, self.g_rad, self.step_count, cfg['lr'], **kw)
-            F.mlp_pack(self.geo_p, self.geo_spec, self.geo_blob)
-            F.mlp_pack(self.rad_p, self.rad_spec, self.rad_blob)
+            self._mlp_opt.step(self.step_count, cfg['lr'], **kw)
         self._run('adam_mlp+pack', mlp_update)
 
     def train_step(self, rays_o, rays_d, target, bkg=None, optimize=True, next_rays=None):
@@ -327,12 +357,63 @@ class NGPPipeline:
         return self.loss
 
     def exchange_and_step(self):
-        """Data-parallel step: ONE sum over ranks of the flat gradient buffer (hash table + both heads, 48.8 MB; NCCL
-        over NVLink/NVSwitch), then Adam with grad_scale = 1/world - the mean gradient DDP would deliver
-        (common/trainer/basic_trainer.py:192-202)."""
+        """Data-parallel step on the mean gradient over ranks - what DDP + Adam deliver in the reference
+        (common/trainer/basic_trainer.py:192-202).
+        'peer': barrier, then one kernel per parameter vector that sums the peers' gradients over NVLink, applies Adam
+        and broadcasts the fp16 working copy (hash table: this rank's slice only; the two small heads: redundantly on
+        every rank, same summation order, so the replicas stay identical), barrier, clear the own gradients.
+        'nccl': ONE all-reduce of the flat gradient buffer (48.8 MB), then the single-GPU Adam kernels."""
+        if self.exchange != 'peer':
+            import torch.distributed as dist
+            self._run('all_reduce', lambda: dist.all_reduce(self.g_all))
+            self.optimizer_step()
+            return
+        from .peer import adam_step_peer
+        cfg, ar, W = self.cfg, self.arena, self.world_size
+        self.step_count += 1
+        _lib.call('arcb200_counter_add', self.step_dev.data_ptr(), 1, _lib.current_stream())
+        kw = dict(beta1=cfg['beta1'], beta2=cfg['beta2'], eps=cfg['eps'], weight_decay=cfg['weight_decay'],
+                  grad_scale=1.0 / W, step_dev=self.step_dev)
+        nt, ng = self.table.numel(), self.geo_p.numel()
+        if not hasattr(self, '_peer_ptrs'):
+            self._peer_ptrs = (ar.pointers('grad'), ar.pointers('grad', nt * 4), ar.pointers('grad', (nt + ng) * 4),
+                               ar.pointers('table_h'))
+        g_t, g_g, g_r, th = self._peer_ptrs
+        self._run('peer_barrier', ar.barrier)
+        lo, hi = self.slice
+        self._run('adam_table_peer', lambda: adam_step_peer(g_t, th, W, lo, hi, self.table, self.m_table, self.v_table,
+                                                            self.step_count, cfg['lr'], **kw))
+
+        if getattr(self, '_mlp_opt_peer', None) is None:
+            self._mlp_opt_peer = F.MlpAdamPack((self.geo_spec, self.rad_spec), (self.geo_p, self.rad_p),
+                                               (self.m_geo, self.m_rad), (self.v_geo, self.v_rad),
+                                               ([x for x in g_g], [x for x in g_r]), (self.geo_blob, self.rad_blob))
+
+        def mlp_update():
+            self._mlp_opt_peer.step(self.step_count, cfg['lr'], zero_grad=False, **kw)
+        self._run('adam_mlp+pack', mlp_update)
+
+        def close():
+            ar.barrier()
+            self.g_all.zero_()
+        self._run('peer_barrier+clear', close)
+
+    def gather_master_table(self):
+        """'peer' exchange keeps the fp32 master of the hash table sharded (each rank owns self.slice); this collects
+        the full fp32 table on every rank (checkpointing; not on the step path)."""
+        if self.exchange != 'peer':
+            return self.table
         import torch.distributed as dist
-        self._run('all_reduce', lambda: dist.all_reduce(self.g_all))
-        self.optimizer_step()
+        from .peer import slice_bounds
+        nt = self.table.numel()
+        per = slice_bounds(nt, 0, self.world_size)[1]
+        pad = torch.zeros(per, dtype=torch.float32, device=self.dev)
+        lo, hi = self.slice
+        pad[:hi - lo] = self.table[lo:hi]
+        outs = [torch.empty_like(pad) for _ in range(self.world_size)]
+        dist.all_gather(outs, pad)
+        self.table.copy_(torch.cat(outs)[:nt])
+        return self.table
 
     # ------------------------------------------------------------------------------------------ replayed step
     def _step_body(self, R, rays_d, target, bkg):
@@ -365,7 +446,7 @@ class NGPPipeline:
             o, d, t, b = self.static_in[1 - self.cur]
             d[:, 2] = 1.0
             self.train_step(o, d, t, b, optimize=False)
-        if self.world_size > 1:                          # communicator set-up must not happen inside the capture
+        if self.exchange == 'nccl':                      # communicator set-up must not happen inside the capture
             import torch.distributed as dist
             dist.all_reduce(self.g_all)
         torch.cuda.synchronize()
@@ -458,4 +539,5 @@ class NGPPipeline:
 
     # number of library kernels one train_step enqueues (for bench.py's gpu_launches)
     LAUNCHES_FORWARD = 1 + 4 + 1 + 1 + 1 + 1 + 1      # aabb, march(4), grid, geo mlp (+density), sh, rad mlp, composite
-    LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1 + 1 + 3 + 2   # huber, comp bwd, rad bwd, geo bwd, grid bwd, step counter, adam x3, pack x2
+    LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1 + 1 + 1 + 1   # huber, comp bwd, rad bwd, geo bwd, grid bwd, step counter, table adam, heads adam+pack
+    LAUNCHES_TRAIN_PEER = LAUNCHES_TRAIN + 2           # + two flag barriers (the gradient clear is a memset, not a kernel of ours)

@@ -1,0 +1,101 @@
+"""Peer-memory arena for the node-local data-parallel step (csrc/peer.cu; include/arcb200.h "data-parallel step over
+peer memory").  One process per GPU: each rank allocates one arena with the library's own cudaMalloc (so that the
+allocation is an IPC-exportable base pointer, independent of torch's caching allocator), the 64-byte handles travel
+through torch.distributed's host channel once at start-up, and every rank maps the others' arenas.  After that the
+step's gradient exchange is plain loads/stores over NVLink from our kernels; NCCL is not on the data path.
+
+Replaces DDP's gradient all-reduce + per-rank Adam of the reference (common/trainer/basic_trainer.py:192-202)."""
+import ctypes as C
+
+import torch
+
+from . import _lib
+
+FLAG_BYTES = 256          # 16 uint64 barrier slots + padding
+ALIGN = 256
+
+
+class _DevMem:
+    """exposes a raw device range to torch through __cuda_array_interface__ (no copy, no ownership)"""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = dict(shape=(nbytes,), typestr='|u1', data=(ptr, False), version=2)
+
+
+def _round_up(x, a):
+    return (x + a - 1) // a * a
+
+
+class PeerArena:
+    """layout (same on every rank): [flags | region_0 | region_1 | ...], regions given as {name: nbytes}"""
+
+    def __init__(self, regions, device, rank, world, exchange):
+        """exchange(bytes) -> list of every rank's bytes, in rank order (e.g. torch.distributed.all_gather_object)"""
+        self.rank, self.world, self.device = rank, world, torch.device(device)
+        self.offsets, off = {}, FLAG_BYTES
+        for name, nbytes in regions.items():
+            self.offsets[name] = (off, nbytes)
+            off = _round_up(off + nbytes, ALIGN)
+        self.nbytes = off
+        with torch.cuda.device(self.device):
+            base, handle = C.c_void_p(), (C.c_ubyte * 64)()
+            _lib.call('arcb200_peer_alloc', self.nbytes, C.byref(base), handle)
+            self.base = base.value
+            handles = exchange(bytes(handle))
+            assert len(handles) == world
+            self.bases = []
+            for w, h in enumerate(handles):
+                if w == rank:
+                    self.bases.append(self.base)
+                    continue
+                p = C.c_void_p()
+                _lib.call('arcb200_peer_open', (C.c_ubyte * 64).from_buffer_copy(h), C.byref(p))
+                self.bases.append(p.value)
+        self._bytes = torch.as_tensor(_DevMem(self.base, self.nbytes), device=self.device)
+        self.epoch = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._flag_ptrs = (C.c_void_p * world)(*self.bases)
+
+    def local(self, name, dtype):
+        """torch view of this rank's own region"""
+        off, nbytes = self.offsets[name]
+        return self._bytes[off:off + nbytes].view(dtype)
+
+    def pointers(self, name, byte_offset=0):
+        """ctypes array of every rank's pointer to the region (index = rank), as mapped in this process"""
+        off = self.offsets[name][0] + byte_offset
+        return (C.c_void_p * self.world)(*[b + off for b in self.bases])
+
+    def barrier(self, timeout_ms=0):
+        """flag barrier between the ranks, on the current stream (nothing blocks on the host)"""
+        _lib.call('arcb200_peer_barrier', self._flag_ptrs, self.world, self.rank, self.epoch.data_ptr(),
+                  self.status.data_ptr(), int(timeout_ms), _lib.current_stream())
+
+    def check(self):
+        """host-side check after a synchronisation: raises if a barrier wait timed out (a rank fell out of step)"""
+        if int(self.status.item()) != 0:
+            raise RuntimeError('peer barrier timed out on rank %d: the ranks are not executing the same steps' % self.rank)
+
+    def close(self):
+        if getattr(self, 'bases', None) is None:
+            return
+        torch.cuda.synchronize(self.device)
+        self._bytes = None
+        for w, b in enumerate(self.bases):
+            if w != self.rank:
+                _lib.call('arcb200_peer_close', b)
+        self.bases = None
+
+
+def adam_step_peer(grads, half_out, world, lo, hi, p, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8,
+                   weight_decay=0.0, grad_scale=1.0, step_dev=None):
+    """grads / half_out: ctypes pointer arrays from PeerArena.pointers (half_out may be None)"""
+    _lib.call('arcb200_adam_step_peer', grads, half_out, int(world), int(lo), int(hi), p.data_ptr(), m.data_ptr(),
+              v.data_ptr(), int(step), float(lr), float(beta1), float(beta2), float(eps), float(weight_decay),
+              float(grad_scale), _lib.ptr(step_dev), _lib.current_stream())
+
+
+def slice_bounds(n, rank, world, quantum=1024):
+    """[lo, hi) of rank's slice of an n-element vector; slices start on multiples of `quantum` elements"""
+    per = _round_up((n + world - 1) // world, quantum)
+    return min(n, rank * per), min(n, (rank + 1) * per)

@@ -108,6 +108,13 @@ def make_batches(n_batches, seed):
     return out
 
 
+EXCHANGE_NOTE = {
+    'none': 'single GPU',
+    'peer': 'fused into the Adam kernel: peer loads of the gradient slices + peer stores of the fp16 table over NVLink (csrc/peer.cu)',
+    'nccl': 'one NCCL all-reduce of the flat fp32 gradient buffer per step, then Adam on every rank',
+}
+
+
 # algorithmic work per unit (SURVEY.md §8d / DESIGN.md §4)
 def stage_work(name, n_samples, n_rays, n_table_params):
     if name == 'grid_fwd':
@@ -127,9 +134,9 @@ def stage_work(name, n_samples, n_rays, n_table_params):
     if name in ('mlp_rad_fwd',):
         return 'tensor', 14336.0 * n_samples
     if name == 'mlp_geo_bwd':
-        return 'tensor', 3 * 6144.0 * n_samples   # recomputed forward + dgrad + wgrad
+        return 'tensor', 2 * 6144.0 * n_samples   # dgrad + wgrad (hidden activations come saved from the forward)
     if name == 'mlp_rad_bwd':
-        return 'tensor', 3 * 14336.0 * n_samples
+        return 'tensor', 2 * 14336.0 * n_samples
     return None, 0.0
 
 
@@ -323,8 +330,8 @@ def main():
     render_ms = None
     if not args.no_render:
         del resident
-        rp = NGPPipeline(max_rays=32768, capacity=3 << 19, device=str(dev), world_size=world,
-                         params=dict(table=pipe.table, geo=pipe.geo_p, rad=pipe.rad_p))
+        rp = NGPPipeline(max_rays=32768, capacity=3 << 19, device=str(dev),
+                         params=dict(table=pipe.gather_master_table(), geo=pipe.geo_p, rad=pipe.rad_p))
         rp.set_occupancy(synth.occupancy_volume('lego'))
         o, d = synth.camera_rays(800, 800, synth.sphere_poses(1, seed=5)[0])
         n_all = o.shape[0]
@@ -381,9 +388,9 @@ def main():
             config=dict(workload=WORKLOAD, rays_per_step_per_gpu=N_RAYS, samples_per_step_per_gpu=n_samples,
                         l2='per-step working set (fp32 table + Adam moments + gradients + fp16 copy, 0.27 GB) exceeds the '
                            '126 MB L2 and every step draws a different ray batch; the Adam sweep evicts L2 between steps',
-                        parallelism='dp%d' % world),
+                        parallelism='dp%d' % world, gradient_exchange=EXCHANGE_NOTE[pipe.exchange]),
             e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=4, ms_per_step=ms_e2e / K, path=e2e_mode),
-            gpu_launches=NGPPipeline.LAUNCHES_TRAIN * K,
+            gpu_launches=(NGPPipeline.LAUNCHES_TRAIN_PEER if pipe.exchange == 'peer' else NGPPipeline.LAUNCHES_TRAIN) * K,
             clocks=clock_info, roofline=roofline, cpu_baseline=cpu_baseline,
             render_ms_800x800=render_ms,
         )

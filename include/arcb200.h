@@ -322,9 +322,43 @@ int arcb200_adam_step(float *p, float *m, float *v, float *g, void *p_half, int6
                       float beta1, float beta2, float eps, float weight_decay, float grad_scale, int zero_grad,
                       const int32_t *step_dev, void *stream);
 int arcb200_counter_add(int32_t *counter, int value, void *stream);
+/* Adam + fp16 operand re-packing of n_mlps (<= 4) small networks in ONE launch (per network: arcb200_adam_step followed
+ * by arcb200_mlp_pack_weights).  Reference: torch.optim.Adam on tcnn's `params` (common/trainer/optimizer.py) and tcnn's
+ * fp32->fp16 parameter cast at the next forward (tinycudann/modules.py:156).  shapes: host int[n_mlps*4] = in_dim,
+ * width, n_hidden, out_dim; p, m, v, blobs: host arrays of n_mlps device pointers; grads: host array of n_mlps*world
+ * device pointers, grads[j*world + w] = gradient source w of network j (world 1 = the local gradient; several = every
+ * rank's copy through peer memory), summed in index order and scaled by grad_scale; zero_grad clears source 0. */
+int arcb200_mlp_adam_pack(int n_mlps, const int *shapes, float *const *p, float *const *m, float *const *v,
+                          void *const *grads, int world, void *const *blobs, int step, float lr, float beta1,
+                          float beta2, float eps, float weight_decay, float grad_scale, int zero_grad,
+                          const int32_t *step_dev, void *stream);
 /* ImgLoss with HuberLoss (arcnerf/loss/img_loss.py:48-98): loss_sum[0] += weight * mean(huber), g_rgb = gradient. */
 int arcb200_huber_loss(const float *rgb, const float *target, float delta, float weight, float *g_rgb,
                        float *loss_sum, int64_t n_rays, void *stream);
+
+/* ---------------------------------------------------------------- data-parallel step over peer memory ----
+ * Replaces, for one node, what the reference gets from torch DDP + torch.optim.Adam: the bucketed all-reduce of the
+ * gradients hooked into backward (common/trainer/basic_trainer.py:192-202, set_model_to_ddp) followed by the same
+ * Adam step on every rank (common/trainer/optimizer.py).  One process per GPU; every rank allocates an arena with
+ * arcb200_peer_alloc, sends the 64-byte handle to the others (any host channel), and maps theirs with
+ * arcb200_peer_open.  Gradients, the fp16 working copy of the sharded parameters and the barrier flags live in the
+ * arena.  Per step: barrier, arcb200_adam_step_peer per parameter vector, barrier, then clear the own gradients. */
+int arcb200_peer_alloc(int64_t bytes, void **ptr_out, unsigned char *handle_out /* 64 bytes */);
+int arcb200_peer_open(const unsigned char *handle /* 64 bytes */, void **ptr_out);
+int arcb200_peer_close(void *ptr);
+int arcb200_peer_free(void *ptr);
+/* Flag barrier between ranks on `stream`: flags[w] = rank w's flag array (16 uint64, zeroed) as mapped in this
+ * process; epoch = private device uint64 (starts at 0); status = device int32 set to 1 if a wait exceeded
+ * timeout_ms (<= 0: 20 s) - the kernel then gives up instead of spinning forever. */
+int arcb200_peer_barrier(void *const *flags, int world, int rank, void *epoch, int32_t *status, int timeout_ms,
+                         void *stream);
+/* Adam over elements [lo, hi) (lo % 4 == 0) of a flat parameter vector on the gradient summed over grads[0..world)
+ * in rank order (peer loads), times grad_scale; the updated fp16 copy of the range is stored into half_out[0..world)
+ * (peer stores; half_out may be NULL).  p, m, v are this rank's full-length vectors.  Gradients are not cleared.
+ * Same arithmetic as arcb200_adam_step.  world <= 16. */
+int arcb200_adam_step_peer(const void *const *grads, void *const *half_out, int world, int64_t lo, int64_t hi,
+                           float *p, float *m, float *v, int step, float lr, float beta1, float beta2, float eps,
+                           float weight_decay, float grad_scale, const int32_t *step_dev, void *stream);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,164 @@
+"""Data-parallel step over peer memory (csrc/peer.cu): the fused exchange+Adam kernel against the plain
+sum-then-Adam path, and (on a box with >= 2 GPUs) two ranks stepping the NGP pipeline with exchange='peer' against
+exchange='nccl' (= DDP's all-reduce followed by Adam, common/trainer/basic_trainer.py:192-202)."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ptrs(tensors):
+    return (C.c_void_p * len(tensors))(*[t.data_ptr() for t in tensors])
+
+
+@pytest.mark.parametrize('world', [1, 2, 3, 4, 8])
+@pytest.mark.parametrize('n,lo,hi', [(4096, 0, 4096), (10007, 1024, 10007), (1 << 20, 4096 * 3, 4096 * 77 + 2)])
+def test_adam_step_peer_matches_sum_then_adam(world, n, lo, hi):
+    """all 'ranks' are buffers on one device: the kernel only sees pointers"""
+    from arcnerf_b200 import functional as F
+    from arcnerf_b200.peer import adam_step_peer
+    g = torch.Generator(device='cuda').manual_seed(world * 131 + n)
+    grads = [torch.randn(n, device='cuda', generator=g) for _ in range(world)]
+    p0 = torch.randn(n, device='cuda', generator=g)
+    m0 = torch.randn(n, device='cuda', generator=g) * 0.1
+    v0 = torch.rand(n, device='cuda', generator=g) * 0.01
+    halves = [torch.full((n,), 7.0, dtype=torch.float16, device='cuda') for _ in range(world)]
+    # reference: rank-ordered sum, then the single-GPU kernel on the range
+    gsum = grads[0].clone()
+    for w in range(1, world):
+        gsum += grads[w]
+    p_ref, m_ref, v_ref = p0.clone(), m0.clone(), v0.clone()
+    h_ref = torch.full((n,), 7.0, dtype=torch.float16, device='cuda')
+    F.adam_step(p_ref[lo:hi], m_ref[lo:hi], v_ref[lo:hi], gsum[lo:hi], 3, 1e-2, weight_decay=1e-3, p_half=h_ref[lo:hi],
+                grad_scale=1.0 / world, zero_grad=False)
+    p, m, v = p0.clone(), m0.clone(), v0.clone()
+    before = [x.clone() for x in grads]
+    adam_step_peer(_ptrs(grads), _ptrs(halves), world, lo, hi, p, m, v, 3, 1e-2, weight_decay=1e-3, grad_scale=1.0 / world)
+    torch.cuda.synchronize()
+    assert torch.equal(p, p_ref) and torch.equal(m, m_ref) and torch.equal(v, v_ref)
+    for h in halves:
+        assert torch.equal(h, h_ref)            # the slice in every copy, nothing outside the range
+    for a, b in zip(grads, before):
+        assert torch.equal(a, b)                # gradients are left for the peers
+
+
+@pytest.mark.parametrize('world', [1, 2, 8])
+def test_mlp_adam_pack_matches_separate_kernels(world):
+    """one launch for both heads == (sum of the gradient sources) -> adam_step -> mlp_pack per head, bit for bit"""
+    from arcnerf_b200 import functional as F
+    specs = [F.MlpSpec(32, 64, 1, 16, 'relu', 'none'), F.MlpSpec(32, 64, 2, 3, 'relu', 'sigmoid')]
+    g = torch.Generator(device='cuda').manual_seed(world)
+    ps = [torch.randn(sp.n_params, device='cuda', generator=g) * 0.3 for sp in specs]
+    ms = [torch.randn(sp.n_params, device='cuda', generator=g) * 0.1 for sp in specs]
+    vs = [torch.rand(sp.n_params, device='cuda', generator=g) * 0.01 for sp in specs]
+    grads = [[torch.randn(sp.n_params, device='cuda', generator=g) for _ in range(world)] for sp in specs]
+    ref = []
+    for j, sp in enumerate(specs):
+        gs = grads[j][0].clone()
+        for w in range(1, world):
+            gs += grads[j][w]
+        p, m, v = ps[j].clone(), ms[j].clone(), vs[j].clone()
+        F.adam_step(p, m, v, gs, 5, 1e-2, weight_decay=1e-4, grad_scale=1.0 / world)
+        ref.append((p, m, v, F.mlp_pack(p, sp)))
+    blobs = [torch.zeros(sp.blob_bytes, dtype=torch.uint8, device='cuda') for sp in specs]
+    srcs = [grads[j][0] if world == 1 else [t.data_ptr() for t in grads[j]] for j in range(2)]
+    opt = F.MlpAdamPack(specs, ps, ms, vs, srcs, blobs)
+    opt.step(5, 1e-2, weight_decay=1e-4, grad_scale=1.0 / world, zero_grad=(world == 1))
+    torch.cuda.synchronize()
+    for j in range(2):
+        assert torch.equal(ps[j], ref[j][0]) and torch.equal(ms[j], ref[j][1]) and torch.equal(vs[j], ref[j][2])
+        assert torch.equal(blobs[j], ref[j][3])
+        if world == 1:
+            assert float(grads[j][0].abs().max()) == 0.0
+
+
+def test_adam_step_peer_rejects_bad_arguments():
+    from arcnerf_b200.peer import adam_step_peer
+    x = torch.zeros(64, device='cuda')
+    with pytest.raises(RuntimeError, match='range'):
+        adam_step_peer(_ptrs([x]), None, 1, 2, 64, x, x, x, 1, 1e-3)
+    with pytest.raises(RuntimeError, match='world'):
+        adam_step_peer(_ptrs([x] * 17), None, 17, 0, 64, x, x, x, 1, 1e-3)
+
+
+def test_peer_barrier_single_rank_and_timeout():
+    """world 1 passes at once; a missing peer trips the timeout flag instead of spinning forever"""
+    from arcnerf_b200 import _lib
+    flags = torch.zeros(32, dtype=torch.int64, device='cuda')
+    epoch = torch.zeros(1, dtype=torch.int64, device='cuda')
+    status = torch.zeros(1, dtype=torch.int32, device='cuda')
+    fp = _ptrs([flags])
+    for _ in range(3):
+        _lib.call('arcb200_peer_barrier', fp, 1, 0, epoch.data_ptr(), status.data_ptr(), 100, _lib.current_stream())
+    torch.cuda.synchronize()
+    assert int(epoch) == 3 and int(flags[0]) == 3 and int(status) == 0
+    # two 'ranks' sharing one flag array layout, but rank 1 never arrives
+    other = torch.zeros(32, dtype=torch.int64, device='cuda')
+    fp2 = _ptrs([flags, other])
+    _lib.call('arcb200_peer_barrier', fp2, 2, 0, epoch.data_ptr(), status.data_ptr(), 50, _lib.current_stream())
+    torch.cuda.synchronize()
+    assert int(status) == 1 and int(other[0]) == 4
+
+
+def _two_rank_worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    os.environ['MASTER_ADDR'], os.environ['MASTER_PORT'] = '127.0.0.1', str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
+    from arcnerf_b200 import synth
+    from arcnerf_b200.ngp import NGP_DEFAULTS, NGPPipeline, init_params
+    params = init_params(dict(NGP_DEFAULTS), seed=3, grid_scale=0.5)
+    n = 1024
+    res = {}
+    for mode in ('nccl', 'peer'):
+        pipe = NGPPipeline(max_rays=n, capacity=1 << 17, device='cuda:%d' % rank, world_size=world, exchange=mode,
+                           params={k: v.clone() for k, v in params.items()}, lr=1e-2)
+        pipe.set_occupancy(synth.occupancy_volume('lego'))
+        losses = []
+        for step in range(4):
+            o, d = synth.train_ray_batch(n, seed=100 + step * world + rank)
+            t = np.random.RandomState(500 + step * world + rank).uniform(0, 1, (n, 3)).astype(np.float32)
+            dv = [torch.from_numpy(x).cuda() for x in (o, d, t)]
+            losses.append(float(pipe.train_step(*dv)))
+        torch.cuda.synchronize()
+        if pipe.arena is not None:
+            pipe.arena.check()
+        res[mode] = dict(table=pipe.gather_master_table().clone(), table_h=pipe.table_h.clone(), geo=pipe.geo_p.clone(),
+                         rad=pipe.rad_p.clone(), loss=losses)
+    ok = True
+    msg = []
+    for k in ('table', 'table_h', 'geo', 'rad'):
+        # the hash-grid backward accumulates with float atomics (run-to-run order differs), and Adam turns a sign flip
+        # of a near-zero gradient into a +-lr step: compare by the fraction of entries that moved apart
+        a, b = res['nccl'][k].float(), res['peer'][k].float()
+        far = float(((a - b).abs() > 2e-3).float().mean())
+        if far > 2e-3:
+            ok = False
+            msg.append('%s differs: fraction beyond 2e-3 = %.3e, max |d| %.3e' % (k, far, float((a - b).abs().max())))
+    if not np.allclose(res['nccl']['loss'], res['peer']['loss'], rtol=2e-3):
+        ok = False
+        msg.append('losses differ %s %s' % (res['nccl']['loss'], res['peer']['loss']))
+    # replicas agree across ranks
+    th = res['peer']['table_h'].float()
+    other = [torch.empty_like(th) for _ in range(world)]
+    dist.all_gather(other, th)
+    if not all(torch.equal(o, th) for o in other):
+        ok = False
+        msg.append('fp16 tables differ between ranks')
+    with open(os.path.join(out_dir, 'rank%d.txt' % rank), 'w') as f:
+        f.write('OK' if ok else 'FAIL ' + '; '.join(msg))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs on one node')
+def test_two_ranks_peer_exchange_matches_all_reduce(tmp_path):
+    import torch.multiprocessing as mp
+    port = 29500 + (os.getpid() % 400)
+    mp.spawn(_two_rank_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    for r in range(2):
+        assert open(tmp_path / ('rank%d.txt' % r)).read() == 'OK'
