@@ -23,6 +23,7 @@
 #include "tc05.cuh"
 #include "adam.cuh"
 #include <string.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -245,6 +246,7 @@ struct BwdExtra {
     int64_t ldx0;
     int x0_is_half;
     float clip;
+    int debug_skip;       // timing experiments only (ARCB200_MLP_DEBUG_SKIP): 1 no wgrad MMAs, 2 no dgrad MMAs, 4 no flush, 8 no dX store
 };
 
 // ---------------------------------------------------------------------------------------------- forward
@@ -667,16 +669,38 @@ static int set_smem(K kernel, size_t bytes) {
     return ARCB200_OK;
 }
 
-static unsigned mlp_grid(int64_t n, size_t smem_bytes, uint32_t tmem_cols) {
+// Persistent grid: resident CTAs per SM (registers and shared memory from the occupancy calculator, TMEM columns on
+// top) times the SM count; a grid larger than what is resident would run its last CTAs as a second, mostly idle wave.
+template <typename K>
+static unsigned mlp_grid(K kernel, int64_t n, size_t smem_bytes, uint32_t tmem_cols) {
     const int64_t tiles = (n + kRows - 1) / kRows;
-    int per_sm = (int)((227 * 1024) / (smem_bytes + 1024));
-    const int by_tmem = (int)(512 / tmem_cols);
-    if (per_sm > by_tmem) per_sm = by_tmem;
-    if (per_sm > 8) per_sm = 8;
-    if (per_sm < 1) per_sm = 1;
+    static thread_local size_t cached_smem = (size_t)-1;
+    static thread_local int cached_per_sm = 0;
+    if (cached_smem != smem_bytes) {
+        int per_sm = (int)((227 * 1024) / (smem_bytes + 1024));
+        cudaFuncAttributes fa;
+        if (cudaFuncGetAttributes(&fa, kernel) == cudaSuccess && fa.numRegs > 0) {
+            const int regs_per_cta = ((fa.numRegs + 7) / 8 * 8) * kRows;      // allocation granularity: 8 registers per thread
+            const int by_regs = 65536 / regs_per_cta;
+            if (per_sm > by_regs) per_sm = by_regs;
+        } else {
+            cudaGetLastError();
+        }
+        if (getenv("ARCB200_MLP_DEBUG")) fprintf(stderr, "[mlp_grid] smem %zu tmem %u regs %d -> %d CTAs/SM before the TMEM limit\n", smem_bytes, tmem_cols, fa.numRegs, per_sm);
+        const int by_tmem = (int)(512 / tmem_cols);
+        if (per_sm > by_tmem) per_sm = by_tmem;
+        if (per_sm > 8) per_sm = 8;
+        if (per_sm < 1) per_sm = 1;
+        cached_per_sm = per_sm;
+        cached_smem = smem_bytes;
+    }
+    int per_sm = cached_per_sm;
+    if (const char *e = getenv("ARCB200_MLP_CTAS_PER_SM")) { const int v = atoi(e); if (v > 0 && v < per_sm) per_sm = v; }   // experiments
     const int64_t cap = (int64_t)arc_sm_count() * per_sm;
     return (unsigned)(tiles < cap ? tiles : cap);
 }
+
+#include "mlp_bwd_v2.cuh"
 
 }  // namespace
 
@@ -797,7 +821,7 @@ int arcb200_mlp_fwd_ex(const void *X, int x_is_half, int64_t ldx, const void *bl
     do {                                                                                                    \
         int rc = set_smem(mlp_fwd_kernel<TI, TO, COLS>, smem);                                              \
         if (rc != ARCB200_OK) return rc;                                                                    \
-        const unsigned grid = mlp_grid(n, smem, COLS);                                                      \
+        const unsigned grid = mlp_grid(mlp_fwd_kernel<TI, TO, COLS>, n, smem, COLS);                         \
         mlp_fwd_kernel<TI, TO, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, (TO *)Y, ldy, io_vec, fex); \
     } while (0)
 #define LAUNCH_FWD(TI, TO) do { if (narrow) LAUNCH_FWD2(TI, TO, 64); else LAUNCH_FWD2(TI, TO, 128); } while (0)
@@ -846,6 +870,8 @@ int arcb200_mlp_bwd_ex(const void *X, int x_is_half, int64_t ldx, const void *bl
     BwdExtra bex;
     bex.act_saved = (const uint8_t *)act_saved; bex.y_saved = y_saved; bex.ldys = ldys; bex.y_is_half = ys_is_half;
     bex.g0 = g0; bex.x0 = x0; bex.ldx0 = ldx0; bex.x0_is_half = x0_is_half; bex.clip = clip;
+    bex.debug_skip = 0;
+    if (const char *e = getenv("ARCB200_MLP_DEBUG_SKIP")) bex.debug_skip = atoi(e);
     if (n == 0) return ARCB200_OK;
     MlpCfg c;
     ARC_REQUIRE(make_cfg(c, in_dim, width, n_hidden, out_dim, hidden_act, out_act) >= 0, "mlp_bwd: unsupported shape");
@@ -863,11 +889,25 @@ int arcb200_mlp_bwd_ex(const void *X, int x_is_half, int64_t ldx, const void *bl
     if (in_dim % 8 == 0 && ldx % 8 == 0 && ((uintptr_t)X & 15u) == 0) io_vec |= 1;
     if (dX && (ldgx * (dx_is_half ? 2 : 4)) % 16 == 0 && ((uintptr_t)dX & 15u) == 0) io_vec |= 2;
     if (ldy % 4 == 0 && ((uintptr_t)dY & 15u) == 0) io_vec |= 4;
+    if (bwd_v2_applies(c, x_is_half, dx_is_half, dX, io_vec, bex)) {
+        int nwg = 4;
+        if (const char *e = getenv("ARCB200_MLP_BWD_SLOTS")) nwg = atoi(e);
+        int rc;
+        switch (nwg) {
+            case 2: rc = launch_bwd_v2<2>(c, plan, n, n_dev, X, ldx, blob, dY, ldy, loss_scale, dX, ldgx, dW, io_vec, bex, st); break;
+            case 3: rc = launch_bwd_v2<3>(c, plan, n, n_dev, X, ldx, blob, dY, ldy, loss_scale, dX, ldgx, dW, io_vec, bex, st); break;
+            case 5: rc = launch_bwd_v2<5>(c, plan, n, n_dev, X, ldx, blob, dY, ldy, loss_scale, dX, ldgx, dW, io_vec, bex, st); break;
+            case 6: rc = launch_bwd_v2<6>(c, plan, n, n_dev, X, ldx, blob, dY, ldy, loss_scale, dX, ldgx, dW, io_vec, bex, st); break;
+            default: rc = launch_bwd_v2<4>(c, plan, n, n_dev, X, ldx, blob, dY, ldy, loss_scale, dX, ldgx, dW, io_vec, bex, st); break;
+        }
+        if (rc < 0) return rc;
+        if (rc == 0) { ARC_LAUNCH_CHECK(); return ARCB200_OK; }
+    }
 #define LAUNCH_BWD(TI, TG, COLS)                                                                            \
     do {                                                                                                    \
         int rc = set_smem(mlp_bwd_kernel<TI, TG, COLS>, smem);                                              \
         if (rc != ARCB200_OK) return rc;                                                                    \
-        const unsigned grid = mlp_grid(n, smem, COLS);                                                      \
+        const unsigned grid = mlp_grid(mlp_bwd_kernel<TI, TG, COLS>, n, smem, COLS);                         \
         mlp_bwd_kernel<TI, TG, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, plan, dY, \
                                                                ldy, loss_scale, (TG *)dX, ldgx, dW, io_vec, bex); \
     } while (0)

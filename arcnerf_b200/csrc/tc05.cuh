@@ -103,6 +103,19 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t *mbar, uint32_t parity) {
         : "=r"(ok) : "r"(smem_u32(mbar)), "r"(parity) : "memory");
     return ok != 0;
 }
+// non-blocking probe (try_wait may suspend the thread for a while when the phase is not complete; a thread that polls
+// SEVERAL barriers must not sit in one of them)
+__device__ __forceinline__ bool mbar_test_wait(uint64_t *mbar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t"
+        ".reg .pred p;\n\t"
+        "mbarrier.test_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t"
+        "}\n"
+        : "=r"(ok) : "r"(smem_u32(mbar)), "r"(parity) : "memory");
+    return ok != 0;
+}
 __device__ __forceinline__ void mbar_wait(uint64_t *mbar, uint32_t parity) {
     while (!mbar_try_wait(mbar, parity)) { }
 }
