@@ -63,6 +63,7 @@ _SIGS = {
     'arcb200_geo_head_grad': [P, I, L, P, F, P, I, L, I, P, L, P, P],
     'arcb200_adam_step': [P, P, P, P, P, L, I, F, F, F, F, F, F, I, P, P],
     'arcb200_counter_add': [P, I, P],
+    'arcb200_fill_f32': [P, F, L, P],
     'arcb200_huber_loss': [P, P, F, F, P, P, L, P],
     'arcb200_mlp_adam_pack': [I, P, P, P, P, P, I, P, I, F, F, F, F, F, F, I, P, P],
     'arcb200_peer_alloc': [L, P, P],

@@ -1,5 +1,6 @@
 // libarcb200: process-level pieces of the C ABI (error text, version, device queries, pcg32 host helpers).
 #include "common.cuh"
+#include <stdlib.h>
 #include "pcg32.cuh"
 #include <stdarg.h>
 #include <string.h>
@@ -23,6 +24,15 @@ int arc_sm_count() {
         sm[dev] = v;
     }
     return sm[dev];
+}
+
+bool arc_pdl_enabled() {
+    static int on = -1;
+    if (on < 0) {
+        const char *e = getenv("ARCB200_PDL");
+        on = (e && e[0] == '0') ? 0 : 1;
+    }
+    return on != 0;
 }
 
 extern "C" {

@@ -47,3 +47,35 @@ static inline unsigned int arc_blocks(long long n, int threads) {
 int arc_sm_count();
 
 #define ARC_FULL_MASK 0xffffffffu
+
+// ---- programmatic dependent launch (PDL) --------------------------------------------------------------
+// Every kernel of the library is launched with cudaLaunchAttributeProgrammaticStreamSerialization and begins with
+// arc_pdl_sync(): wait until the preceding kernel of the stream has completed (griddepcontrol.wait), then allow the
+// following kernel to be scheduled (griddepcontrol.launch_dependents).  The next kernel's CTAs are placed on the SMs as
+// this kernel's CTAs drain and sit in their own wait, so launch latency and CTA start-up no longer lie between two
+// kernels of a step.  Because a kernel signals only AFTER its own wait, anything older than the direct predecessor is
+// complete by the time a kernel starts.  Without the launch attribute both instructions are no-ops.
+// ARCB200_PDL=0 in the environment turns the attribute off (plain stream order).
+#ifdef __CUDACC__
+__device__ __forceinline__ void arc_pdl_sync() {
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+#endif
+
+bool arc_pdl_enabled();   // abi.cu
+
+template <typename... KArgs, typename... Args>
+static inline void arc_launch(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args &&...args) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = arc_pdl_enabled() ? 1 : 0;
+    cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);   // errors surface through ARC_LAUNCH_CHECK()
+}

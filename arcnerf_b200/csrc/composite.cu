@@ -99,6 +99,7 @@ composite_fwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
                      int add_inf_z, int white_bkg, const float *__restrict__ bkg, int bkg_per_ray,
                      float *__restrict__ rgb, float *__restrict__ depth, float *__restrict__ acc_out,
                      float *__restrict__ w_out, float *__restrict__ trans_out, float *__restrict__ alpha_out) {
+    arc_pdl_sync();
     const uint32_t ray = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31u;
     if (ray >= n_rays) return;
@@ -172,6 +173,7 @@ composite_bwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
                      const float *__restrict__ g_rgb, const float *__restrict__ g_depth,
                      const float *__restrict__ g_acc, const float *__restrict__ g_w,
                      float *__restrict__ d_geo, float *__restrict__ d_rad) {
+    arc_pdl_sync();
     const uint32_t ray = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31u;
     if (ray >= n_rays) return;
@@ -281,6 +283,7 @@ composite_bwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
 __global__ void sdf_to_alpha_kernel(int64_t n, int32_t p, const float *__restrict__ sdf,
                                     const float *__restrict__ zvals, const float *__restrict__ slope,
                                     const float *__restrict__ s_dev, float s_host, int clip, float *__restrict__ alpha) {
+    arc_pdl_sync();
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n) return;
     const float sc = s_dev ? __ldg(s_dev) : s_host;
@@ -301,6 +304,7 @@ __global__ void sdf_to_alpha_bwd_kernel(int64_t n, int32_t p, const float *__res
                                         const float *__restrict__ s_dev, float s_host, int clip,
                                         const float *__restrict__ g_alpha, float *__restrict__ d_sdf,
                                         float *__restrict__ d_slope, float *__restrict__ d_s) {
+    arc_pdl_sync();
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     float ds = 0.f;
     if (k < n) {
@@ -336,6 +340,7 @@ __global__ void sdf_to_alpha_bwd_kernel(int64_t n, int32_t p, const float *__res
 __global__ void sample_cdf_kernel(int64_t total, int32_t nb, int32_t ns, const float *__restrict__ bins,
                                   const float *__restrict__ cdf, const float *__restrict__ u, int u_per_ray,
                                   float eps, float *__restrict__ out) {
+    arc_pdl_sync();
     const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= total) return;
     const int64_t r = k / ns;
@@ -378,11 +383,11 @@ int arcb200_composite_fwd(const int32_t *offsets, int dense_p, int64_t capacity,
     const unsigned blocks = arc_blocks(n_rays * 32, 256);
     cudaStream_t st = (cudaStream_t)stream;
     if (is_alpha)
-        composite_fwd_kernel<true><<<blocks, 256, 0, st>>>((uint32_t)n_rays, offsets, dense_p, capacity, pmax_dev, geo, rad,
+        arc_launch(composite_fwd_kernel<true>, blocks, 256, 0, st, (uint32_t)n_rays, offsets, dense_p, capacity, pmax_dev, geo, rad,
                                                            t, noise, add_inf_z, white_bkg, bkg, bkg_per_ray, rgb, depth,
                                                            acc, w_out, trans_out, alpha_out);
     else
-        composite_fwd_kernel<false><<<blocks, 256, 0, st>>>((uint32_t)n_rays, offsets, dense_p, capacity, pmax_dev, geo, rad,
+        arc_launch(composite_fwd_kernel<false>, blocks, 256, 0, st, (uint32_t)n_rays, offsets, dense_p, capacity, pmax_dev, geo, rad,
                                                             t, noise, add_inf_z, white_bkg, bkg, bkg_per_ray, rgb, depth,
                                                             acc, w_out, trans_out, alpha_out);
     ARC_LAUNCH_CHECK();
@@ -409,11 +414,11 @@ int arcb200_composite_bwd(const int32_t *offsets, int dense_p, int64_t capacity,
     const unsigned blocks = arc_blocks(n_rays * 32, 256);
     cudaStream_t st = (cudaStream_t)stream;
     if (is_alpha)
-        composite_bwd_kernel<true><<<blocks, 256, 0, st>>>((uint32_t)n_rays, offsets, dense_p, capacity, pmax_dev, geo, rad,
+        arc_launch(composite_bwd_kernel<true>, blocks, 256, 0, st, (uint32_t)n_rays, offsets, dense_p, capacity, pmax_dev, geo, rad,
                                                            t, noise, add_inf_z, white_bkg, bkg, bkg_per_ray, g_rgb,
                                                            g_depth, g_acc, g_w, d_geo, d_rad);
     else
-        composite_bwd_kernel<false><<<blocks, 256, 0, st>>>((uint32_t)n_rays, offsets, dense_p, capacity, pmax_dev, geo, rad,
+        arc_launch(composite_bwd_kernel<false>, blocks, 256, 0, st, (uint32_t)n_rays, offsets, dense_p, capacity, pmax_dev, geo, rad,
                                                             t, noise, add_inf_z, white_bkg, bkg, bkg_per_ray, g_rgb,
                                                             g_depth, g_acc, g_w, d_geo, d_rad);
     ARC_LAUNCH_CHECK();
@@ -428,7 +433,7 @@ int arcb200_sdf_to_alpha(const float *sdf, const float *zvals, const float *slop
     const int64_t n = n_rays * p;
     if (n == 0) return ARCB200_OK;
     ARC_REQUIRE(sdf && zvals && slope && alpha, "sdf_to_alpha: null pointer");
-    sdf_to_alpha_kernel<<<arc_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>(n, p, sdf, zvals, slope, s_dev, s_host, clip, alpha);
+    arc_launch(sdf_to_alpha_kernel, arc_blocks(n, 256), 256, 0, (cudaStream_t)stream, n, p, sdf, zvals, slope, s_dev, s_host, clip, alpha);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
@@ -441,7 +446,7 @@ int arcb200_sdf_to_alpha_bwd(const float *sdf, const float *zvals, const float *
     const int64_t n = n_rays * p;
     if (n == 0) return ARCB200_OK;
     ARC_REQUIRE(sdf && zvals && slope && g_alpha, "sdf_to_alpha_bwd: null pointer");
-    sdf_to_alpha_bwd_kernel<<<arc_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>(n, p, sdf, zvals, slope, s_dev, s_host, clip,
+    arc_launch(sdf_to_alpha_bwd_kernel, arc_blocks(n, 256), 256, 0, (cudaStream_t)stream, n, p, sdf, zvals, slope, s_dev, s_host, clip,
                                                                               g_alpha, d_sdf, d_slope, d_s);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
@@ -455,7 +460,7 @@ int arcb200_sample_cdf(const float *bins, const float *cdf, const float *u, int 
     const int64_t total = n_rays * n_sample;
     if (total == 0) return ARCB200_OK;
     ARC_REQUIRE(bins && cdf && u && out, "sample_cdf: null pointer");
-    sample_cdf_kernel<<<arc_blocks(total, 256), 256, 0, (cudaStream_t)stream>>>(total, n_bins, n_sample, bins, cdf, u,
+    arc_launch(sample_cdf_kernel, arc_blocks(total, 256), 256, 0, (cudaStream_t)stream, total, n_bins, n_sample, bins, cdf, u,
                                                                              u_per_ray, eps, out);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;

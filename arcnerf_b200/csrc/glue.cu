@@ -21,6 +21,7 @@ template <> __device__ __forceinline__ float ldv<__half>(const __half *p) { retu
 template <typename T>
 __global__ void trunc_exp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const T *__restrict__ x, int64_t ldx,
                                      float *__restrict__ y) {
+    arc_pdl_sync();
     if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
         y[i] = expf(ldv<T>(x + i * ldx));
@@ -29,6 +30,7 @@ __global__ void trunc_exp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_de
 template <typename T>
 __global__ void trunc_exp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const T *__restrict__ x, int64_t ldx,
                                      const float *__restrict__ g, float clip, float *__restrict__ gx) {
+    arc_pdl_sync();
     if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
         gx[i] = g[i] * expf(fminf(fmaxf(ldv<T>(x + i * ldx), -clip), clip));
@@ -39,6 +41,7 @@ template <typename TX, typename TF>
 __global__ void geo_head_grad_kernel(int64_t n, const int32_t *__restrict__ n_dev, int width, const TX *__restrict__ x0,
                                      int64_t ldx, const float *__restrict__ g_sigma, float clip,
                                      const TF *__restrict__ d_feat, int64_t ldf, float *__restrict__ dY) {
+    arc_pdl_sync();
     if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < n * width; k += (int64_t)gridDim.x * blockDim.x) {
         const int64_t i = k / width;
@@ -59,8 +62,8 @@ int arcb200_trunc_exp_fwd(const void *x, int x_is_half, int64_t ldx, float *y, i
     ARC_REQUIRE(n >= 0, "trunc_exp_fwd: negative n");
     if (n == 0) return ARCB200_OK;
     ARC_REQUIRE(x && y && ldx >= 1, "trunc_exp_fwd: null pointer / bad stride");
-    if (x_is_half) trunc_exp_fwd_kernel<__half><<<stride_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>(n, n_dev, (const __half *)x, ldx, y);
-    else trunc_exp_fwd_kernel<float><<<stride_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>(n, n_dev, (const float *)x, ldx, y);
+    if (x_is_half) arc_launch(trunc_exp_fwd_kernel<__half>, stride_blocks(n, 256), 256, 0, (cudaStream_t)stream, n, n_dev, (const __half *)x, ldx, y);
+    else arc_launch(trunc_exp_fwd_kernel<float>, stride_blocks(n, 256), 256, 0, (cudaStream_t)stream, n, n_dev, (const float *)x, ldx, y);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
@@ -71,8 +74,8 @@ int arcb200_trunc_exp_bwd(const void *x, int x_is_half, int64_t ldx, const float
     ARC_REQUIRE(n >= 0, "trunc_exp_bwd: negative n");
     if (n == 0) return ARCB200_OK;
     ARC_REQUIRE(x && g && gx && ldx >= 1, "trunc_exp_bwd: null pointer / bad stride");
-    if (x_is_half) trunc_exp_bwd_kernel<__half><<<stride_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>(n, n_dev, (const __half *)x, ldx, g, clip, gx);
-    else trunc_exp_bwd_kernel<float><<<stride_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>(n, n_dev, (const float *)x, ldx, g, clip, gx);
+    if (x_is_half) arc_launch(trunc_exp_bwd_kernel<__half>, stride_blocks(n, 256), 256, 0, (cudaStream_t)stream, n, n_dev, (const __half *)x, ldx, g, clip, gx);
+    else arc_launch(trunc_exp_bwd_kernel<float>, stride_blocks(n, 256), 256, 0, (cudaStream_t)stream, n, n_dev, (const float *)x, ldx, g, clip, gx);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
@@ -88,7 +91,7 @@ int arcb200_geo_head_grad(const void *x0, int x_is_half, int64_t ldx, const floa
     ARC_REQUIRE(x0 && g_sigma && dY, "geo_head_grad: null pointer");
     const unsigned blocks = stride_blocks(n * width, 256);
     cudaStream_t st = (cudaStream_t)stream;
-#define GO(TX, TF) geo_head_grad_kernel<TX, TF><<<blocks, 256, 0, st>>>(n, n_dev, width, (const TX *)x0, ldx, g_sigma, clip, (const TF *)d_feat, ldf, dY)
+#define GO(TX, TF) arc_launch(geo_head_grad_kernel<TX, TF>, blocks, 256, 0, st, n, n_dev, width, (const TX *)x0, ldx, g_sigma, clip, (const TF *)d_feat, ldf, dY)
     if (x_is_half) { if (f_is_half) GO(__half, __half); else GO(__half, float); }
     else { if (f_is_half) GO(float, __half); else GO(float, float); }
 #undef GO

@@ -95,6 +95,7 @@ template <int F, bool DYDX>
 __global__ void __launch_bounds__(kTileSamples * kFwdWarps)
 grid_fwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__restrict__ xyz,
                 const __half *__restrict__ table, GridGeom geom, __half *__restrict__ out, float *__restrict__ dy_dx) {
+    arc_pdl_sync();
     extern __shared__ __half tile[];   // [32][L*F + 2]
     if (n_dev) n = min(n, (uint32_t)max(*n_dev, 0));
     const uint32_t L = geom.n_levels;
@@ -193,6 +194,7 @@ __global__ void __launch_bounds__(kTileSamples * kFwdWarps)
 grid_bwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__restrict__ xyz,
                 const T *__restrict__ dL_dy, GridGeom geom, float *__restrict__ grad_table, float gscale,
                 const float *__restrict__ v_in) {
+    arc_pdl_sync();
     extern __shared__ float gtile[];   // [32][L*F + 1]
     if (n_dev) n = min(n, (uint32_t)max(*n_dev, 0));
     const uint32_t L = geom.n_levels;
@@ -245,6 +247,7 @@ grid_bwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__re
 template <typename T>
 __global__ void grid_bwd_input_kernel(uint32_t n, uint32_t row, const T *__restrict__ dL_dy,
                                       const float *__restrict__ dy_dx, float gscale, float *__restrict__ dL_dx) {
+    arc_pdl_sync();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     float ax = 0.f, ay = 0.f, az = 0.f;
@@ -267,6 +270,7 @@ __global__ void grid_bwd_bwd_input_kernel(uint32_t n, const float *__restrict__ 
                                           GridGeom geom, const T *__restrict__ dL_dy, float gscale,
                                           const float *__restrict__ v_in, float *__restrict__ d_dLdy,
                                           float *__restrict__ d_x) {
+    arc_pdl_sync();
     const uint32_t L = geom.n_levels;
     const uint32_t row = L * F;
     const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
@@ -318,6 +322,7 @@ __global__ void grid_bwd_bwd_input_kernel(uint32_t n, const float *__restrict__ 
 }
 
 __global__ void cast_f32_f16_kernel(size_t n, const float *__restrict__ src, __half *__restrict__ dst) {
+    arc_pdl_sync();
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     const size_t n4 = n / 4;
     for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n4; k += stride) {
@@ -400,7 +405,7 @@ int arcb200_cast_f32_to_f16(const float *src, void *dst_half, int64_t n, void *s
     const long long cap = (long long)arc_sm_count() * 16;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    cast_f32_f16_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((size_t)n, src, (__half *)dst_half);
+    arc_launch(cast_f32_f16_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, (size_t)n, src, (__half *)dst_half);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
@@ -432,9 +437,9 @@ int arcb200_grid_fwd(const float *xyz, const void *table_half, int n_levels, int
     const size_t smem = (size_t)kTileSamples * (n_levels * n_features + 2) * sizeof(__half);
     cudaStream_t st = (cudaStream_t)stream;
     GRID_DISPATCH_F(n_features,
-        if (dy_dx) grid_fwd_kernel<F, true><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(
+        if (dy_dx) arc_launch(grid_fwd_kernel<F, true>, blocks, kTileSamples * kFwdWarps, smem, st, 
             (uint32_t)n, n_dev, xyz, (const __half *)table_half, geom, (__half *)out_half, dy_dx);
-        else grid_fwd_kernel<F, false><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(
+        else arc_launch(grid_fwd_kernel<F, false>, blocks, kTileSamples * kFwdWarps, smem, st, 
             (uint32_t)n, n_dev, xyz, (const __half *)table_half, geom, (__half *)out_half, nullptr));
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
@@ -455,9 +460,9 @@ int arcb200_grid_bwd(const float *xyz, const void *dL_dy, int dy_is_half, float 
     const size_t smem = (size_t)kTileSamples * (n_levels * n_features + 1) * sizeof(float);
     cudaStream_t st = (cudaStream_t)stream;
     GRID_DISPATCH_F(n_features,
-        if (dy_is_half) grid_bwd_kernel<F, __half, false><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(
+        if (dy_is_half) arc_launch(grid_bwd_kernel<F, __half, false>, blocks, kTileSamples * kFwdWarps, smem, st, 
             (uint32_t)n, n_dev, xyz, (const __half *)dL_dy, geom, grad_table, gscale, nullptr);
-        else grid_bwd_kernel<F, float, false><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(
+        else arc_launch(grid_bwd_kernel<F, float, false>, blocks, kTileSamples * kFwdWarps, smem, st, 
             (uint32_t)n, n_dev, xyz, (const float *)dL_dy, geom, grad_table, gscale, nullptr));
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
@@ -470,9 +475,9 @@ int arcb200_grid_bwd_input(const void *dL_dy, int dy_is_half, float gscale, cons
     if (n == 0) return ARCB200_OK;
     ARC_REQUIRE(dL_dy && dy_dx && dL_dx && n_levels > 0 && n_features > 0, "grid_bwd_input: null/invalid argument");
     const uint32_t row = (uint32_t)(n_levels * n_features);
-    if (dy_is_half) grid_bwd_input_kernel<__half><<<arc_blocks(n, 128), 128, 0, (cudaStream_t)stream>>>(
+    if (dy_is_half) arc_launch(grid_bwd_input_kernel<__half>, arc_blocks(n, 128), 128, 0, (cudaStream_t)stream, 
         (uint32_t)n, row, (const __half *)dL_dy, dy_dx, gscale, dL_dx);
-    else grid_bwd_input_kernel<float><<<arc_blocks(n, 128), 128, 0, (cudaStream_t)stream>>>(
+    else arc_launch(grid_bwd_input_kernel<float>, arc_blocks(n, 128), 128, 0, (cudaStream_t)stream, 
         (uint32_t)n, row, (const float *)dL_dy, dy_dx, gscale, dL_dx);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
@@ -497,9 +502,9 @@ int arcb200_grid_bwd_bwd_input(const float *xyz, const void *table_half, const v
         const unsigned blocks = tile_blocks(n);
         const size_t smem = (size_t)kTileSamples * (n_levels * n_features + 1) * sizeof(float);
         GRID_DISPATCH_F(n_features,
-            if (dy_is_half) grid_bwd_kernel<F, __half, true><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(
+            if (dy_is_half) arc_launch(grid_bwd_kernel<F, __half, true>, blocks, kTileSamples * kFwdWarps, smem, st, 
                 (uint32_t)n, nullptr, xyz, (const __half *)dL_dy, geom, grad_table, gscale, v);
-            else grid_bwd_kernel<F, float, true><<<blocks, kTileSamples * kFwdWarps, smem, st>>>(
+            else arc_launch(grid_bwd_kernel<F, float, true>, blocks, kTileSamples * kFwdWarps, smem, st, 
                 (uint32_t)n, nullptr, xyz, (const float *)dL_dy, geom, grad_table, gscale, v));
         ARC_LAUNCH_CHECK();
     }
@@ -507,9 +512,9 @@ int arcb200_grid_bwd_bwd_input(const float *xyz, const void *table_half, const v
         if (d_x) ARC_CUDA(cudaMemsetAsync(d_x, 0, (size_t)n * 3 * sizeof(float), st));
         const unsigned blocks = arc_blocks(n * n_levels, 128);
         GRID_DISPATCH_F(n_features,
-            if (dy_is_half) grid_bwd_bwd_input_kernel<F, __half><<<blocks, 128, 0, st>>>(
+            if (dy_is_half) arc_launch(grid_bwd_bwd_input_kernel<F, __half>, blocks, 128, 0, st, 
                 (uint32_t)n, xyz, (const __half *)table_half, geom, (const __half *)dL_dy, gscale, v, d_dLdy, d_x);
-            else grid_bwd_bwd_input_kernel<F, float><<<blocks, 128, 0, st>>>(
+            else arc_launch(grid_bwd_bwd_input_kernel<F, float>, blocks, 128, 0, st, 
                 (uint32_t)n, xyz, (const __half *)table_half, geom, (const float *)dL_dy, gscale, v, d_dLdy, d_x));
         ARC_LAUNCH_CHECK();
     }

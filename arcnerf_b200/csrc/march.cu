@@ -33,6 +33,7 @@ __global__ void aabb_kernel(uint32_t n_rays, uint32_t n_v, const float *__restri
                             const float *__restrict__ rays_d, const float *__restrict__ aabb,
                             float *__restrict__ near, float *__restrict__ far, float *__restrict__ pts,
                             uint8_t *__restrict__ mask) {
+    arc_pdl_sync();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_rays * n_v) return;
     const uint32_t r = i / n_v, v = i % n_v;
@@ -53,6 +54,7 @@ __global__ void aabb_kernel(uint32_t n_rays, uint32_t n_v, const float *__restri
 
 __global__ void occ_points_kernel(uint32_t n, const float *__restrict__ xyz, const uint8_t *__restrict__ vol,
                                   const float *__restrict__ aabb, uint32_t n_grid, uint8_t *__restrict__ out) {
+    arc_pdl_sync();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     const Box box = load_box(aabb);
@@ -71,6 +73,7 @@ march_warp_kernel(uint32_t n_rays, const float *__restrict__ rays_o, const float
                   const uint8_t *__restrict__ field, uint32_t n_grid, uint32_t n_pts, float dt,
                   float near_distance, uint64_t rng_state, uint64_t rng_inc, float *__restrict__ zvals,
                   uint8_t *__restrict__ mask, int32_t *__restrict__ counts, int fill_tail) {
+    arc_pdl_sync();
     const uint32_t ray = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31u;
     if (ray >= n_rays) return;
@@ -223,6 +226,7 @@ __global__ void march_multivol_kernel(uint32_t n_rays, const float *__restrict__
                                       uint32_t n_pts, float cone, float smin, float smax, float near_distance,
                                       int inclusive, uint64_t rng_state, uint64_t rng_inc,
                                       float *__restrict__ zvals, uint8_t *__restrict__ mask) {
+    arc_pdl_sync();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_rays) return;
     const Box inner = load_box(min_aabb), outer = load_box(aabb);
@@ -267,6 +271,7 @@ constexpr int kScanTile = 1024;
 __global__ void __launch_bounds__(kScanTile)
 scan_tiles_kernel(uint32_t n, const int32_t *__restrict__ counts, int32_t *__restrict__ offsets,
                   int32_t *__restrict__ tile_sums, int32_t *__restrict__ max_count) {
+    arc_pdl_sync();
     __shared__ int32_t warp_sums[32];
     const uint32_t i = blockIdx.x * kScanTile + threadIdx.x;
     const uint32_t lane = threadIdx.x & 31u, w = threadIdx.x >> 5;
@@ -300,6 +305,7 @@ scan_tiles_kernel(uint32_t n, const int32_t *__restrict__ counts, int32_t *__res
 
 __global__ void __launch_bounds__(1024)
 scan_tile_sums_kernel(uint32_t n_tiles, int32_t *__restrict__ tile_sums, int32_t *__restrict__ total) {
+    arc_pdl_sync();
     // single block: exclusive scan of tile_sums in place, total to *total
     __shared__ int32_t warp_sums[32];
     __shared__ int32_t carry_s;
@@ -346,6 +352,7 @@ pack_samples_kernel(uint32_t n_rays, uint32_t n_pts, const float *__restrict__ r
                     const int32_t *__restrict__ tile_prefix, const int32_t *__restrict__ total,
                     int64_t capacity, float *__restrict__ t_out, float *__restrict__ xyz_out,
                     int32_t *__restrict__ ray_id_out, const float *__restrict__ aabb, float *__restrict__ unit_out) {
+    arc_pdl_sync();
     const uint32_t ray = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31u;
     if (ray > n_rays) return;
@@ -387,7 +394,7 @@ int arcb200_aabb_intersection(const float *rays_o, const float *rays_d, const fl
     if (n_rays * n_v == 0) return ARCB200_OK;
     ARC_REQUIRE(rays_o && rays_d && aabb && near && far && mask, "aabb_intersection: null pointer");
     ARC_REQUIRE(n_rays * n_v < (1ll << 32), "aabb_intersection: n_rays*n_v must fit 32 bits");
-    aabb_kernel<<<arc_blocks(n_rays * n_v, 256), 256, 0, (cudaStream_t)stream>>>(
+    arc_launch(aabb_kernel, arc_blocks(n_rays * n_v, 256), 256, 0, (cudaStream_t)stream, 
         (uint32_t)n_rays, (uint32_t)n_v, rays_o, rays_d, aabb, near, far, pts, mask);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
@@ -398,7 +405,7 @@ int arcb200_check_pts_in_occ_voxel(const float *xyz, const uint8_t *bitfield, co
     ARC_REQUIRE(n >= 0 && n < (1ll << 32), "check_pts_in_occ_voxel: bad n");
     if (n == 0) return ARCB200_OK;
     ARC_REQUIRE(xyz && bitfield && aabb && out && n_grid > 0, "check_pts_in_occ_voxel: null/invalid argument");
-    occ_points_kernel<<<arc_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>((uint32_t)n, xyz, bitfield,
+    arc_launch(occ_points_kernel, arc_blocks(n, 256), 256, 0, (cudaStream_t)stream, (uint32_t)n, xyz, bitfield,
                                                                           aabb, (uint32_t)n_grid, out);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
@@ -414,11 +421,11 @@ static int launch_march(int bit, const float *rays_o, const float *rays_d, const
     ARC_REQUIRE(n_pts > 0 && n_grid > 0 && dt > 0.0f, "sparse_volume_sampling: n_pts, n_grid and dt must be positive");
     const unsigned int blocks = arc_blocks(n_rays * 32, 256);
     if (bit)
-        march_warp_kernel<1><<<blocks, 256, 0, (cudaStream_t)stream>>>(
+        arc_launch(march_warp_kernel<1>, blocks, 256, 0, (cudaStream_t)stream, 
             (uint32_t)n_rays, rays_o, rays_d, near, far, aabb, field, (uint32_t)n_grid, (uint32_t)n_pts, dt,
             near_distance, rng_state, rng_inc, zvals, mask, counts, fill_tail);
     else
-        march_warp_kernel<0><<<blocks, 256, 0, (cudaStream_t)stream>>>(
+        arc_launch(march_warp_kernel<0>, blocks, 256, 0, (cudaStream_t)stream, 
             (uint32_t)n_rays, rays_o, rays_d, near, far, aabb, field, (uint32_t)n_grid, (uint32_t)n_pts, dt,
             near_distance, rng_state, rng_inc, zvals, mask, counts, fill_tail);
     ARC_LAUNCH_CHECK();
@@ -455,7 +462,7 @@ int arcb200_sparse_sampling_in_multivol_bitfield(const float *rays_o, const floa
     ARC_REQUIRE(rays_o && rays_d && near && far && min_aabb && aabb && bitfield && zvals && mask,
                 "multivol sampling: null pointer");
     ARC_REQUIRE(n_pts > 0 && n_grid > 0 && n_cascade > 0 && min_step > 0.0f, "multivol sampling: invalid sizes/steps");
-    march_multivol_kernel<<<arc_blocks(n_rays, 128), 128, 0, (cudaStream_t)stream>>>(
+    arc_launch(march_multivol_kernel, arc_blocks(n_rays, 128), 128, 0, (cudaStream_t)stream, 
         (uint32_t)n_rays, rays_o, rays_d, near, far, min_aabb, aabb, bitfield,
         (uint32_t)n_grid, (uint32_t)n_cascade, (uint32_t)n_pts, cone_angle, min_step, max_step, near_distance,
         inclusive, rng_state, rng_inc, zvals, mask);
@@ -498,11 +505,11 @@ int arcb200_march_packed(int bit, const float *rays_o, const float *rays_d, cons
     int rc = launch_march(bit, rays_o, rays_d, near, far, n_pts, dt, aabb, n_grid, field, near_distance, zrows,
                           nullptr, counts, 0, n_rays, rng_state, rng_inc, stream);
     if (rc != ARCB200_OK) return rc;
-    scan_tiles_kernel<<<n_tiles, kScanTile, 0, st>>>((uint32_t)n_rays, counts, offsets, tile_sums, meta + 1);
+    arc_launch(scan_tiles_kernel, n_tiles, kScanTile, 0, st, (uint32_t)n_rays, counts, offsets, tile_sums, meta + 1);
     ARC_LAUNCH_CHECK();
-    scan_tile_sums_kernel<<<1, 1024, 0, st>>>(n_tiles, tile_sums, meta);
+    arc_launch(scan_tile_sums_kernel, 1, 1024, 0, st, n_tiles, tile_sums, meta);
     ARC_LAUNCH_CHECK();
-    pack_samples_kernel<<<arc_blocks((n_rays + 1) * 32, 256), 256, 0, st>>>(
+    arc_launch(pack_samples_kernel, arc_blocks((n_rays + 1) * 32, 256), 256, 0, st, 
         (uint32_t)n_rays, (uint32_t)n_pts, rays_o, rays_d, zrows, counts, offsets, tile_sums, meta, capacity,
         t_out, xyz_out, ray_id_out, aabb, unit_out);
     ARC_LAUNCH_CHECK();

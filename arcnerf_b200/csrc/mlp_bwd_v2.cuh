@@ -85,7 +85,6 @@ mlp_bwd_v2_kernel(int64_t n, const int32_t *__restrict__ n_dev, const __half *__
                   const float *__restrict__ dY, int64_t ldy, float loss_scale, float *__restrict__ dX, int64_t ldgx,
                   float *__restrict__ dW, int io_vec, BwdExtra ex) {
     extern __shared__ __align__(128) uint8_t smem[];
-    if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     SharedV2 *sh = reinterpret_cast<SharedV2 *>(smem);
     uint8_t *w_s = smem + 512;
     const size_t x_bytes = (size_t)kRows * cfg.in_pad * 2, h_bytes = (size_t)kRows * cfg.width * 2;
@@ -113,6 +112,8 @@ mlp_bwd_v2_kernel(int64_t n, const int32_t *__restrict__ n_dev, const __half *__
     tc05::fence_before_sync();
     __syncthreads();
     tc05::fence_after_sync();
+    arc_pdl_sync();      // barriers and tensor memory are set up; from here on inputs of earlier kernels are read
+    if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     const uint32_t tmem = sh->tmem_base;
     const int64_t n_tiles = (n + kRows - 1) / kRows;
     const float inv_scale = 1.0f / loss_scale;
@@ -344,7 +345,7 @@ static int launch_bwd_v2(const MlpCfg &c, const BwdPlan &plan, int64_t n, const 
     const int64_t tiles = (n + kRows - 1) / kRows;
     const int64_t sms = arc_sm_count();
     const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
-    mlp_bwd_v2_kernel<NWG><<<grid, NWG * 128 + 32, smem, st>>>(n, n_dev, (const __half *)X, ldx, (const uint8_t *)blob, c, plan,
+    arc_launch(mlp_bwd_v2_kernel<NWG>, grid, NWG * 128 + 32, smem, st, n, n_dev, (const __half *)X, ldx, (const uint8_t *)blob, c, plan,
                                                               cols, dY, ldy, loss_scale, (float *)dX, ldgx, dW, io_vec, ex);
     return 0;
 }

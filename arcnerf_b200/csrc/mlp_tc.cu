@@ -256,7 +256,6 @@ mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
                const uint8_t *__restrict__ blob, const __grid_constant__ MlpCfg cfg, TOUT *__restrict__ Y, int64_t ldy,
                int io_vec, FwdExtra ex) {
     extern __shared__ __align__(128) uint8_t smem[];
-    if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     Shared *sh = reinterpret_cast<Shared *>(smem);
     uint8_t *w_s = smem + 128;
     uint8_t *a_s = w_s + ((cfg.w_bytes + 127u) & ~127u);
@@ -272,6 +271,8 @@ mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
     tc05::fence_before_sync();
     __syncthreads();
     tc05::fence_after_sync();
+    arc_pdl_sync();      // barriers and tensor memory are set up; from here on inputs of earlier kernels are read
+    if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     const uint32_t tmem = sh->tmem_base;
     if (tid == 0) {
         tc05::mbar_expect_tx(&sh->mbar_w, cfg.w_bytes);
@@ -346,7 +347,6 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
                const float *__restrict__ dY, int64_t ldy, float loss_scale, TGX *__restrict__ dX, int64_t ldgx,
                float *__restrict__ dW, int io_vec, BwdExtra ex) {
     extern __shared__ __align__(128) uint8_t smem[];
-    if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     Shared *sh = reinterpret_cast<Shared *>(smem);
     uint8_t *w_s = smem + 128;
     uint8_t *x_s = w_s + ((cfg.w_bytes + 127u) & ~127u);                  // 128 x in_pad
@@ -365,6 +365,8 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
     tc05::fence_before_sync();
     __syncthreads();
     tc05::fence_after_sync();
+    arc_pdl_sync();      // barriers and tensor memory are set up; from here on inputs of earlier kernels are read
+    if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
     const uint32_t tmem = sh->tmem_base;
     if (tid == 0) {
         tc05::mbar_expect_tx(&sh->mbar_w, cfg.w_bytes);
@@ -562,6 +564,7 @@ mlp_bwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
 
 // fp32 flat parameters (out x in row-major per layer) -> fp16 core-matrix tiles (see tc05.cuh)
 __global__ void pack_weights_kernel(MlpCfg cfg, const float *__restrict__ params, uint8_t *__restrict__ blob) {
+    arc_pdl_sync();
     const int l = blockIdx.y;
     if (l >= cfg.n_mm) return;
     const int K = cfg.K[l], N = cfg.N[l];
@@ -589,6 +592,7 @@ struct AdamPackJobs { AdamPackJob job[kMaxJobs]; };
 
 __global__ void mlp_adam_pack_kernel(const __grid_constant__ AdamPackJobs jobs, int world, AdamHyper h, int zero_grad,
                                      const int32_t *__restrict__ step_dev) {
+    arc_pdl_sync();
     const AdamPackJob &J = jobs.job[blockIdx.y];
     if (step_dev) bias_from_step(h, max(*step_dev, 1));
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < J.n_params; i += gridDim.x * blockDim.x) {
@@ -728,7 +732,7 @@ int arcb200_mlp_pack_weights(const float *params, void *blob, int in_dim, int wi
     MlpCfg c;
     ARC_REQUIRE(make_cfg(c, in_dim, width, n_hidden, out_dim, 0, 0) >= 0, "mlp_pack_weights: unsupported shape");
     ARC_REQUIRE(params && blob && ((uintptr_t)blob & 15u) == 0, "mlp_pack_weights: null or misaligned pointer");
-    pack_weights_kernel<<<dim3(8, c.n_mm), 256, 0, (cudaStream_t)stream>>>(c, params, (uint8_t *)blob);
+    arc_launch(pack_weights_kernel, dim3(8, c.n_mm), 256, 0, (cudaStream_t)stream, c, params, (uint8_t *)blob);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
@@ -763,7 +767,7 @@ int arcb200_mlp_adam_pack(int n_mlps, const int *shapes, float *const *p, float 
         n_max = J.n_params > n_max ? J.n_params : n_max;
     }
     const AdamHyper h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, grad_scale, step < 1 ? 1 : step);
-    mlp_adam_pack_kernel<<<dim3((n_max + 255) / 256, n_mlps), 256, 0, (cudaStream_t)stream>>>(jobs, world, h, zero_grad, step_dev);
+    arc_launch(mlp_adam_pack_kernel, dim3((n_max + 255) / 256, n_mlps), 256, 0, (cudaStream_t)stream, jobs, world, h, zero_grad, step_dev);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
@@ -822,7 +826,7 @@ int arcb200_mlp_fwd_ex(const void *X, int x_is_half, int64_t ldx, const void *bl
         int rc = set_smem(mlp_fwd_kernel<TI, TO, COLS>, smem);                                              \
         if (rc != ARCB200_OK) return rc;                                                                    \
         const unsigned grid = mlp_grid(mlp_fwd_kernel<TI, TO, COLS>, n, smem, COLS);                         \
-        mlp_fwd_kernel<TI, TO, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, (TO *)Y, ldy, io_vec, fex); \
+        arc_launch(mlp_fwd_kernel<TI, TO, COLS>, grid, kRows, smem, st, n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, (TO *)Y, ldy, io_vec, fex); \
     } while (0)
 #define LAUNCH_FWD(TI, TO) do { if (narrow) LAUNCH_FWD2(TI, TO, 64); else LAUNCH_FWD2(TI, TO, 128); } while (0)
     if (x_is_half) { if (y_is_half) LAUNCH_FWD(__half, __half); else LAUNCH_FWD(__half, float); }
@@ -908,7 +912,7 @@ int arcb200_mlp_bwd_ex(const void *X, int x_is_half, int64_t ldx, const void *bl
         int rc = set_smem(mlp_bwd_kernel<TI, TG, COLS>, smem);                                              \
         if (rc != ARCB200_OK) return rc;                                                                    \
         const unsigned grid = mlp_grid(mlp_bwd_kernel<TI, TG, COLS>, n, smem, COLS);                         \
-        mlp_bwd_kernel<TI, TG, COLS><<<grid, kRows, smem, st>>>(n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, plan, dY, \
+        arc_launch(mlp_bwd_kernel<TI, TG, COLS>, grid, kRows, smem, st, n, n_dev, (const TI *)X, ldx, (const uint8_t *)blob, c, plan, dY, \
                                                                ldy, loss_scale, (TG *)dX, ldgx, dW, io_vec, bex); \
     } while (0)
 #define LAUNCH_BWD_T(COLS)                                                                                  \

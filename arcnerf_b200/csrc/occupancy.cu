@@ -16,6 +16,7 @@ namespace {
 // volume_func_kernel.cu:297-309 and bitfield_func_kernel.cu:217-234).
 __global__ void group_max_kernel(uint32_t n, const float *__restrict__ vals, const int64_t *__restrict__ group,
                                  float *__restrict__ out) {
+    arc_pdl_sync();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     atomicMax((uint32_t *)&out[group[i]], __float_as_uint(vals[i]));
@@ -23,6 +24,7 @@ __global__ void group_max_kernel(uint32_t n, const float *__restrict__ vals, con
 
 __global__ void splat_max_kernel(uint32_t n, const uint32_t *__restrict__ idx, const float *__restrict__ vals,
                                  float *__restrict__ grid_tmp) {
+    arc_pdl_sync();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     atomicMax((uint32_t *)&grid_tmp[idx[i]], __float_as_uint(vals[i]));
@@ -35,6 +37,7 @@ __global__ void grid_samples_kernel(uint32_t n_elements, Pcg32 rng, uint32_t ste
                                     float *__restrict__ pos_out, uint32_t *__restrict__ idx_out, uint32_t n_grid,
                                     float thresh, const float *__restrict__ aabb, uint32_t n_cascades,
                                     int inclusive) {
+    arc_pdl_sync();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_elements) return;
     rng.advance((uint64_t)(int64_t)(i * 4u));
@@ -70,6 +73,7 @@ __global__ void grid_samples_kernel(uint32_t n_elements, Pcg32 rng, uint32_t ste
 
 // grid = grid < 0 ? grid : max(grid*decay, tmp)   (bitfield_func_kernel.cu:260-275)
 __global__ void ema_kernel(uint32_t n, float decay, float *__restrict__ grid, const float *__restrict__ tmp) {
+    arc_pdl_sync();
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const float prev = grid[i];
         grid[i] = prev < 0.f ? prev : fmaxf(prev * decay, tmp[i]);
@@ -80,6 +84,7 @@ __global__ void ema_kernel(uint32_t n, float decay, float *__restrict__ grid, co
 // per byte; `mean` may come from device memory (no host round trip for the mean).
 __global__ void to_bitfield_kernel(uint32_t n_bytes, const float *__restrict__ grid, uint8_t *__restrict__ bits,
                                    float mean_host, const float *__restrict__ mean_dev, float opa_thres) {
+    arc_pdl_sync();
     const float mean = mean_dev ? __ldg(mean_dev) : mean_host;
     const float thresh = opa_thres < mean ? opa_thres : mean;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_bytes; i += gridDim.x * blockDim.x) {
@@ -98,6 +103,7 @@ __global__ void to_bitfield_kernel(uint32_t n_bytes, const float *__restrict__ g
 // (bitfield_func_kernel.cu:365), which adds 8 for every non-zero byte.
 __global__ void count_bits_kernel(uint32_t n_bytes, const uint8_t *__restrict__ bits, float *__restrict__ counter,
                                   int faithful) {
+    arc_pdl_sync();
     uint32_t c = 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_bytes; i += gridDim.x * blockDim.x) {
         const uint32_t b = bits[i];
@@ -133,7 +139,7 @@ int arcb200_tensor_reduce_max(const float *full_tensor, const int64_t *group_idx
     ARC_REQUIRE(n >= 0 && n < (1ll << 32), "tensor_reduce_max: bad n");
     if (n == 0) return ARCB200_OK;
     ARC_REQUIRE(full_tensor && group_idx && uni_tensor, "tensor_reduce_max: null pointer");
-    group_max_kernel<<<arc_blocks(n, 256), 256, 0, (cudaStream_t)stream>>>((uint32_t)n, full_tensor, group_idx, uni_tensor);
+    arc_launch(group_max_kernel, arc_blocks(n, 256), 256, 0, (cudaStream_t)stream, (uint32_t)n, full_tensor, group_idx, uni_tensor);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
@@ -147,7 +153,7 @@ int arcb200_generate_grid_samples(const float *density_grid, int ema_step, int64
     Pcg32 rng;
     rng.state = rng_state;
     rng.inc = rng_inc;
-    grid_samples_kernel<false><<<arc_blocks(n_elements, 256), 256, 0, (cudaStream_t)stream>>>(
+    arc_launch(grid_samples_kernel<false>, arc_blocks(n_elements, 256), 256, 0, (cudaStream_t)stream, 
         (uint32_t)n_elements, rng, (uint32_t)ema_step, density_grid, positions, indices, (uint32_t)n_grid, thresh,
         nullptr, 0u, 0);
     ARC_LAUNCH_CHECK();
@@ -165,7 +171,7 @@ int arcb200_generate_grid_samples_multivol(const float *density_grid, int ema_st
     Pcg32 rng;
     rng.state = rng_state;
     rng.inc = rng_inc;
-    grid_samples_kernel<true><<<arc_blocks(n_elements, 256), 256, 0, (cudaStream_t)stream>>>(
+    arc_launch(grid_samples_kernel<true>, arc_blocks(n_elements, 256), 256, 0, (cudaStream_t)stream, 
         (uint32_t)n_elements, rng, (uint32_t)ema_step, density_grid, positions, indices, (uint32_t)n_grid, thresh,
         aabb, (uint32_t)n_cascade, inclusive);
     ARC_LAUNCH_CHECK();
@@ -177,7 +183,7 @@ int arcb200_splat_grid_samples(const float *density, const uint32_t *indices, in
     ARC_REQUIRE(n_samples >= 0 && n_samples < (1ll << 32), "splat_grid_samples: bad n");
     if (n_samples == 0) return ARCB200_OK;
     ARC_REQUIRE(density && indices && density_grid_tmp, "splat_grid_samples: null pointer");
-    splat_max_kernel<<<arc_blocks(n_samples, 256), 256, 0, (cudaStream_t)stream>>>((uint32_t)n_samples, indices,
+    arc_launch(splat_max_kernel, arc_blocks(n_samples, 256), 256, 0, (cudaStream_t)stream, (uint32_t)n_samples, indices,
                                                                                   density, density_grid_tmp);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
@@ -188,7 +194,7 @@ int arcb200_ema_grid_samples_nerf(const float *density_grid_tmp, int64_t n_eleme
     ARC_REQUIRE(n_elements >= 0 && n_elements < (1ll << 32), "ema_grid_samples_nerf: bad n");
     if (n_elements == 0) return ARCB200_OK;
     ARC_REQUIRE(density_grid_tmp && density_grid, "ema_grid_samples_nerf: null pointer");
-    ema_kernel<<<sweep_blocks(n_elements, 256), 256, 0, (cudaStream_t)stream>>>((uint32_t)n_elements, decay,
+    arc_launch(ema_kernel, sweep_blocks(n_elements, 256), 256, 0, (cudaStream_t)stream, (uint32_t)n_elements, decay,
                                                                                density_grid, density_grid_tmp);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
@@ -202,7 +208,7 @@ int arcb200_update_bitfield(const float *density_grid, float mean_host, const fl
     if (n_cells == 0) return ARCB200_OK;
     ARC_REQUIRE(density_grid && bitfield, "update_bitfield: null pointer");
     ARC_REQUIRE(((uintptr_t)density_grid & 15u) == 0, "update_bitfield: density grid must be 16-byte aligned");
-    to_bitfield_kernel<<<sweep_blocks(n_cells / 8, 256), 256, 0, (cudaStream_t)stream>>>(
+    arc_launch(to_bitfield_kernel, sweep_blocks(n_cells / 8, 256), 256, 0, (cudaStream_t)stream, 
         (uint32_t)(n_cells / 8), density_grid, bitfield, mean_host, mean_dev, opa_thres);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
@@ -212,7 +218,7 @@ int arcb200_count_bitfield(const uint8_t *bitfield, float *counter, int64_t n_ce
     ARC_REQUIRE(n_cells >= 0 && n_cells % 8 == 0 && n_cells < (1ll << 35), "count_bitfield: n_cells must be a multiple of 8");
     if (n_cells == 0) return ARCB200_OK;
     ARC_REQUIRE(bitfield && counter, "count_bitfield: null pointer");
-    count_bits_kernel<<<sweep_blocks(n_cells / 8, 256), 256, 0, (cudaStream_t)stream>>>((uint32_t)(n_cells / 8), bitfield,
+    arc_launch(count_bits_kernel, sweep_blocks(n_cells / 8, 256), 256, 0, (cudaStream_t)stream, (uint32_t)(n_cells / 8), bitfield,
                                                                                        counter, faithful);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;

@@ -11,6 +11,7 @@ namespace {
 __global__ void adam_kernel(size_t n, float *__restrict__ p, float *__restrict__ m, float *__restrict__ v,
                             float *__restrict__ g, __half *__restrict__ p_half, AdamHyper h, int zero_grad,
                             const int32_t *__restrict__ step_dev) {
+    arc_pdl_sync();
     if (step_dev) bias_from_step(h, max(*step_dev, 1));    // step count kept on the device (replayable launches)
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     const size_t n4 = n / 4;
@@ -40,11 +41,20 @@ __global__ void adam_kernel(size_t n, float *__restrict__ p, float *__restrict__
     }
 }
 
-__global__ void counter_add_kernel(int32_t *c, int32_t v) { if (threadIdx.x == 0 && blockIdx.x == 0) *c += v; }
+__global__ void counter_add_kernel(int32_t *c, int32_t v) {
+    arc_pdl_sync();
+    if (threadIdx.x == 0 && blockIdx.x == 0) *c += v;
+}
+
+__global__ void fill_f32_kernel(float *dst, float value, size_t n) {
+    arc_pdl_sync();
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = value;
+}
 
 // loss_sum[0] += weight/(3R) * sum huber(rgb - target);  g_rgb = d loss / d rgb
 __global__ void huber_kernel(uint32_t n_elem, const float *__restrict__ rgb, const float *__restrict__ target,
                              float delta, float scale, float *__restrict__ g_rgb, float *__restrict__ loss_sum) {
+    arc_pdl_sync();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     float l = 0.f;
     if (i < n_elem) {
@@ -92,7 +102,7 @@ int arcb200_adam_step(float *p, float *m, float *v, float *g, void *p_half, int6
     const long long cap = (long long)arc_sm_count() * 16;
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
-    adam_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((size_t)n, p, m, v, g, (__half *)p_half, h, zero_grad, step_dev);
+    arc_launch(adam_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, (size_t)n, p, m, v, g, (__half *)p_half, h, zero_grad, step_dev);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
@@ -100,7 +110,19 @@ int arcb200_adam_step(float *p, float *m, float *v, float *g, void *p_half, int6
 // counter[0] += value on the stream (device-resident step counter for replayed launch sequences)
 int arcb200_counter_add(int32_t *counter, int value, void *stream) {
     ARC_REQUIRE(counter != nullptr, "counter_add: null pointer");
-    counter_add_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(counter, value);
+    arc_launch(counter_add_kernel, 1, 32, 0, (cudaStream_t)stream, counter, value);
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// dst[0..n) = value on the stream (accumulators that a later kernel adds into, e.g. the loss)
+int arcb200_fill_f32(float *dst, float value, int64_t n, void *stream) {
+    ARC_REQUIRE(n >= 0 && (dst || n == 0), "fill_f32: bad argument");
+    if (n == 0) return ARCB200_OK;
+    long long blocks = (n + 255) / 256;
+    const long long cap = (long long)arc_sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    arc_launch(fill_f32_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, dst, value, (size_t)n);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
@@ -112,7 +134,7 @@ int arcb200_huber_loss(const float *rgb, const float *target, float delta, float
     if (n_rays == 0) return ARCB200_OK;
     ARC_REQUIRE(rgb && target && delta > 0.f, "huber_loss: null pointer or non-positive delta");
     const uint32_t n_elem = (uint32_t)(n_rays * 3);
-    huber_kernel<<<arc_blocks(n_elem, 256), 256, 0, (cudaStream_t)stream>>>(n_elem, rgb, target, delta,
+    arc_launch(huber_kernel, arc_blocks(n_elem, 256), 256, 0, (cudaStream_t)stream, n_elem, rgb, target, delta,
                                                                            weight / (float)n_elem, g_rgb, loss_sum);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;

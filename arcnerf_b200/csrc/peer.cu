@@ -43,6 +43,7 @@ template <int W>
 __global__ void adam_peer_kernel(size_t lo, size_t hi, float *__restrict__ p, float *__restrict__ m,
                                  float *__restrict__ v, const __grid_constant__ PeerList peers, int world,
                                  AdamHyper h, const int32_t *__restrict__ step_dev) {
+    arc_pdl_sync();
     if (step_dev) bias_from_step(h, max(*step_dev, 1));
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     const size_t k_lo = lo / 4, k_hi = hi / 4;            // lo is a multiple of 4
@@ -126,6 +127,7 @@ __device__ __forceinline__ unsigned long long global_ns() {
 // (the step's results are then invalid, but the GPU is not left spinning).
 __global__ void peer_barrier_kernel(const __grid_constant__ FlagList fl, int world, int rank,
                                     unsigned long long *epoch, int32_t *status, unsigned long long timeout_ns) {
+    arc_pdl_sync();
     __shared__ unsigned long long target;
     if (threadIdx.x == 0) {
         target = *epoch + 1ull;
@@ -154,7 +156,7 @@ __global__ void peer_barrier_kernel(const __grid_constant__ FlagList fl, int wor
 template <int W>
 void launch_adam_peer(unsigned blocks, cudaStream_t st, size_t lo, size_t hi, float *p, float *m, float *v,
                       const PeerList &pl, int world, const AdamHyper &h, const int32_t *step_dev) {
-    adam_peer_kernel<W><<<blocks, 256, 0, st>>>(lo, hi, p, m, v, pl, world, h, step_dev);
+    arc_launch(adam_peer_kernel<W>, blocks, 256, 0, st, lo, hi, p, m, v, pl, world, h, step_dev);
 }
 
 }  // namespace
@@ -214,7 +216,7 @@ int arcb200_peer_barrier(void *const *flags, int world, int rank, void *epoch, i
     for (int w = 0; w < kMaxWorld; ++w) fl.flags[w] = w < world ? (unsigned long long *)flags[w] : nullptr;
     for (int w = 0; w < world; ++w) ARC_REQUIRE(fl.flags[w] != nullptr, "peer_barrier: flags[%d] is null", w);
     if (timeout_ms <= 0) timeout_ms = 20000;
-    peer_barrier_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(fl, world, rank, (unsigned long long *)epoch, status,
+    arc_launch(peer_barrier_kernel, 1, 32, 0, (cudaStream_t)stream, fl, world, rank, (unsigned long long *)epoch, status,
                                                            (unsigned long long)timeout_ms * 1000000ull);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;

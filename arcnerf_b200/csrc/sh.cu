@@ -55,6 +55,7 @@ template <typename OUT>
 __global__ void sh_fwd_kernel(uint32_t n, const int32_t *__restrict__ n_dev, const float *__restrict__ dirs,
                               const int32_t *__restrict__ index, int degree, int remap, OUT *__restrict__ out,
                               uint32_t out_stride, int vec) {
+    arc_pdl_sync();
     if (n_dev) n = min(n, (uint32_t)max(*n_dev, 0));
     const int nd = degree * degree;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
@@ -102,10 +103,10 @@ int arcb200_sh_fwd(const float *dirs, const int32_t *index, int degree, int rema
     if (blocks > cap) blocks = cap;
     const int vec = out_is_half && (((uintptr_t)out & 15u) == 0) && ((out_stride * 2) % 16 == 0);
     if (out_is_half)
-        sh_fwd_kernel<__half><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((uint32_t)n, n_dev, dirs, index, degree, remap,
+        arc_launch(sh_fwd_kernel<__half>, (unsigned)blocks, 256, 0, (cudaStream_t)stream, (uint32_t)n, n_dev, dirs, index, degree, remap,
                                                                                 (__half *)out, (uint32_t)out_stride, vec);
     else
-        sh_fwd_kernel<float><<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>((uint32_t)n, n_dev, dirs, index, degree, remap,
+        arc_launch(sh_fwd_kernel<float>, (unsigned)blocks, 256, 0, (cudaStream_t)stream, (uint32_t)n, n_dev, dirs, index, degree, remap,
                                                                                (float *)out, (uint32_t)out_stride, 0);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;

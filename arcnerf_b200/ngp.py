@@ -344,7 +344,7 @@ class NGPPipeline:
         (the sampler does not depend on the parameters being updated)."""
         R = rays_o.shape[0]
         self.forward(rays_o, rays_d, bkg, next_rays=next_rays)
-        self.loss.zero_()
+        _lib.call('arcb200_fill_f32', self.loss.data_ptr(), 0.0, 1, _lib.current_stream())
         self._run('huber_loss', lambda: _lib.call(
             'arcb200_huber_loss', self.rgb.data_ptr(), target.data_ptr(), self.cfg['huber_delta'],
             self.cfg['loss_weight'], self.g_rgb.data_ptr(), self.loss.data_ptr(), R, _lib.current_stream()))
@@ -420,7 +420,7 @@ class NGPPipeline:
         """everything of a training step after the sampler, on the current sample set and the current stream"""
         self.field_forward(rays_d)
         self.composite(R, bkg)
-        self.loss.zero_()
+        _lib.call('arcb200_fill_f32', self.loss.data_ptr(), 0.0, 1, _lib.current_stream())
         self._run('huber_loss', lambda: _lib.call(
             'arcb200_huber_loss', self.rgb.data_ptr(), target.data_ptr(), self.cfg['huber_delta'],
             self.cfg['loss_weight'], self.g_rgb.data_ptr(), self.loss.data_ptr(), R, _lib.current_stream()))
@@ -438,6 +438,8 @@ class NGPPipeline:
         self.static_in = [tuple(torch.empty((n_rays, 3), dtype=f32, device=dev) for _ in range(4)) for _ in range(2)]
         self.graph_rays = n_rays
         self.graphs = [None, None]
+        self._gate_events = [torch.cuda.Event(), torch.cuda.Event()]
+        self._ready_events = [torch.cuda.Event(), torch.cuda.Event()]
         rng_state = (self.rng.state, self.rng.inc)       # the warm-up marches must not consume the jitter stream
         # warm up outside capture (lazy module loading, function attributes), on both parities
         for _ in range(2):
@@ -500,17 +502,18 @@ class NGPPipeline:
         ss.ready = None
         self.cur = p
         if next_batch is not None:
+            gate = self._gate_events[p]
+            gate.record()                      # the side stream may touch slot 1-p once everything queued so far is done
+        self.step_count += 1
+        self.graphs[p].replay()                # the GPU starts on this step before the CPU prepares the next one
+        if next_batch is not None:
             q = 1 - p
-            gate = torch.cuda.Event()
-            gate.record()
             with torch.cuda.stream(self.side_stream):
                 self.side_stream.wait_event(gate)
                 self._upload_and_sample(q, next_batch)
                 self.sets[q].key = ('slot', q, id(next_batch[0]))
-                self.sets[q].ready = torch.cuda.Event()
+                self.sets[q].ready = self._ready_events[q]
                 self.sets[q].ready.record()
-        self.step_count += 1
-        self.graphs[p].replay()
         return self.loss
 
     @torch.no_grad()
