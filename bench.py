@@ -116,13 +116,15 @@ EXCHANGE_NOTE = {
 
 
 # algorithmic work per unit (SURVEY.md §8d / DESIGN.md §4)
-def stage_work(name, n_samples, n_rays, n_table_params):
+def stage_work(name, n_samples, n_rays, n_table_params, world=1):
     if name == 'grid_fwd':
         return 'hbm', 588.0 * n_samples          # 12 B in + 16 levels * 8 corners * 4 B gathered + 64 B out
     if name == 'grid_bwd':
         return 'hbm', 588.0 * n_samples          # 12 B + 64 B in + 16*8 entries of 4 B updated
     if name == 'adam_table':
         return 'hbm', 34.0 * n_table_params      # p,m,v,g read; p,m,v,g(=0) written; fp16 copy written
+    if name == 'adam_table_peer':               # per rank: its 1/world slice; p,m,v in and out, `world` gradients in, `world` fp16 copies out
+        return 'hbm', (24.0 + 6.0 * world) * n_table_params / world
     if name == 'composite_fwd':
         return 'hbm', 20.0 * n_samples + 20.0 * n_rays
     if name == 'composite_bwd':
@@ -308,7 +310,7 @@ def main():
     step_ms_staged = sum(v[0] for v in stages.values())
     table = []
     for name, (ms, cnt) in sorted(stages.items(), key=lambda kv: -kv[1][0]):
-        bound, work = stage_work(name, n_samples, N_RAYS, n_table)
+        bound, work = stage_work(name, n_samples, N_RAYS, n_table, world)
         ach = work / (ms * 1e-3) / (1e9 if bound == 'hbm' else 1e12) if bound else None
         peak = peaks['hbm_gbs'] if bound == 'hbm' else (peaks['bf16_tflops'] if bound == 'tensor' else None)
         table.append(dict(stage=name, ms=round(ms, 4), share=round(ms / step_ms_staged, 3), bound=bound,
@@ -317,13 +319,21 @@ def main():
         for r in table:
             sys.stderr.write('%-16s %8.4f ms  share %5.3f  %-6s achieved %-10s frac %s\n' %
                              (r['stage'], r['ms'], r['share'], r['bound'], r['achieved'], r['frac']))
-    bound, work = stage_work(top[0], n_samples, N_RAYS, n_table)
+    bound, work = stage_work(top[0], n_samples, N_RAYS, n_table, world)
     if bound is None:
         bound, work = 'hbm', 0.0
     ach = work / (top[1][0] * 1e-3) / (1e9 if bound == 'hbm' else 1e12)
     peak = peaks['hbm_gbs'] if bound == 'hbm' else peaks['bf16_tflops']
+    traffic, traffic_src = None, None
+    try:                                        # DRAM bytes per launch of that kernel from the committed ncu --set full capture
+        with open(os.path.join(ROOT, 'profiles', 'r01b_traffic.json')) as f:
+            tj = json.load(f)
+        if top[0] in tj:
+            traffic, traffic_src = tj[top[0]]['traffic_bytes'], 'profiles/r01b_traffic.json (ncu --set full, dram read + write per launch)'
+    except (OSError, ValueError):
+        pass
     roofline = dict(kernel=top[0], bound=bound, achieved=ach, peak=peak, unit='GB/s' if bound == 'hbm' else 'TFLOP/s',
-                    frac=ach / peak, traffic=None, ms_per_launch=top[1][0], share_of_step=top[1][0] / step_ms_staged,
+                    frac=ach / peak, traffic=traffic, traffic_source=traffic_src, algorithmic_bytes_per_launch=work if bound == 'hbm' else None, ms_per_launch=top[1][0], share_of_step=top[1][0] / step_ms_staged,
                     peak_source=peaks['source'], stages=table)
 
     # ---- 800x800 frame render (forward only), rays sharded over ranks, final gather
