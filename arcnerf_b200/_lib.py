@@ -66,6 +66,11 @@ _SIGS = {
     'arcb200_fill_f32': [P, F, L, P],
     'arcb200_huber_loss': [P, P, F, F, P, P, L, P],
     'arcb200_mlp_adam_pack': [I, P, P, P, P, P, I, P, I, F, F, F, F, F, F, I, P, P],
+    'arcb200_sphere_ray_intersection': [P, P, P, P, P, P, P, P, L, L, P],
+    'arcb200_zvals_from_near_far': [P, P, I, I, I, P, P, L, P],
+    'arcb200_zvals_fix_step': [P, P, F, I, I, P, P, P, L, P],
+    'arcb200_ray_points': [P, P, P, P, L, I, P],
+    'arcb200_sort_rows': [P, P, L, I, P],
     'arcb200_peer_alloc': [L, P, P],
     'arcb200_peer_open': [P, P],
     'arcb200_peer_close': [P],

@@ -30,6 +30,7 @@ SOURCES = {
     'glue.cu': [],
     'noalloc.cu': [],
     'peer.cu': [],
+    'zvals.cu': ['-fmad=false'],
 }
 
 

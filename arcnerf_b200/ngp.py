@@ -222,6 +222,54 @@ class NGPPipeline:
         assert v.shape == self.volume.shape
         self.volume.copy_(v)
 
+    # ------------------------------------------------------------------------------------------ occupancy maintenance
+    @torch.no_grad()
+    def forward_pts(self, pts, chunk=1 << 19):
+        """Density at arbitrary world points (N,3) -> (N,): hash encode + geometry head with the TruncExp epilogue, in
+        chunks (the reference's Base3dModel.forward_pts through chunk_processing, base_3d_model.py:343-366)."""
+        pts = pts.to(self.dev, torch.float32)
+        n = pts.shape[0]
+        out = torch.empty((n, ), dtype=torch.float32, device=self.dev)
+        lo, side = self.aabb[0], self.aabb[1] - self.aabb[0]
+        for a in range(0, n, chunk):
+            b = min(n, a + chunk)
+            unit = ((pts[a:b] - lo) / side).contiguous()
+            enc = F.grid_forward(unit, self.table_h, self.geom)
+            feat = torch.empty((b - a, self.cfg['w_feat']), dtype=torch.float16, device=self.dev)
+            F.mlp_forward(enc, self.geo_blob, self.geo_spec, out=feat, exp0_out=out[a:b])
+        return out
+
+    @torch.no_grad()
+    def get_est_opacity(self, dt, pts):
+        """base_3d_model.py:368-389: opacity = density * dt (the instant-ngp convention)"""
+        return self.forward_pts(pts) * dt
+
+    def attach_bound(self, bound):
+        """Use an object bound (plugin/obj_bound.py VolumeBound) as the owner of the occupancy state; its bool volume is
+        mirrored into the sampler's buffer after every refresh."""
+        self.bound = bound.to(self.dev)
+        if bound.volume.get_voxel_bitfield() is not None:
+            self.volume.copy_(bound.volume.get_voxel_bitfield())
+
+    @torch.no_grad()
+    def update_occupancy(self, cur_epoch):
+        """FgModel.optimize (fg_model.py:400-410): obj_bound.optimize(cur_epoch, n_coarse_sample, get_est_opacity) every
+        `epoch_optim` steps; warm-up sweeps every voxel, afterwards 1/4 random + 1/4 occupied voxels."""
+        bound = getattr(self, 'bound', None)
+        if bound is None:
+            from .plugin.obj_bound import VolumeBound
+            cfg = self.cfg
+            bound = VolumeBound(dict(volume=dict(n_grid=cfg['n_grid'], side=cfg['side']), epoch_optim=cfg.get('epoch_optim', 16),
+                                     epoch_optim_warmup=cfg.get('epoch_optim_warmup', 256), ray_sample_acc=True,
+                                     ray_sample_fix_step=True, near_distance=cfg['near_distance'],
+                                     opa_thres=cfg.get('opa_thres', 0.01)))
+            self.attach_bound(bound)
+            bound = self.bound
+        bound.optimize(cur_epoch, self.cfg['n_sample'], self.get_est_opacity)
+        self.volume.copy_(bound.volume.get_voxel_bitfield())
+        for ss in self.sets:                    # a prefetched sample set was marched through the old occupancy
+            ss.key = None
+
     # ------------------------------------------------------------------------------------------ stages
     def _sample_into(self, ss, rays_o, rays_d):
         """slab test + packed occupancy march into sample set `ss` on the current stream; stays on the device"""

@@ -4,6 +4,7 @@
 on libarcb200's segmented-scan kernels instead of ~15 eager torch ops over padded tensors."""
 import torch
 
+from .. import _lib
 from .. import functional as F
 
 
@@ -85,7 +86,7 @@ def sample_cdf(bins, cdf, n_sample, det=False, eps=1e-5):
         u = torch.rand(list(cdf.shape[:-1]) + [n_sample], device=bins.device)
     with torch.no_grad():
         samples = F.sample_cdf_gather(bins.contiguous().float(), cdf.detach().contiguous().float(), u.contiguous(), eps)
-        samples, _ = torch.sort(samples, -1)
+        samples = sort_rows(samples)
     return samples
 
 
@@ -119,3 +120,142 @@ class _SdfToAlphaFn(torch.autograd.Function):
 def sdf_to_alpha(mid_sdf, zvals, mid_slope, s, clip=True):
     """arcnerf/models/neus_model.py:242-265; differentiable w.r.t. mid_sdf, mid_slope and the scale s."""
     return _SdfToAlphaFn.apply(mid_sdf, zvals, mid_slope, s, clip)
+
+
+# ------------------------------------------------------------------------------------------ depth samples (a15)
+def _f32(t):
+    return t.contiguous() if t.dtype == torch.float32 else t.float().contiguous()
+
+
+def sort_rows(vals):
+    """ascending sort of every row (torch.sort(vals, -1)[0] of the reference's sample merge)"""
+    v = _f32(vals)
+    flat = v.reshape(-1, v.shape[-1])
+    out = torch.empty_like(flat)
+    _lib.call('arcb200_sort_rows', flat.data_ptr(), out.data_ptr(), flat.shape[0], flat.shape[1], _lib.current_stream())
+    return out.reshape(v.shape)
+
+
+@torch.no_grad()
+def sphere_ray_intersection(rays_o, rays_d, radius, origin=(0, 0, 0)):
+    """arcnerf/geometry/ray.py:180-255 -> near, far (N_rays, N_r), pts (N_rays, N_r, 2, 3), mask (N_rays, N_r) bool"""
+    rays_o, rays_d = _f32(rays_o), _f32(rays_d)
+    if not isinstance(radius, torch.Tensor):
+        assert isinstance(radius, (float, int)), 'Invalid type'
+        radius = torch.tensor([radius], dtype=torch.float32, device=rays_o.device)
+    radius = _f32(radius).to(rays_o.device)
+    n, nr = rays_o.shape[0], radius.shape[0]
+    dev = rays_o.device
+    near = torch.empty((n, nr), dtype=torch.float32, device=dev)
+    far = torch.empty((n, nr), dtype=torch.float32, device=dev)
+    pts = torch.empty((n, nr, 2, 3), dtype=torch.float32, device=dev)
+    mask = torch.empty((n, nr), dtype=torch.bool, device=dev)
+    import ctypes
+    org = (ctypes.c_float * 3)(*[float(x) for x in origin])
+    _lib.call('arcb200_sphere_ray_intersection', rays_o.data_ptr(), rays_d.data_ptr(), radius.data_ptr(), org, near.data_ptr(),
+              far.data_ptr(), pts.data_ptr(), mask.data_ptr(), n, nr, _lib.current_stream())
+    return near, far, pts, mask
+
+
+@torch.no_grad()
+def get_ray_points_by_zvals(rays_o, rays_d, zvals):
+    """arcnerf/geometry/ray.py:11-30 -> (N_rays, N_pts, 3)"""
+    rays_o, rays_d, zvals = _f32(rays_o), _f32(rays_d), _f32(zvals)
+    assert zvals.shape[0] == rays_o.shape[0], 'Invalid shape for zvals... Should be (N_rays, N_pts)'
+    pts = torch.empty((zvals.shape[0], zvals.shape[1], 3), dtype=torch.float32, device=zvals.device)
+    _lib.call('arcb200_ray_points', rays_o.data_ptr(), rays_d.data_ptr(), zvals.data_ptr(), pts.data_ptr(), zvals.shape[0],
+              zvals.shape[1], _lib.current_stream())
+    return pts
+
+
+@torch.no_grad()
+def get_near_far_from_rays(rays_o, rays_d, bounds=None, near_hardcode=None, far_hardcode=None, bounding_radius=None):
+    """ray_helper.py:175-228 -> near, far (N_rays, 1)"""
+    dev, n_rays = rays_o.device, rays_o.shape[0]
+    if near_hardcode is None or far_hardcode is None:
+        if bounds is None and bounding_radius is None:
+            raise NotImplementedError('You must specify near/far in some place...')
+        if bounds is None:
+            near, far, _, _ = sphere_ray_intersection(rays_o, rays_d, float(bounding_radius))
+        else:
+            near, far = bounds[:, 0:1].float().clone(), bounds[:, 1:2].float().clone()
+            if bounding_radius is not None:
+                _, far_bound, _, _ = sphere_ray_intersection(rays_o, rays_d, float(bounding_radius))
+                far = torch.where(far > far_bound, far_bound, far)
+        if near_hardcode is not None:
+            near = near * 0 + near_hardcode
+        if far_hardcode is not None:
+            far = far * 0 + far_hardcode
+    else:
+        near = torch.full((n_rays, 1), float(near_hardcode), dtype=torch.float32, device=dev)
+        far = torch.full((n_rays, 1), float(far_hardcode), dtype=torch.float32, device=dev)
+    far = torch.where(far <= near, near + 1e-5, far)
+    return near, far
+
+
+@torch.no_grad()
+def get_zvals_from_near_far(near, far, n_pts, inclusive=True, inverse_linear=False, perturb=False, u=None):
+    """ray_helper.py:231-263 -> (N_rays, n_pts).  u: optional uniforms (N_rays, n_pts) for the jitter (default torch.rand)."""
+    near, far = _f32(near).reshape(-1), _f32(far).reshape(-1)
+    n = near.shape[0]
+    if perturb and u is None:
+        u = torch.rand((n, n_pts), dtype=torch.float32, device=near.device)
+    zvals = torch.empty((n, n_pts), dtype=torch.float32, device=near.device)
+    _lib.call('arcb200_zvals_from_near_far', near.data_ptr(), far.data_ptr(), int(n_pts), int(bool(inclusive)),
+              int(bool(inverse_linear)), _lib.ptr(_f32(u) if (perturb and u is not None) else None), zvals.data_ptr(), n,
+              _lib.current_stream())
+    return zvals
+
+
+@torch.no_grad()
+def get_zvals_from_near_far_fix_step(near, far, fix_t, n_pts, inclusive=True, perturb=False, u=None):
+    """ray_helper.py:266-315 -> zvals (N_rays, n_pts), mask_pts (N_rays, n_pts) bool; jitters always, as the reference"""
+    assert fix_t > 0, 'Only allow positive step...'
+    near, far = _f32(near).reshape(-1), _f32(far).reshape(-1)
+    n = near.shape[0]
+    if u is None:
+        u = torch.rand((n, n_pts), dtype=torch.float32, device=near.device)
+    zvals = torch.empty((n, n_pts), dtype=torch.float32, device=near.device)
+    mask = torch.empty((n, n_pts), dtype=torch.bool, device=near.device)
+    _lib.call('arcb200_zvals_fix_step', near.data_ptr(), far.data_ptr(), float(fix_t), int(n_pts), int(bool(inclusive)),
+              _f32(u).data_ptr(), zvals.data_ptr(), mask.data_ptr(), n, _lib.current_stream())
+    return zvals, mask
+
+
+@torch.no_grad()
+def perturb_interval(vals, u=None):
+    """ray_helper.py:361-378 on any (B, N) values (kept in torch: four elementwise ops on a small tensor)"""
+    mids = .5 * (vals[..., 1:] + vals[..., :-1])
+    upper = torch.cat([mids, vals[..., -1:]], -1)
+    lower = torch.cat([vals[..., :1], mids], -1)
+    if u is None:
+        u = torch.rand(upper.shape, dtype=vals.dtype, device=vals.device)
+    return lower + (upper - lower) * u
+
+
+@torch.no_grad()
+def get_zvals_from_sphere_radius(rays_o, rays_d, sphere_radius):
+    """ray_helper.py:344-358: far intersection with every shell -> (N_rays, N)"""
+    _, zvals, _, _ = sphere_ray_intersection(rays_o, rays_d, sphere_radius)
+    return zvals
+
+
+@torch.no_grad()
+def get_zvals_outside_sphere(rays_o, rays_d, n_pts, radius, perturb=False, u=None):
+    """ray_helper.py:318-341 (NeRF++ inverse-sphere shells) -> zvals (N_rays, n_pts), sphere_radius (n_pts,)"""
+    t_vals = torch.linspace(0.0, 1.0, n_pts + 2, dtype=torch.float32, device=rays_o.device)[1:-1]
+    sphere_radius = radius / torch.flip(t_vals, dims=[-1])
+    if perturb:
+        sphere_radius = perturb_interval(sphere_radius[None], u)[0]
+    return get_zvals_from_sphere_radius(rays_o, rays_d, sphere_radius), sphere_radius
+
+
+@torch.no_grad()
+def upsample_zvals(zvals, weights, n_importance, det=True, eps=1e-5):
+    """NeRF.upsample_zvals (arcnerf/models/nerf_model.py:93-117) without the mask bookkeeping: importance samples from
+    the coarse weights on the interval mid-points, merged into the coarse samples in ascending order."""
+    n_sample = zvals.shape[1]
+    weights_coarse = weights[:, 1:n_sample - 1]
+    zvals_mid = 0.5 * (zvals[..., 1:] + zvals[..., :-1])
+    new = sample_pdf(zvals_mid, weights_coarse, n_importance, det, eps).detach()
+    return sort_rows(torch.cat([zvals, new], -1)), new

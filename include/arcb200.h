@@ -338,6 +338,25 @@ int arcb200_mlp_adam_pack(int n_mlps, const int *shapes, float *const *p, float 
 int arcb200_huber_loss(const float *rgb, const float *target, float delta, float weight, float *g_rgb,
                        float *loss_sum, int64_t n_rays, void *stream);
 
+/* ---------------------------------------------------------------- depth samples around the march (a15) ----
+ * arcnerf/geometry/ray.py:180-255 sphere_ray_intersection (near/far/pts/mask against n_r concentric spheres; used by
+ * get_near_far_from_rays, ray_helper.py:175-228, and the NeRF++ shells, :318-358). */
+int arcb200_sphere_ray_intersection(const float *rays_o, const float *rays_d, const float *radius, const float *origin,
+                                    float *near, float *far, float *pts, uint8_t *mask, int64_t n_rays, int64_t n_r,
+                                    void *stream);
+/* ray_helper.py:231-263 get_zvals_from_near_far (+ :361-378 perturb_interval when u, the caller's uniforms, is given). */
+int arcb200_zvals_from_near_far(const float *near, const float *far, int n_pts, int inclusive, int inverse_linear,
+                                const float *u, float *zvals, int64_t n_rays, void *stream);
+/* ray_helper.py:266-315 get_zvals_from_near_far_fix_step (+ :381-407 perturb_interval_with_mask when u is given). */
+int arcb200_zvals_fix_step(const float *near, const float *far, float fix_t, int n_pts, int inclusive, const float *u,
+                           float *zvals, uint8_t *mask, int64_t n_rays, void *stream);
+/* arcnerf/geometry/ray.py:11-30 get_ray_points_by_zvals. */
+int arcb200_ray_points(const float *rays_o, const float *rays_d, const float *zvals, float *pts, int64_t n_rays, int n_pts,
+                       void *stream);
+/* torch.sort(torch.cat([zvals, new_zvals], -1), -1) of NeRF/NeuS upsample_zvals (nerf_model.py:112, neus_model.py:171):
+ * ascending sort of every row, n <= 8192, out may alias in. */
+int arcb200_sort_rows(const float *in, float *out, int64_t n_rows, int n, void *stream);
+
 /* ---------------------------------------------------------------- data-parallel step over peer memory ----
  * Replaces, for one node, what the reference gets from torch DDP + torch.optim.Adam: the bucketed all-reduce of the
  * gradients hooked into backward (common/trainer/basic_trainer.py:192-202, set_model_to_ddp) followed by the same

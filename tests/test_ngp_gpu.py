@@ -139,3 +139,34 @@ def test_graph_replay_and_sampler_prefetch_equal_eager_steps():
         for a, b in zip(other[2:5], ref[2:5]):
             err = (a - b).abs()
             assert float((err > 2e-3).float().mean()) < 5e-3        # Adam sign flips at the noise floor only
+
+
+def test_occupancy_refresh_through_volume_bound():
+    """FgModel.optimize path: the pipeline's density query feeds VolumeBound.optimize, the refreshed bool volume is what the
+    sampler marches through afterwards (fg_model.py:400-410, volume_bound.py:160-212)."""
+    from arcnerf_b200 import synth
+    from arcnerf_b200.ngp import NGP_DEFAULTS, NGPPipeline, init_params
+    params = init_params(dict(NGP_DEFAULTS), seed=5, grid_scale=0.5)
+    pipe = NGPPipeline(max_rays=512, capacity=1 << 16, params=params)
+    pts = (torch.rand((3000, 3), device='cuda') - 0.5) * 1.9
+    sig = pipe.forward_pts(pts, chunk=1024)
+    sig_all = pipe.forward_pts(pts)
+    assert sig.shape == (3000,) and torch.equal(sig, sig_all) and bool((sig > 0).all())
+    assert torch.allclose(pipe.get_est_opacity(0.01, pts), sig * 0.01)
+    assert bool(pipe.volume.all())
+    pipe.update_occupancy(5)                       # not a refresh step
+    assert bool(pipe.volume.all())
+    pipe.update_occupancy(16)                      # warm-up refresh over all 128^3 voxels
+    occ = float(pipe.volume.float().mean())
+    vol = pipe.bound.volume
+    dens = pipe.forward_pts(vol.get_volume_pts()).view(128, 128, 128)
+    dt = vol.get_diag_len() / pipe.cfg['n_sample']
+    thres = min(float(vol.get_voxel_opafield().clamp(min=0).mean()), 0.01)
+    assert torch.equal(pipe.volume, vol.get_voxel_opafield() >= thres)
+    # jittered sample vs voxel centre: the two occupancy estimates agree on most voxels
+    agree = float(((dens * dt >= thres) == pipe.volume).float().mean())
+    assert agree > 0.55 and 0.0 < occ <= 1.0      # random-init field: sub-voxel noise, but clearly better than chance
+    o, d = synth.train_ray_batch(512, seed=9)
+    t = torch.rand((512, 3), device='cuda')
+    loss = pipe.train_step(torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda(), t)
+    assert torch.isfinite(loss).all()
