@@ -60,12 +60,16 @@ _SIGS = {
     'arcb200_sample_cdf': [P, P, P, I, F, P, L, I, I, P],
     'arcb200_trunc_exp_fwd': [P, I, L, P, L, P, P],
     'arcb200_trunc_exp_bwd': [P, I, L, P, F, P, L, P, P],
+    'arcb200_world_to_unit': [P, P, P, L, P],
     'arcb200_geo_head_grad': [P, I, L, P, F, P, I, L, I, P, L, P, P],
     'arcb200_adam_step': [P, P, P, P, P, L, I, F, F, F, F, F, F, I, P, P],
     'arcb200_counter_add': [P, I, P],
     'arcb200_fill_f32': [P, F, L, P],
     'arcb200_huber_loss': [P, P, F, F, P, P, L, P],
     'arcb200_mlp_adam_pack': [I, P, P, P, P, P, I, P, I, F, F, F, F, F, F, I, P, P],
+    'arcb200_volume_refresh_scratch_bytes': [I],
+    'arcb200_volume_refresh_candidates': [P, I, L, L, C.c_uint32, U64, U64, P, P, P, P, P],
+    'arcb200_volume_refresh_apply': [P, P, L, F, F, I, P, P, P, P],
     'arcb200_sphere_ray_intersection': [P, P, P, P, P, P, P, P, L, L, P],
     'arcb200_zvals_from_near_far': [P, P, I, I, I, P, P, L, P],
     'arcb200_zvals_fix_step': [P, P, F, I, I, P, P, P, L, P],
@@ -86,6 +90,7 @@ _RESTYPE = {
     'arcb200_march_packed_static_max_slots': L,
     'arcb200_grid_geometry': L,
     'arcb200_mlp_act_save_bytes': L,
+    'arcb200_volume_refresh_scratch_bytes': L,
 }
 
 _lib = None

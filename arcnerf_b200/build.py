@@ -31,6 +31,7 @@ SOURCES = {
     'noalloc.cu': [],
     'peer.cu': [],
     'zvals.cu': ['-fmad=false'],
+    'volume_refresh.cu': [],
 }
 
 

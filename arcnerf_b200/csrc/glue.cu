@@ -52,6 +52,15 @@ __global__ void geo_head_grad_kernel(int64_t n, const int32_t *__restrict__ n_de
     }
 }
 
+// world position -> unit-cube coordinate of the hash grid: (p - min) / (max - min) per axis
+__global__ void world_to_unit_kernel(size_t n3, const float *__restrict__ pts, const float *__restrict__ aabb, float *__restrict__ unit) {
+    arc_pdl_sync();
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n3; i += (size_t)gridDim.x * blockDim.x) {
+        const int a = (int)(i % 3);
+        unit[i] = (pts[i] - aabb[a]) / (aabb[3 + a] - aabb[a]);
+    }
+}
+
 }  // namespace
 
 extern "C" {
@@ -95,6 +104,17 @@ int arcb200_geo_head_grad(const void *x0, int x_is_half, int64_t ldx, const floa
     if (x_is_half) { if (f_is_half) GO(__half, __half); else GO(__half, float); }
     else { if (f_is_half) GO(float, __half); else GO(float, float); }
 #undef GO
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// unit (n,3) = (pts - aabb_min) / (aabb_max - aabb_min); aabb (2,3) = min; max.  The normalisation the reference does
+// inside HashGridEmbedder.forward before calling tcnn (hashgrid_encoder.py:150-160); out may alias pts.
+int arcb200_world_to_unit(const float *pts, const float *aabb, float *unit, int64_t n, void *stream) {
+    ARC_REQUIRE(n >= 0, "world_to_unit: negative n");
+    if (n == 0) return ARCB200_OK;
+    ARC_REQUIRE(pts && aabb && unit, "world_to_unit: null pointer");
+    arc_launch(world_to_unit_kernel, stride_blocks(n * 3, 256), 256, 0, (cudaStream_t)stream, (size_t)n * 3, pts, aabb, unit);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }

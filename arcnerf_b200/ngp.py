@@ -227,16 +227,20 @@ class NGPPipeline:
     def forward_pts(self, pts, chunk=1 << 19):
         """Density at arbitrary world points (N,3) -> (N,): hash encode + geometry head with the TruncExp epilogue, in
         chunks (the reference's Base3dModel.forward_pts through chunk_processing, base_3d_model.py:343-366)."""
-        pts = pts.to(self.dev, torch.float32)
+        pts = pts.to(self.dev, torch.float32).contiguous()
         n = pts.shape[0]
         out = torch.empty((n, ), dtype=torch.float32, device=self.dev)
-        lo, side = self.aabb[0], self.aabb[1] - self.aabb[0]
+        m = min(n, chunk)
+        if getattr(self, '_pts_buf', None) is None or self._pts_buf[0].shape[0] < m:
+            self._pts_buf = (torch.empty((m, 3), dtype=torch.float32, device=self.dev),
+                             torch.empty((m, self.enc_dim), dtype=torch.float16, device=self.dev),
+                             torch.empty((m, self.cfg['w_feat']), dtype=torch.float16, device=self.dev))
+        unit, enc, feat = self._pts_buf
         for a in range(0, n, chunk):
             b = min(n, a + chunk)
-            unit = ((pts[a:b] - lo) / side).contiguous()
-            enc = F.grid_forward(unit, self.table_h, self.geom)
-            feat = torch.empty((b - a, self.cfg['w_feat']), dtype=torch.float16, device=self.dev)
-            F.mlp_forward(enc, self.geo_blob, self.geo_spec, out=feat, exp0_out=out[a:b])
+            _lib.call('arcb200_world_to_unit', pts[a:b].data_ptr(), self.aabb.data_ptr(), unit.data_ptr(), b - a, _lib.current_stream())
+            F.grid_forward(unit[:b - a], self.table_h, self.geom, out=enc[:b - a])
+            F.mlp_forward(enc[:b - a], self.geo_blob, self.geo_spec, out=feat[:b - a], exp0_out=out[a:b])
         return out
 
     @torch.no_grad()
@@ -252,9 +256,10 @@ class NGPPipeline:
             self.volume.copy_(bound.volume.get_voxel_bitfield())
 
     @torch.no_grad()
-    def update_occupancy(self, cur_epoch):
+    def update_occupancy(self, cur_epoch, apply=True):
         """FgModel.optimize (fg_model.py:400-410): obj_bound.optimize(cur_epoch, n_coarse_sample, get_est_opacity) every
-        `epoch_optim` steps; warm-up sweeps every voxel, afterwards 1/4 random + 1/4 occupied voxels."""
+        `epoch_optim` steps; warm-up sweeps every voxel, afterwards 1/4 random + 1/4 occupied voxels.
+        apply=False does all the work but leaves the sampler's volume as it is (benchmarks on a fixed synthetic scene)."""
         bound = getattr(self, 'bound', None)
         if bound is None:
             from .plugin.obj_bound import VolumeBound
@@ -263,12 +268,14 @@ class NGPPipeline:
                                      epoch_optim_warmup=cfg.get('epoch_optim_warmup', 256), ray_sample_acc=True,
                                      ray_sample_fix_step=True, near_distance=cfg['near_distance'],
                                      opa_thres=cfg.get('opa_thres', 0.01)))
-            self.attach_bound(bound)
+            self.bound = bound.to(self.dev)
+            self.bound.volume.bitfield.copy_(self.volume)          # the bound starts from the occupancy in use
             bound = self.bound
         bound.optimize(cur_epoch, self.cfg['n_sample'], self.get_est_opacity)
-        self.volume.copy_(bound.volume.get_voxel_bitfield())
-        for ss in self.sets:                    # a prefetched sample set was marched through the old occupancy
-            ss.key = None
+        if apply:
+            self.volume.copy_(bound.volume.get_voxel_bitfield())
+            for ss in self.sets:                # a prefetched sample set was marched through the old occupancy
+                ss.key = None
 
     # ------------------------------------------------------------------------------------------ stages
     def _sample_into(self, ss, rays_o, rays_d):

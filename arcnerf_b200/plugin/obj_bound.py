@@ -174,12 +174,18 @@ class VolumeBound(BasicBound):
     def optimize(self, cur_epoch=0, n_pts=128, get_est_opacity=None):
         """volume_bound.py:160-212.  Warm-up: every voxel; afterwards 1/4 random voxels + the first 1/4 occupied ones.
         One jittered point per chosen voxel -> opacity -> per-voxel max -> decayed-max update of the opacity field ->
-        occupancy = opacity >= min(mean, threshold)."""
+        occupancy = opacity >= min(mean, threshold).
+        Default: the device path (csrc/volume_refresh.cu: no randperm / where / unique / host round trip).  With
+        `native_refresh: False` in the cfgs the selection and update are composed from torch ops in the reference's order."""
         epoch_optim = self.get_optim_cfgs('epoch_optim')
         epoch_optim_warmup = self.get_optim_cfgs('epoch_optim_warmup')
         if cur_epoch <= 0 or epoch_optim is None or cur_epoch % epoch_optim != 0:
             return
         vol = self.volume
+        if get_value_from_cfgs_field(self.cfgs, 'native_refresh', True) and vol.get_range().is_cuda:
+            warm = epoch_optim_warmup is not None and cur_epoch < epoch_optim_warmup
+            n_vox = vol.get_n_voxel()
+            return self._optimize_native(n_vox if warm else n_vox // 4, 0 if warm else n_vox // 4, n_pts, get_est_opacity)
         n_grid, dev = vol.get_n_grid(), vol.get_device()
         if epoch_optim_warmup is not None and cur_epoch < epoch_optim_warmup:
             flat_idx = torch.arange(vol.get_n_voxel(), dtype=torch.long, device=dev)
@@ -200,6 +206,47 @@ class VolumeBound(BasicBound):
         vol.update_opafield_by_voxel_idx(vol.convert_flatten_index_to_xyz_index(uni_flat, n_grid), uni_opa,
                                          ema=self.get_optim_cfgs('ema_optim_decay'))
         vol.update_bitfield_by_opafield(threshold=self.get_optim_cfgs('opa_thres'), ops='overwrite')
+
+
+    def _optimize_native(self, n_uniform, n_occ, n_pts, get_est_opacity):
+        from .. import _lib
+        vol = self.volume
+        n_grid, dev = vol.get_n_grid(), vol.get_device()
+        n_cand = n_uniform + n_occ
+        if getattr(self, '_refresh_scratch', None) is None or self._refresh_scratch.device != dev:
+            nbytes = _lib.load().arcb200_volume_refresh_scratch_bytes(int(n_grid))
+            self._refresh_scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            self._refresh_rng = _lib.Rng()
+            self._refresh_count = 0
+        if getattr(self, '_refresh_idx', None) is None or self._refresh_idx.shape[0] < n_cand:
+            self._refresh_idx = torch.empty((n_cand, ), dtype=torch.int32, device=dev)
+            self._refresh_pts = torch.empty((n_cand, 3), dtype=torch.float32, device=dev)
+        idx, pts = self._refresh_idx[:n_cand], self._refresh_pts[:n_cand]
+        bits = vol.get_voxel_bitfield()
+        if not bits.is_contiguous():
+            bits = bits.contiguous()
+        if getattr(self, '_refresh_aabb', None) is None or self._refresh_aabb.device != dev:
+            self._refresh_aabb = vol.get_range().t().contiguous()      # (2, 3): min; max
+        aabb = self._refresh_aabb
+        st = _lib.current_stream()
+        if n_uniform == vol.get_n_voxel() and n_occ == 0:
+            key = 0xffffffff                                           # warm-up: every voxel once (any permutation will do)
+        else:
+            key = (self._refresh_count * 2654435761) & 0xffffffff
+        r = self._refresh_rng
+        _lib.call('arcb200_volume_refresh_candidates', bits.data_ptr(), int(n_grid), n_uniform, n_occ, key, r.state, r.inc,
+                  aabb.data_ptr(), self._refresh_scratch.data_ptr(), idx.data_ptr(), pts.data_ptr(), st)
+        r.advance()
+        self._refresh_count += 1
+        dt = vol.get_diag_len() / float(n_pts)
+        opacity = get_est_opacity(dt, pts).float().contiguous()
+        ema = self.get_optim_cfgs('ema_optim_decay')
+        opa = vol.get_voxel_opafield()
+        _lib.call('arcb200_volume_refresh_apply', idx.data_ptr(), opacity.data_ptr(), n_cand, -1.0 if ema is None else float(ema),
+                  float(self.get_optim_cfgs('opa_thres')), int(n_grid), self._refresh_scratch.data_ptr(), opa.data_ptr(),
+                  bits.data_ptr(), st)
+        if bits.data_ptr() != vol.bitfield.data_ptr():
+            vol.bitfield.copy_(bits)
 
 
 @BOUND_REGISTRY.register()

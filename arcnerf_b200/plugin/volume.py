@@ -34,9 +34,13 @@ class Volume(nn.Module):
         self.origin.copy_(torch.tensor([float(origin[0]), float(origin[1]), float(origin[2])], dtype=self.dtype))
         lens = [float(side)] * 3 if side is not None else [float(x) for x in xyz_len]
         self.xyz_len.copy_(torch.tensor(lens, dtype=self.dtype))
+        # host copies of the box: the getters below are called every refresh and must not read device memory back
+        self._host_min = [float(origin[a]) - lens[a] / 2.0 for a in range(3)]
+        self._host_max = [float(origin[a]) + lens[a] / 2.0 for a in range(3)]
         self.set_pts()
 
     def set_pts(self):
+        self._diag_len = None
         self.cal_range()
         if self.n_grid is not None:
             self.cal_volume_pts()
@@ -65,13 +69,18 @@ class Volume(nn.Module):
         return self.range
 
     def get_diag_len(self):
-        return float(torch.sqrt(((self.range[:, 1] - self.range[:, 0]) ** 2).sum()))
+        """length of the box diagonal, evaluated like the reference (fp32 tensor arithmetic) but once, on the host"""
+        if getattr(self, '_diag_len', None) is None:
+            r = torch.tensor([self._host_min, self._host_max], dtype=self.dtype).t()
+            self._diag_len = float(torch.sqrt(((r[:, 1] - r[:, 0]) ** 2).sum()))
+        return self._diag_len
 
     def get_voxel_size(self, to_list=True):
-        xyz_s = (self.get_range()[:, 1] - self.get_range()[:, 0]) / self.n_grid
         if to_list:
+            r = torch.tensor([self._host_min, self._host_max], dtype=self.dtype).t()
+            xyz_s = (r[:, 1] - r[:, 0]) / self.n_grid
             return float(xyz_s[0]), float(xyz_s[1]), float(xyz_s[2])
-        return xyz_s
+        return (self.get_range()[:, 1] - self.get_range()[:, 0]) / self.n_grid
 
     def cal_volume_pts(self):
         """centres of all voxels, (n_grid**3, 3), x-major flat order (x*n*n + y*n + z)"""

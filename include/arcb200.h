@@ -309,6 +309,9 @@ int arcb200_trunc_exp_bwd(const void *x, int x_is_half, int64_t ldx, const float
 /* Gradient entering FusedMLPGeoNet's network from its two consumers (handle_output_combine,
  * tcnn_fusedmlp_module.py:99-111, differentiated): dY (n,width) fp32 = d_feat (optional) with channel 0 increased by
  * g_sigma * exp(clamp(x0)) where x0 is channel 0 of the stored head output. */
+/* unit (n,3) = (pts - aabb_min) / (aabb_max - aabb_min), aabb (2,3) = min; max: the normalisation in front of the hash
+ * grid (hashgrid_encoder.py:150-160).  unit may alias pts. */
+int arcb200_world_to_unit(const float *pts, const float *aabb, float *unit, int64_t n, void *stream);
 int arcb200_geo_head_grad(const void *x0, int x_is_half, int64_t ldx, const float *g_sigma, float clip,
                           const void *d_feat, int f_is_half, int64_t ldf, int width, float *dY, int64_t n,
                           const int32_t *n_dev, void *stream);
@@ -337,6 +340,21 @@ int arcb200_mlp_adam_pack(int n_mlps, const int *shapes, float *const *p, float 
 /* ImgLoss with HuberLoss (arcnerf/loss/img_loss.py:48-98): loss_sum[0] += weight * mean(huber), g_rgb = gradient. */
 int arcb200_huber_loss(const float *rgb, const float *target, float delta, float weight, float *g_rgb,
                        float *loss_sum, int64_t n_rays, void *stream);
+
+/* ---------------------------------------------------------------- occupancy refresh of the volume bound (a6) ----
+ * VolumeBound.optimize (obj_bound/volume_bound.py:160-212) + Volume.update_opafield_by_voxel_idx /
+ * update_bitfield_by_opafield (arcnerf/geometry/volume.py:983-1018) without torch.randperm / where / unique / host
+ * synchronisation.  candidates: n_uniform distinct voxels (keyed permutation of the flat index = sampling without
+ * replacement) + the first n_occ_max occupied voxels in flat order, one pcg32-jittered point each (idx -1 = unused
+ * slot); the caller evaluates opacity = density * dt at pts; apply: per-voxel max, opa = opa >= 0 ? max(opa*ema, new)
+ * : opa for the sampled voxels only, volume byte = opa >= min(mean(max(opa,0)), threshold).  scratch:
+ * arcb200_volume_refresh_scratch_bytes(n_grid), shared by both calls. */
+int64_t arcb200_volume_refresh_scratch_bytes(int n_grid);
+int arcb200_volume_refresh_candidates(const uint8_t *volume, int n_grid, int64_t n_uniform, int64_t n_occ_max,
+                                      uint32_t key, uint64_t rng_state, uint64_t rng_inc, const float *aabb, void *scratch,
+                                      int32_t *idx_out, float *pts_out, void *stream);
+int arcb200_volume_refresh_apply(const int32_t *idx, const float *opacity, int64_t n_cand, float ema, float threshold,
+                                 int n_grid, void *scratch, float *opafield, uint8_t *volume, void *stream);
 
 /* ---------------------------------------------------------------- depth samples around the march (a15) ----
  * arcnerf/geometry/ray.py:180-255 sphere_ray_intersection (near/far/pts/mask against n_r concentric spheres; used by

@@ -164,3 +164,83 @@ def test_bitfield_sphere_and_basic_bounds():
     zvals, none2 = bound.get_zvals_from_near_far(near, far, 64)
     assert none is None and none2 is None and torch.allclose(near.cpu(), T('nf_radius_near'), atol=2e-6)
     assert torch.allclose(zvals[:, 0:1], near) and torch.allclose(zvals[:, -1:], far)
+
+
+def test_native_volume_refresh_kernels():
+    """csrc/volume_refresh.cu: candidate selection (distinct random voxels + the first occupied ones in flat order, jittered
+    points inside their voxels) and the update rule against oracle/zvals.py:update_opafield (= the reference's Volume rule)."""
+    import ctypes as C
+    from arcnerf_b200 import _lib
+    n_grid = 24
+    n = n_grid ** 3
+    g = torch.Generator().manual_seed(3)
+    vol = (torch.rand((n, ), generator=g) < 0.2)
+    vol_d = vol.cuda().contiguous()
+    aabb = torch.tensor([[-1.0, -0.5, 0.0], [1.0, 1.5, 3.0]], device='cuda')
+    scratch = torch.empty(_lib.load().arcb200_volume_refresh_scratch_bytes(n_grid), dtype=torch.uint8, device='cuda')
+    n_uni, n_occ = n // 4, n // 4
+    idx = torch.empty((n_uni + n_occ, ), dtype=torch.int32, device='cuda')
+    pts = torch.empty((n_uni + n_occ, 3), dtype=torch.float32, device='cuda')
+    rng = _lib.Rng()
+    sets = []
+    for key in (1, 2):
+        _lib.call('arcb200_volume_refresh_candidates', vol_d.data_ptr(), n_grid, n_uni, n_occ, key, rng.state, rng.inc,
+                  aabb.data_ptr(), scratch.data_ptr(), idx.data_ptr(), pts.data_ptr(), _lib.current_stream())
+        torch.cuda.synchronize()
+        uni = idx[:n_uni].cpu().long()
+        assert int(uni.min()) >= 0 and int(uni.max()) < n and uni.unique().numel() == n_uni      # without replacement
+        occ_ref = torch.where(vol)[0][:n_occ]
+        occ = idx[n_uni:].cpu().long()
+        assert torch.equal(occ[:occ_ref.numel()], occ_ref) and bool((occ[occ_ref.numel():] == -1).all())
+        # every point lies inside its voxel
+        valid = idx.cpu() >= 0
+        v = idx.cpu().long()[valid]
+        cell = torch.stack([v // (n_grid * n_grid), (v // n_grid) % n_grid, v % n_grid], 1).float()
+        size = ((aabb[1] - aabb[0]) / n_grid).cpu()
+        lo = aabb[0].cpu() + cell * size
+        p = pts.cpu()[valid]
+        assert bool((p >= lo - 1e-5).all()) and bool((p <= lo + size + 1e-5).all())
+        frac = (p - lo) / size
+        assert 0.45 < float(frac.mean()) < 0.55 and float(frac.std()) > 0.25                     # jitter fills the voxel
+        sets.append(uni)
+    assert not torch.equal(sets[0], sets[1])                                                      # key changes the subset
+    # full sweep: a permutation of all voxels
+    idx_all = torch.empty((n, ), dtype=torch.int32, device='cuda')
+    pts_all = torch.empty((n, 3), dtype=torch.float32, device='cuda')
+    _lib.call('arcb200_volume_refresh_candidates', vol_d.data_ptr(), n_grid, n, 0, 7, rng.state, rng.inc, aabb.data_ptr(),
+              scratch.data_ptr(), idx_all.data_ptr(), pts_all.data_ptr(), _lib.current_stream())
+    assert torch.equal(torch.sort(idx_all.cpu().long())[0], torch.arange(n))
+    # update rule, duplicates included (max per voxel), frozen (negative) voxels kept
+    opa0 = (torch.rand((n_grid, n_grid, n_grid), generator=g) * 0.02 - 0.002)
+    cand = torch.randint(0, n, (5000, ), generator=g)
+    cand[::50] = -1
+    new = torch.rand((5000, ), generator=g) * 0.03
+    ok = cand >= 0
+    uni, inv = torch.unique(cand[ok], return_inverse=True)
+    mx = torch.zeros(uni.numel()).scatter_reduce(0, inv, new[ok], 'amax', include_self=False)
+    vidx = torch.stack([uni // (n_grid * n_grid), (uni // n_grid) % n_grid, uni % n_grid], 1)
+    opa_ref, bits_ref = oz.update_opafield(opa0, None, vidx, mx, 0.95, 0.01)
+    opa_d = opa0.cuda().contiguous()
+    bits_d = torch.zeros((n, ), dtype=torch.bool, device='cuda')
+    cand_d, new_d = cand.int().cuda(), new.cuda()
+    _lib.call('arcb200_volume_refresh_apply', cand_d.data_ptr(), new_d.data_ptr(), 5000, 0.95, 0.01, n_grid,
+              scratch.data_ptr(), opa_d.data_ptr(), bits_d.data_ptr(), _lib.current_stream())
+    assert torch.equal(opa_d.cpu(), opa_ref)
+    thres = min(float(opa_ref.clamp(min=0).mean()), 0.01)
+    near_thres = (opa_ref.view(-1) - thres).abs() < 1e-7                 # the mean is summed in a different order
+    assert torch.equal(bits_d.cpu()[~near_thres], bits_ref.view(-1)[~near_thres])
+
+
+def test_volume_bound_native_and_torch_refresh_agree():
+    from arcnerf_b200.plugin.obj_bound import VolumeBound
+    base = dict(volume=dict(n_grid=32, side=2.0), epoch_optim=16, epoch_optim_warmup=64, ray_sample_acc=True, opa_thres=0.01)
+    a = VolumeBound(dict(base)).cuda()
+    b = VolumeBound(dict(base, native_refresh=False)).cuda()
+    est = _density_sphere()
+    for ep in (16, 32, 64, 80, 96):
+        a.optimize(ep, 128, est)
+        b.optimize(ep, 128, est)
+    bits_a, bits_b = a.volume.get_voxel_bitfield(), b.volume.get_voxel_bitfield()
+    # same field, different random points: the two occupancies differ only in the shell of voxels cut by the surface
+    assert float((bits_a != bits_b).float().mean()) < 0.02
+    assert abs(float(bits_a.float().mean()) - float(bits_b.float().mean())) < 0.01
