@@ -278,6 +278,148 @@ composite_bwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
     }
 }
 
+// ------------------------------------------------------------------------------------------------ fused training pass
+// Forward compositing, the Huber image loss of the ray and the backward in ONE kernel (density input, radiance given):
+// the step's composite_fwd + huber_loss + composite_bwd.  Pass 1 is the forward kernel's loop (same accumulation order,
+// so rgb is bit-identical) and also records the chunk carries; the loss gradient of the ray's colour is formed in
+// registers; pass 2 is the backward kernel's reverse loop.  Semantics: ray_marching (ray_helper.py:476-593) ->
+// ImgLoss/HuberLoss (arcnerf/loss/img_loss.py:48-98) -> autograd.
+__global__ void __launch_bounds__(256)
+composite_train_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32_t dense_p, int64_t capacity,
+                       const int32_t *__restrict__ pmax_dev, const float *__restrict__ geo, const float *__restrict__ rad,
+                       const float *__restrict__ t, const float *__restrict__ noise, int add_inf_z, int white_bkg,
+                       const float *__restrict__ bkg, int bkg_per_ray, const float *__restrict__ target, float delta_h,
+                       float scale, float *__restrict__ rgb, float *__restrict__ g_rgb_out, float *__restrict__ loss_sum,
+                       float *__restrict__ d_geo, float *__restrict__ d_rad) {
+    arc_pdl_sync();
+    const uint32_t ray = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const uint32_t lane = threadIdx.x & 31u;
+    __shared__ float block_loss[8];
+    float my_loss = 0.0f;
+    if (ray < n_rays) {
+        const Seg sg = segment(ray, offsets, dense_p, capacity);
+        const int32_t n = sg.n;
+        const int32_t m = add_inf_z ? n : (n > 0 ? n - 1 : 0);
+        const int32_t pmax = offsets ? (pmax_dev ? *pmax_dev : -1) : dense_p;
+        const int32_t k_bkg = (n == pmax || add_inf_z || !offsets) ? (m > 0 ? m - 1 : 0) : m;
+
+        // pass 1: forward
+        const int32_t n_chunks = (m + 31) >> 5;
+        float carries[kMaxChunks / 32];
+        #pragma unroll
+        for (int q = 0; q < kMaxChunks / 32; ++q) carries[q] = 1.0f;
+        float carry = 1.0f, t_bkg = 1.0f;
+        float ar = 0.f, ag = 0.f, ab = 0.f, aw = 0.f;
+        Item cur = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, (int32_t)lane, n, m);
+        for (int32_t c = 0; c < n_chunks; ++c) {
+            const int32_t base = c << 5;
+            const int32_t i = base + (int32_t)lane;
+            const bool on = i < m;
+            const Item nxt = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, i + 32, n, m);
+            float delta, dens;
+            const float alpha = on ? item_alpha<false>(cur, i, n, delta, dens) : 0.0f;
+            const float f = on ? (1.0f - alpha + 1e-10f) : 1.0f;
+            const float incl = warp_prod_inclusive(f, lane);
+            float excl = __shfl_up_sync(ARC_FULL_MASK, incl, 1);
+            if (lane == 0) excl = 1.0f;
+            const float T = carry * excl;
+            const float w = alpha * T;
+            if (on) { ar = fmaf(w, cur.r, ar); ag = fmaf(w, cur.g, ag); ab = fmaf(w, cur.b, ab); aw += w; }
+            #pragma unroll
+            for (int q = 0; q < kMaxChunks / 32; ++q)
+                if ((c >> 5) == q && (int32_t)lane == (c & 31)) carries[q] = carry;
+            if (k_bkg >= base && k_bkg < base + 32) t_bkg = __shfl_sync(ARC_FULL_MASK, T, k_bkg - base);
+            carry *= __shfl_sync(ARC_FULL_MASK, incl, 31);
+            if (k_bkg == base + 32) t_bkg = carry;
+            cur = nxt;
+        }
+        ar = warp_sum(ar); ag = warp_sum(ag); ab = warp_sum(ab); aw = warp_sum(aw);
+        float b0 = 0.f, b1 = 0.f, b2 = 0.f;
+        if (bkg) {
+            const float *b = bkg + (bkg_per_ray ? 3 * (size_t)ray : 0);
+            b0 = b[0]; b1 = b[1]; b2 = b[2];
+            ar += t_bkg * b0; ag += t_bkg * b1; ab += t_bkg * b2;
+        } else if (white_bkg) {
+            ar += 1.0f - aw; ag += 1.0f - aw; ab += 1.0f - aw;
+        }
+        // Huber loss of this ray's colour and its gradient (every lane holds the same values)
+        float gr, gg, gb;
+        {
+            const float col[3] = {ar, ag, ab};
+            float gcol[3];
+            #pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const float d = col[k] - target[3 * (size_t)ray + k];
+                const float a = fabsf(d);
+                if (a < delta_h) { my_loss += 0.5f / delta_h * (a * a); gcol[k] = scale * d / delta_h; }
+                else { my_loss += a - 0.5f * delta_h; gcol[k] = scale * (d > 0.f ? 1.f : -1.f); }
+            }
+            gr = gcol[0]; gg = gcol[1]; gb = gcol[2];
+        }
+        if (lane == 0) {
+            if (rgb) { rgb[3 * (size_t)ray] = ar; rgb[3 * (size_t)ray + 1] = ag; rgb[3 * (size_t)ray + 2] = ab; }
+            if (g_rgb_out) { g_rgb_out[3 * (size_t)ray] = gr; g_rgb_out[3 * (size_t)ray + 1] = gg; g_rgb_out[3 * (size_t)ray + 2] = gb; }
+        }
+        float ga = 0.f, v_bkg = 0.f;
+        if (bkg) v_bkg = gr * b0 + gg * b1 + gb * b2;
+        else if (white_bkg) ga -= (gr + gg + gb);
+        const float bkg_term = t_bkg * v_bkg;
+
+        // pass 2: reverse, suffix sums of w_j * v_j
+        float suffix = 0.0f;
+        cur = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, ((n_chunks - 1) << 5) + (int32_t)lane, n, m);
+        for (int32_t c = n_chunks - 1; c >= 0; --c) {
+            const int32_t base = c << 5;
+            const int32_t i = base + (int32_t)lane;
+            const bool on = i < m;
+            const int64_t s = sg.start + i;
+            const Item nxt = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, i - 32, n, m);
+            float delta = 0.f, dens = 0.f;
+            const float alpha = on ? item_alpha<false>(cur, i, n, delta, dens) : 0.0f;
+            const float f = on ? (1.0f - alpha + 1e-10f) : 1.0f;
+            const float incl = warp_prod_inclusive(f, lane);
+            float excl = __shfl_up_sync(ARC_FULL_MASK, incl, 1);
+            if (lane == 0) excl = 1.0f;
+            float c0 = 1.0f;
+            #pragma unroll
+            for (int q = 0; q < kMaxChunks / 32; ++q)
+                if ((c >> 5) == q) c0 = __shfl_sync(ARC_FULL_MASK, carries[q], c & 31);
+            const float T = c0 * excl;
+            const float w = alpha * T;
+            float v = 0.f;
+            if (on) { v = gr * cur.r + gg * cur.g + gb * cur.b; v += 0.0f * cur.t0 + ga + 0.0f; }
+            float wv = w * v, sfx = wv;
+            #pragma unroll
+            for (int st = 1; st < 32; st <<= 1) {
+                const float dn = __shfl_down_sync(ARC_FULL_MASK, sfx, st);
+                if ((int)lane + st < 32) sfx += dn;
+            }
+            const float later = suffix + (sfx - wv);
+            if (on) {
+                const float tail = later + (i < k_bkg ? bkg_term : 0.0f);
+                const float d_alpha = T * v - tail / f;
+                d_geo[s] = dens > 0.0f ? d_alpha * delta * (1.0f - alpha) : 0.0f;
+                if (d_rad) { d_rad[3 * s] = w * gr; d_rad[3 * s + 1] = w * gg; d_rad[3 * s + 2] = w * gb; }
+            }
+            suffix += __shfl_sync(ARC_FULL_MASK, sfx, 0);
+            cur = nxt;
+        }
+        for (int32_t i = m + (int32_t)lane; i < n; i += 32) {
+            const int64_t s = sg.start + i;
+            d_geo[s] = 0.f;
+            if (d_rad) { d_rad[3 * s] = 0.f; d_rad[3 * s + 1] = 0.f; d_rad[3 * s + 2] = 0.f; }
+        }
+    }
+    // one atomic per CTA for the loss
+    if (lane == 0) block_loss[threadIdx.x >> 5] = my_loss;
+    __syncthreads();
+    if (threadIdx.x == 0 && loss_sum) {
+        float l = 0.f;
+        for (int w = 0; w < 8; ++w) l += block_loss[w];
+        if (l != 0.f) atomicAdd(loss_sum, l * scale);
+    }
+}
+
 // NeuS: alpha from SDF at interval mid points (arcnerf/models/neus_model.py:242-265), dense (R, P) inputs with
 // zvals (R, P+1):  a = (Phi(s*(f - slope*d/2)) - Phi(s*(f + slope*d/2)) + 1e-5) / (Phi(prev) + 1e-5), clipped.
 __global__ void sdf_to_alpha_kernel(int64_t n, int32_t p, const float *__restrict__ sdf,
@@ -421,6 +563,29 @@ int arcb200_composite_bwd(const int32_t *offsets, int dense_p, int64_t capacity,
         arc_launch(composite_bwd_kernel<false>, blocks, 256, 0, st, (uint32_t)n_rays, offsets, dense_p, capacity, pmax_dev, geo, rad,
                                                             t, noise, add_inf_z, white_bkg, bkg, bkg_per_ray, g_rgb,
                                                             g_depth, g_acc, g_w, d_geo, d_rad);
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// Fused training pass over the rays: rgb = composite(sigma, radiance, t) as arcb200_composite_fwd, loss_sum[0] += weight *
+// mean(huber_delta(rgb - target)) as arcb200_huber_loss, and d_geo / d_rad as arcb200_composite_bwd fed with that loss
+// gradient - one kernel instead of three (density input; rgb, g_rgb_out optional outputs).
+int arcb200_composite_huber_train(const int32_t *offsets, int dense_p, int64_t capacity, const int32_t *pmax_dev,
+                                  const float *geo, const float *rad, const float *t, const float *noise, int add_inf_z,
+                                  int white_bkg, const float *bkg, int bkg_per_ray, const float *target, float delta,
+                                  float weight, float *rgb, float *g_rgb_out, float *loss_sum, float *d_geo, float *d_rad,
+                                  int max_samples_per_ray, int64_t n_rays, void *stream) {
+    ARC_REQUIRE(n_rays >= 0 && n_rays < (1ll << 27), "composite_huber_train: n_rays out of range");
+    if (n_rays == 0) return ARCB200_OK;
+    ARC_REQUIRE(geo && rad && t && target && d_geo && delta > 0.f, "composite_huber_train: null input or non-positive delta");
+    ARC_REQUIRE(offsets || dense_p > 0, "composite_huber_train: need offsets or a positive dense_p");
+    if ((offsets ? max_samples_per_ray : dense_p) > kMaxChunks * 32) {
+        arcb200_set_error("composite_huber_train: at most %d samples per ray are supported", kMaxChunks * 32);
+        return ARCB200_ERR_LIMIT;
+    }
+    arc_launch(composite_train_kernel, arc_blocks(n_rays * 32, 256), 256, 0, (cudaStream_t)stream, (uint32_t)n_rays, offsets,
+               dense_p, capacity, pmax_dev, geo, rad, t, noise, add_inf_z, white_bkg, bkg, bkg_per_ray, target, delta,
+               weight / (float)(n_rays * 3), rgb, g_rgb_out, loss_sum, d_geo, d_rad);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }

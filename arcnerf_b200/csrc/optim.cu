@@ -15,14 +15,16 @@ __global__ void adam_kernel(size_t n, float *__restrict__ p, float *__restrict__
     if (step_dev) bias_from_step(h, max(*step_dev, 1));    // step count kept on the device (replayable launches)
     const size_t stride = (size_t)gridDim.x * blockDim.x;
     const size_t n4 = n / 4;
+    // p, m, v and g are touched exactly once per step: streaming (evict-first) loads and stores keep them from pushing
+    // the fp16 working copy - which the next forward gathers from - out of L2
     for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n4; k += stride) {
-        float4 pp = reinterpret_cast<float4 *>(p)[k], mm = reinterpret_cast<float4 *>(m)[k],
-               vv = reinterpret_cast<float4 *>(v)[k], gg = reinterpret_cast<float4 *>(g)[k];
+        float4 pp = __ldcs(reinterpret_cast<const float4 *>(p) + k), mm = __ldcs(reinterpret_cast<const float4 *>(m) + k),
+               vv = __ldcs(reinterpret_cast<const float4 *>(v) + k), gg = __ldcs(reinterpret_cast<const float4 *>(g) + k);
         adam_one(pp.x, mm.x, vv.x, gg.x, h); adam_one(pp.y, mm.y, vv.y, gg.y, h);
         adam_one(pp.z, mm.z, vv.z, gg.z, h); adam_one(pp.w, mm.w, vv.w, gg.w, h);
-        reinterpret_cast<float4 *>(p)[k] = pp;
-        reinterpret_cast<float4 *>(m)[k] = mm;
-        reinterpret_cast<float4 *>(v)[k] = vv;
+        __stcs(reinterpret_cast<float4 *>(p) + k, pp);
+        __stcs(reinterpret_cast<float4 *>(m) + k, mm);
+        __stcs(reinterpret_cast<float4 *>(v) + k, vv);
         if (zero_grad) reinterpret_cast<float4 *>(g)[k] = make_float4(0.f, 0.f, 0.f, 0.f);
         if (p_half) {
             __half2 a = __floats2half2_rn(pp.x, pp.y), b = __floats2half2_rn(pp.z, pp.w);

@@ -357,14 +357,16 @@ class NGPPipeline:
         self.composite(R, bkg)
         return self.rgb[:R], self.depth[:R], self.acc[:R]
 
-    def backward(self, rays_d, R, bkg):
+    def backward(self, rays_d, R, bkg, composite=True):
+        """backward of forward() from self.g_rgb (composite=False: d_sigma / d_rgb_s are already there)"""
         cfg, C, nd, st = self.cfg, self.capacity, self.n_dev, _lib.current_stream()
         bkg_per_ray = int(bkg is not None and bkg.shape[0] == R and R > 1)
-        self._run('composite_bwd', lambda: _lib.call(
-            'arcb200_composite_bwd', self.offsets.data_ptr(), 0, C, self.pmax.data_ptr(), self.sigma.data_ptr(), 0,
-            self.rgb_s.data_ptr(), self.t.data_ptr(), None, 0, 0, _lib.ptr(bkg), bkg_per_ray,
-            self.g_rgb.data_ptr(), None, None, None, self.d_sigma.data_ptr(), self.d_rgb_s.data_ptr(),
-            cfg['n_sample'], R, st))
+        if composite:
+            self._run('composite_bwd', lambda: _lib.call(
+                'arcb200_composite_bwd', self.offsets.data_ptr(), 0, C, self.pmax.data_ptr(), self.sigma.data_ptr(), 0,
+                self.rgb_s.data_ptr(), self.t.data_ptr(), None, 0, 0, _lib.ptr(bkg), bkg_per_ray,
+                self.g_rgb.data_ptr(), None, None, None, self.d_sigma.data_ptr(), self.d_rgb_s.data_ptr(),
+                cfg['n_sample'], R, st))
         self._run('mlp_rad_bwd', lambda: F.mlp_backward(self.rad_in, self.rad_blob, self.rad_spec, self.d_rgb_s,
                                                         dW=self.g_rad, dx=self.d_rad_in, n_dev=nd,
                                                         act_saved=self.rad_act, y_saved=self.rgb_s))
@@ -398,12 +400,10 @@ class NGPPipeline:
         next_rays = (rays_o, rays_d) of the following batch, if known: it is sampled on the side stream meanwhile
         (the sampler does not depend on the parameters being updated)."""
         R = rays_o.shape[0]
-        self.forward(rays_o, rays_d, bkg, next_rays=next_rays)
-        _lib.call('arcb200_fill_f32', self.loss.data_ptr(), 0.0, 1, _lib.current_stream())
-        self._run('huber_loss', lambda: _lib.call(
-            'arcb200_huber_loss', self.rgb.data_ptr(), target.data_ptr(), self.cfg['huber_delta'],
-            self.cfg['loss_weight'], self.g_rgb.data_ptr(), self.loss.data_ptr(), R, _lib.current_stream()))
-        self.backward(rays_d, R, bkg)
+        self.sample(rays_o, rays_d)
+        if next_rays is not None:
+            self.prefetch(*next_rays)
+        self._step_core(R, rays_d, target, bkg)
         if optimize:
             if self.world_size > 1:
                 self.exchange_and_step()
@@ -471,15 +471,23 @@ class NGPPipeline:
         return self.table
 
     # ------------------------------------------------------------------------------------------ replayed step
+    def _step_core(self, R, rays_d, target, bkg):
+        """field forward -> compositing + Huber loss + compositing backward (one kernel) -> field backward, on the current
+        sample set; fills self.rgb, self.g_rgb, self.loss and the flat gradient buffer"""
+        self.field_forward(rays_d)
+        st = _lib.current_stream()
+        _lib.call('arcb200_fill_f32', self.loss.data_ptr(), 0.0, 1, st)
+        bkg_per_ray = int(bkg is not None and bkg.shape[0] == R and R > 1)
+        self._run('composite_train', lambda: _lib.call(
+            'arcb200_composite_huber_train', self.offsets.data_ptr(), 0, self.capacity, self.pmax.data_ptr(),
+            self.sigma.data_ptr(), self.rgb_s.data_ptr(), self.t.data_ptr(), None, 0, 0, _lib.ptr(bkg), bkg_per_ray,
+            target.data_ptr(), self.cfg['huber_delta'], self.cfg['loss_weight'], self.rgb.data_ptr(), self.g_rgb.data_ptr(),
+            self.loss.data_ptr(), self.d_sigma.data_ptr(), self.d_rgb_s.data_ptr(), self.cfg['n_sample'], R, st))
+        self.backward(rays_d, R, bkg, composite=False)
+
     def _step_body(self, R, rays_d, target, bkg):
         """everything of a training step after the sampler, on the current sample set and the current stream"""
-        self.field_forward(rays_d)
-        self.composite(R, bkg)
-        _lib.call('arcb200_fill_f32', self.loss.data_ptr(), 0.0, 1, _lib.current_stream())
-        self._run('huber_loss', lambda: _lib.call(
-            'arcb200_huber_loss', self.rgb.data_ptr(), target.data_ptr(), self.cfg['huber_delta'],
-            self.cfg['loss_weight'], self.g_rgb.data_ptr(), self.loss.data_ptr(), R, _lib.current_stream()))
-        self.backward(rays_d, R, bkg)
+        self._step_core(R, rays_d, target, bkg)
         if self.world_size > 1:
             self.exchange_and_step()
         else:
@@ -597,5 +605,5 @@ class NGPPipeline:
 
     # number of library kernels one train_step enqueues (for bench.py's gpu_launches)
     LAUNCHES_FORWARD = 1 + 4 + 1 + 1 + 1 + 1 + 1      # aabb, march(4), grid, geo mlp (+density), sh, rad mlp, composite
-    LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1 + 1 + 1 + 1   # huber, comp bwd, rad bwd, geo bwd, grid bwd, step counter, table adam, heads adam+pack
+    LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1 + 1 + 1   # loss clear, (composite fused with loss + its backward), rad bwd, geo bwd, grid bwd, step counter, table adam, heads adam+pack
     LAUNCHES_TRAIN_PEER = LAUNCHES_TRAIN + 2           # + two flag barriers (the gradient clear is a memset, not a kernel of ours)

@@ -125,6 +125,8 @@ def stage_work(name, n_samples, n_rays, n_table_params, world=1):
         return 'hbm', 34.0 * n_table_params      # p,m,v,g read; p,m,v,g(=0) written; fp16 copy written
     if name == 'adam_table_peer':               # per rank: its 1/world slice; p,m,v in and out, `world` gradients in, `world` fp16 copies out
         return 'hbm', (24.0 + 6.0 * world) * n_table_params / world
+    if name == 'composite_train':                # sigma, rgb, t read (twice, second time from L1/L2); d_sigma, d_rgb written
+        return 'hbm', 36.0 * n_samples + 44.0 * n_rays
     if name == 'composite_fwd':
         return 'hbm', 20.0 * n_samples + 20.0 * n_rays
     if name == 'composite_bwd':

@@ -285,6 +285,13 @@ int arcb200_composite_bwd(const int32_t *offsets, int dense_p, int64_t capacity,
                           const float *g_depth, const float *g_acc, const float *g_w, float *d_geo, float *d_rad,
                           int max_samples_per_ray, int64_t n_rays, void *stream);
 
+/* Fused training pass: arcb200_composite_fwd (density input) -> arcb200_huber_loss -> arcb200_composite_bwd in one
+ * kernel; same arithmetic as the three calls.  rgb and g_rgb_out (n_rays,3) are optional outputs. */
+int arcb200_composite_huber_train(const int32_t *offsets, int dense_p, int64_t capacity, const int32_t *pmax_dev,
+                                  const float *geo, const float *rad, const float *t, const float *noise, int add_inf_z,
+                                  int white_bkg, const float *bkg, int bkg_per_ray, const float *target, float delta,
+                                  float weight, float *rgb, float *g_rgb_out, float *loss_sum, float *d_geo, float *d_rad,
+                                  int max_samples_per_ray, int64_t n_rays, void *stream);
 /* Replaces sdf_to_alpha (arcnerf/models/neus_model.py:242-265).  sdf, slope, alpha (n_rays,p); zvals (n_rays,p+1);
  * scale s from s_dev (device float) when not NULL, else s_host. */
 int arcb200_sdf_to_alpha(const float *sdf, const float *zvals, const float *slope, const float *s_dev, float s_host,

@@ -154,3 +154,55 @@ def test_sdf_to_alpha_and_sample_cdf(cuda):
     close(got, GOLD['pdf_samples'], atol=2e-5)
     u2 = u.expand(bins.shape[0], -1).contiguous()
     assert torch.equal(F.sample_cdf_gather(bins, cdf, u2), F.sample_cdf_gather(bins, cdf, u))
+
+
+@pytest.mark.parametrize('mode', ['packed_bkg', 'packed_white', 'dense'])
+def test_fused_composite_huber_train_equals_three_kernels(mode):
+    """arcb200_composite_huber_train == composite_fwd -> huber_loss -> composite_bwd, bit for bit (loss: atomics order)"""
+    from arcnerf_b200 import _lib
+    g = torch.Generator().manual_seed(17)
+    R = 777
+    if mode == 'dense':
+        P = 67
+        counts = torch.full((R, ), P, dtype=torch.int32)
+    else:
+        counts = torch.randint(0, 200, (R, ), generator=g, dtype=torch.int32)
+        counts[::13] = 0
+        counts[5] = 1
+        counts[7] = 199
+    offsets = torch.zeros(R + 1, dtype=torch.int32)
+    offsets[1:] = torch.cumsum(counts, 0)
+    N = int(offsets[-1])
+    t = torch.cat([torch.sort(2.0 + 4.0 * torch.rand(int(c), generator=g))[0] for c in counts]) if N else torch.zeros(0)
+    sigma = (torch.rand(N, generator=g) * 30.0 * (torch.rand(N, generator=g) > 0.4)).float()
+    rad = torch.rand((N, 3), generator=g)
+    target = torch.rand((R, 3), generator=g)
+    bkg = torch.rand((R, 3), generator=g) if mode == 'packed_bkg' else None
+    white = int(mode == 'packed_white')
+    dev = 'cuda'
+    off_d = offsets.to(dev) if mode != 'dense' else None
+    pmax = torch.tensor([int(counts.max())], dtype=torch.int32, device=dev)
+    sig_d, rad_d, t_d, tgt_d = sigma.to(dev), rad.to(dev), t.to(dev), target.to(dev)
+    bkg_d = bkg.to(dev) if bkg is not None else None
+    st = _lib.current_stream()
+    dense_p = P if mode == 'dense' else 0
+    rgb1, depth, acc = (torch.empty((R, 3), device=dev), torch.empty(R, device=dev), torch.empty(R, device=dev))
+    _lib.call('arcb200_composite_fwd', _lib.ptr(off_d), dense_p, N, pmax.data_ptr(), sig_d.data_ptr(), 0, rad_d.data_ptr(),
+              t_d.data_ptr(), None, 0, white, _lib.ptr(bkg_d), int(bkg is not None), rgb1.data_ptr(), depth.data_ptr(), acc.data_ptr(),
+              None, None, None, R, st)
+    loss1, g_rgb1 = torch.zeros(1, device=dev), torch.empty((R, 3), device=dev)
+    _lib.call('arcb200_huber_loss', rgb1.data_ptr(), tgt_d.data_ptr(), 0.1, 3000.0, g_rgb1.data_ptr(), loss1.data_ptr(), R, st)
+    dg1, dr1 = torch.full((N, ), 7.0, device=dev), torch.full((N, 3), 7.0, device=dev)
+    _lib.call('arcb200_composite_bwd', _lib.ptr(off_d), dense_p, N, pmax.data_ptr(), sig_d.data_ptr(), 0, rad_d.data_ptr(),
+              t_d.data_ptr(), None, 0, white, _lib.ptr(bkg_d), int(bkg is not None), g_rgb1.data_ptr(), None, None, None,
+              dg1.data_ptr(), dr1.data_ptr(), 256, R, st)
+    rgb2, g_rgb2, loss2 = torch.empty((R, 3), device=dev), torch.empty((R, 3), device=dev), torch.zeros(1, device=dev)
+    dg2, dr2 = torch.full((N, ), 9.0, device=dev), torch.full((N, 3), 9.0, device=dev)
+    _lib.call('arcb200_composite_huber_train', _lib.ptr(off_d), dense_p, N, pmax.data_ptr(), sig_d.data_ptr(), rad_d.data_ptr(),
+              t_d.data_ptr(), None, 0, white, _lib.ptr(bkg_d), int(bkg is not None), tgt_d.data_ptr(), 0.1, 3000.0, rgb2.data_ptr(),
+              g_rgb2.data_ptr(), loss2.data_ptr(), dg2.data_ptr(), dr2.data_ptr(), 256, R, st)
+    torch.cuda.synchronize()
+    assert torch.equal(rgb1, rgb2) and torch.equal(g_rgb1, g_rgb2)
+    assert torch.equal(dg1, dg2) and torch.equal(dr1, dr2)
+    assert abs(float(loss1) - float(loss2)) <= 2e-6 * abs(float(loss1))
+    assert float(dg2.abs().max()) > 0
