@@ -51,6 +51,7 @@ _SIGS = {
     'arcb200_mlp_fwd': [P, I, L, P, I, I, I, I, I, I, P, I, L, L, P, P],
     'arcb200_mlp_act_save_bytes': [L, I, I],
     'arcb200_mlp_fwd_ex': [P, I, L, P, I, I, I, I, I, I, P, I, L, P, P, L, P, P],
+    'arcb200_mlp_fwd_sh': [P, I, L, P, I, I, I, I, I, I, P, L, P, P, P, P, I, I, L, P, P],
     'arcb200_mlp_bwd_ex': [P, I, L, P, I, I, I, I, I, I, P, L, F, P, I, L, P, P, P, I, L, P, P, I, L, F, L, P, P],
     'arcb200_mlp_bwd': [P, I, L, P, I, I, I, I, I, I, P, L, F, P, I, L, P, L, P, P],
     'arcb200_composite_fwd': [P, I, L, P, P, I, P, P, P, I, I, P, I, P, P, P, P, P, P, L, P],

@@ -22,6 +22,7 @@
 #include "common.cuh"
 #include "tc05.cuh"
 #include "adam.cuh"
+#include "sh.cuh"
 #include <string.h>
 #include <stdlib.h>
 
@@ -233,6 +234,12 @@ struct Shared {
 struct FwdExtra {
     uint8_t *act_save;
     float *exp0_out;
+    // spherical-harmonics encoding of a per-row direction written into columns [sh_col, sh_col + 16) of the (fp16) output
+    // row: the geometry head then leaves the complete input row of the radiance head behind (no separate SH launch)
+    const float *sh_dirs;
+    const int32_t *sh_index;
+    int sh_col;
+    int sh_remap;
 };
 // Optional extras of the backward: saved hidden activations / outputs instead of re-computation, and an extra
 // gradient on output channel 0 that arrives through exp(): g0[row] * exp(clamp(x0[row], +-clip)).
@@ -296,6 +303,21 @@ mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
                 tc05::fence_after_sync();
                 issue_forward_mm(tmem, a_addr, w_addr + cfg.w_off[l], cfg.K[l], cfg.N[l]);
                 tc05::mma_commit(&sh->mbar_mma);
+            }
+            if (l == 0 && ex.sh_dirs && sizeof(TOUT) == 2 && grow < n) {
+                // while the first layer's MMAs run: degree-4 SH of this row's direction -> 16 fp16 values
+                const size_t src = ex.sh_index ? (size_t)__ldg(ex.sh_index + grow) : (size_t)grow;
+                float x = __ldg(ex.sh_dirs + 3 * src), y = __ldg(ex.sh_dirs + 3 * src + 1), z = __ldg(ex.sh_dirs + 3 * src + 2);
+                sh_input(x, y, z, ex.sh_remap);
+                float o[25];
+                sh_basis(x, y, z, 4, o);
+                uint4 w[2];
+                uint32_t *pw = reinterpret_cast<uint32_t *>(w);
+                #pragma unroll
+                for (int k = 0; k < 8; ++k) pw[k] = tc05::pack_half2(o[2 * k], o[2 * k + 1]);
+                uint4 *dst = reinterpret_cast<uint4 *>(reinterpret_cast<__half *>(Y) + grow * ldy + ex.sh_col);
+                dst[0] = w[0];
+                dst[1] = w[1];
             }
             tc05::mbar_wait(&sh->mbar_mma, phase);
             phase ^= 1u;
@@ -796,14 +818,16 @@ int arcb200_mlp_fwd(const void *X, int x_is_half, int64_t ldx, const void *blob,
 // As arcb200_mlp_fwd, plus: act_save (optional, arcb200_mlp_act_save_bytes(n,...) bytes, 16-byte aligned) receives the
 // hidden activations for arcb200_mlp_bwd_ex; exp0_out (optional, n floats) receives exp(output channel 0), taken from
 // the value as stored in Y (the density head's TruncExp forward, arcnerf/ops/trunc_exp.py:10-24).
-int arcb200_mlp_fwd_ex(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
-                       int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, void *act_save,
-                       float *exp0_out, int64_t n, const int32_t *n_dev, void *stream) {
+static int mlp_fwd_impl(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                        int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, FwdExtra fex, int64_t n,
+                        const int32_t *n_dev, void *stream) {
     ARC_REQUIRE(n >= 0, "mlp_fwd: negative n");
-    ARC_REQUIRE(((uintptr_t)act_save & 15u) == 0, "mlp_fwd: act_save must be 16-byte aligned");
-    FwdExtra fex;
-    fex.act_save = (uint8_t *)act_save;
-    fex.exp0_out = exp0_out;
+    ARC_REQUIRE(((uintptr_t)fex.act_save & 15u) == 0, "mlp_fwd: act_save must be 16-byte aligned");
+    if (fex.sh_dirs) {
+        ARC_REQUIRE(y_is_half && fex.sh_col >= out_dim && fex.sh_col + 16 <= ldy && (fex.sh_col * 2) % 16 == 0 &&
+                    (ldy * 2) % 16 == 0 && ((uintptr_t)Y & 15u) == 0,
+                    "mlp_fwd_sh: needs an fp16 output whose rows are 16-byte aligned and have room for 16 more columns at sh_col");
+    }
     if (n == 0) return ARCB200_OK;
     MlpCfg c;
     ARC_REQUIRE(make_cfg(c, in_dim, width, n_hidden, out_dim, hidden_act, out_act) >= 0, "mlp_fwd: unsupported shape");
@@ -835,6 +859,35 @@ int arcb200_mlp_fwd_ex(const void *X, int x_is_half, int64_t ldx, const void *bl
 #undef LAUNCH_FWD2
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
+}
+
+int arcb200_mlp_fwd_ex(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                       int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, void *act_save,
+                       float *exp0_out, int64_t n, const int32_t *n_dev, void *stream) {
+    FwdExtra fex;
+    memset(&fex, 0, sizeof(fex));
+    fex.act_save = (uint8_t *)act_save;
+    fex.exp0_out = exp0_out;
+    return mlp_fwd_impl(X, x_is_half, ldx, blob, in_dim, width, n_hidden, out_dim, hidden_act, out_act, Y, y_is_half, ldy, fex, n,
+                        n_dev, stream);
+}
+
+// As arcb200_mlp_fwd_ex with an fp16 output, plus the degree-4 spherical-harmonics encoding of a per-row direction
+// (dirs (n_dirs,3) fp32, row i uses dirs[index[i]] or dirs[i]) written to output columns [sh_col, sh_col+16): what
+// FusedMLPGeoNet followed by SHEmbedder and the `[feat, sh]` concatenation of fuse_radiance_inputs (mode 'fv',
+// encoder_mlp_network.py:93-118) leave behind, in one launch.  Same values as arcb200_sh_fwd(degree 4, remap).
+int arcb200_mlp_fwd_sh(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                       int out_dim, int hidden_act, int out_act, void *Y, int64_t ldy, void *act_save, float *exp0_out,
+                       const float *sh_dirs, const int32_t *sh_index, int sh_col, int sh_remap, int64_t n,
+                       const int32_t *n_dev, void *stream) {
+    ARC_REQUIRE(sh_dirs != nullptr, "mlp_fwd_sh: null direction pointer");
+    FwdExtra fex;
+    memset(&fex, 0, sizeof(fex));
+    fex.act_save = (uint8_t *)act_save;
+    fex.exp0_out = exp0_out;
+    fex.sh_dirs = sh_dirs; fex.sh_index = sh_index; fex.sh_col = sh_col; fex.sh_remap = sh_remap;
+    return mlp_fwd_impl(X, x_is_half, ldx, blob, in_dim, width, n_hidden, out_dim, hidden_act, out_act, Y, 1, ldy, fex, n, n_dev,
+                        stream);
 }
 
 // Backward.  dY (n, out_dim) fp32 (leading dimension ldy); dX (n, in_dim) fp32 or fp16 or NULL; dW: flat fp32

@@ -331,10 +331,13 @@ class NGPPipeline:
         # geometry head writes its W_feat outputs straight into the radiance input row; SH fills the rest
         # (the density sigma = TruncExp(channel 0) comes out of the same kernel's epilogue)
         tr = self.training
+        fuse_sh = self.cfg['sh_degree'] == 4
         self._run('mlp_geo_fwd', lambda: F.mlp_forward(self.enc, self.geo_blob, self.geo_spec, out=self.rad_in, out_col=0,
-                                                       n_dev=nd, act_save=self.geo_act if tr else None, exp0_out=self.sigma))
-        self._run('sh_fwd', lambda: F.sh_forward(rays_d, self.cfg['sh_degree'], index=self.ray_id, remap=True, out=self.rad_in,
-                                                 out_col=self.cfg['w_feat'], n_dev=nd))
+                                                       n_dev=nd, act_save=self.geo_act if tr else None, exp0_out=self.sigma,
+                                                       sh=(rays_d, self.ray_id, self.cfg['w_feat'], True) if fuse_sh else None))
+        if not fuse_sh:
+            self._run('sh_fwd', lambda: F.sh_forward(rays_d, self.cfg['sh_degree'], index=self.ray_id, remap=True, out=self.rad_in,
+                                                     out_col=self.cfg['w_feat'], n_dev=nd))
         self._run('mlp_rad_fwd', lambda: F.mlp_forward(self.rad_in, self.rad_blob, self.rad_spec, out=self.rgb_s, n_dev=nd,
                                                        act_save=self.rad_act if tr else None))
 
@@ -604,6 +607,6 @@ class NGPPipeline:
         return rgb, depth, acc
 
     # number of library kernels one train_step enqueues (for bench.py's gpu_launches)
-    LAUNCHES_FORWARD = 1 + 4 + 1 + 1 + 1 + 1 + 1      # aabb, march(4), grid, geo mlp (+density), sh, rad mlp, composite
+    LAUNCHES_FORWARD = 1 + 4 + 1 + 1 + 1 + 1          # aabb, march(4), grid, geo mlp (+density, +SH of the view direction), rad mlp, composite
     LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1 + 1 + 1   # loss clear, (composite fused with loss + its backward), rad bwd, geo bwd, grid bwd, step counter, table adam, heads adam+pack
     LAUNCHES_TRAIN_PEER = LAUNCHES_TRAIN + 2           # + two flag barriers (the gradient clear is a memset, not a kernel of ours)

@@ -245,6 +245,13 @@ int64_t arcb200_mlp_act_save_bytes(int64_t n, int width, int n_hidden);
 int arcb200_mlp_fwd_ex(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
                        int out_dim, int hidden_act, int out_act, void *Y, int y_is_half, int64_t ldy, void *act_save,
                        float *exp0_out, int64_t n, const int32_t *n_dev, void *stream);
+/* arcb200_mlp_fwd_ex with an fp16 output, plus the degree-4 SH encoding of a per-row direction (row i: dirs[index[i]] or
+ * dirs[i]) in output columns [sh_col, sh_col+16): FusedMLPGeoNet -> SHEmbedder (sh_encoder.py:104-123) -> the `[feat, sh]`
+ * concatenation of fuse_radiance_inputs (encoder_mlp_network.py:93-118) in one launch. */
+int arcb200_mlp_fwd_sh(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
+                       int out_dim, int hidden_act, int out_act, void *Y, int64_t ldy, void *act_save, float *exp0_out,
+                       const float *sh_dirs, const int32_t *sh_index, int sh_col, int sh_remap, int64_t n,
+                       const int32_t *n_dev, void *stream);
 /* Backward with extras.  act_saved: buffer written by arcb200_mlp_fwd_ex for the same X / weights / n - the forward is
  * then not re-computed, and y_saved (n,out_dim; fp16 if ys_is_half else fp32; leading dimension ldys) must hold the
  * network outputs whenever out_act != 0.  g0/x0: extra gradient on output channel 0 that arrives through exp():

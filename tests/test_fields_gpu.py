@@ -265,3 +265,28 @@ def test_mlp_saved_activations_and_density_extras(cuda, cfg, n):
     if oa != 'none':
         with pytest.raises(RuntimeError):
             F.mlp_backward(x, blob, spec, dy, act_saved=save)        # saved path needs the saved outputs
+
+
+def test_mlp_forward_with_fused_sh_equals_separate_launches(cuda):
+    """geometry head + SH of the per-row direction in one launch == mlp_forward followed by sh_forward"""
+    spec = F.MlpSpec(32, 64, 1, 16, 'relu', 'none')
+    rng = np.random.RandomState(8)
+    n, n_rays = 5000, 300
+    params = rand_params(rng, spec.n_params)
+    blob = F.mlp_pack(T(params, cuda), spec)
+    x = T(rng.uniform(-1, 1, (n, 32)).astype(np.float32), cuda, torch.float16)
+    dirs = rng.normal(size=(n_rays, 3)).astype(np.float32)
+    dirs /= np.linalg.norm(dirs, axis=1, keepdims=True)
+    dirs_d = T(dirs, cuda)
+    idx = T(rng.randint(0, n_rays, n).astype(np.int32), cuda)
+    a = torch.zeros((n, 32), dtype=torch.float16, device=cuda)
+    sig_a = torch.empty(n, device=cuda)
+    F.mlp_forward(x, blob, spec, out=a, exp0_out=sig_a)
+    F.sh_forward(dirs_d, 4, index=idx, remap=True, out=a, out_col=16)
+    b = torch.zeros((n, 32), dtype=torch.float16, device=cuda)
+    sig_b = torch.empty(n, device=cuda)
+    F.mlp_forward(x, blob, spec, out=b, exp0_out=sig_b, sh=(dirs_d, idx, 16, True))
+    assert torch.equal(a, b) and torch.equal(sig_a, sig_b)
+    assert float(b[:, 16:].float().abs().max()) > 0.1
+    with pytest.raises(RuntimeError):
+        F.mlp_forward(x, blob, spec, out=torch.zeros((n, 32), device=cuda), sh=(dirs_d, idx, 16, True))     # fp32 output
