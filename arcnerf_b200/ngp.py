@@ -216,6 +216,13 @@ class NGPPipeline:
     n_dev = property(lambda self: self.sets[self.cur].n_dev)
     pmax = property(lambda self: self.sets[self.cur].pmax)
 
+    def sync_params(self):
+        """Re-derive the fp16 hash table and the packed MLP operands from the fp32 masters (after an external optimiser or
+        a checkpoint load changed them; tcnn does this cast at every forward, tinycudann/modules.py:156)."""
+        F.cast_f16(self.table, self.table_h)
+        F.mlp_pack(self.geo_p, self.geo_spec, self.geo_blob)
+        F.mlp_pack(self.rad_p, self.rad_spec, self.rad_blob)
+
     def set_occupancy(self, volume_bool):
         """(n,n,n) bool occupancy (numpy or tensor), the VolumeBound bitfield."""
         v = torch.as_tensor(volume_bool).to(self.dev, torch.bool).contiguous()
@@ -360,7 +367,7 @@ class NGPPipeline:
         self.composite(R, bkg)
         return self.rgb[:R], self.depth[:R], self.acc[:R]
 
-    def backward(self, rays_d, R, bkg, composite=True):
+    def backward(self, rays_d, R, bkg, composite=True, g_depth=None, g_mask=None):
         """backward of forward() from self.g_rgb (composite=False: d_sigma / d_rgb_s are already there)"""
         cfg, C, nd, st = self.cfg, self.capacity, self.n_dev, _lib.current_stream()
         bkg_per_ray = int(bkg is not None and bkg.shape[0] == R and R > 1)
@@ -368,8 +375,8 @@ class NGPPipeline:
             self._run('composite_bwd', lambda: _lib.call(
                 'arcb200_composite_bwd', self.offsets.data_ptr(), 0, C, self.pmax.data_ptr(), self.sigma.data_ptr(), 0,
                 self.rgb_s.data_ptr(), self.t.data_ptr(), None, 0, 0, _lib.ptr(bkg), bkg_per_ray,
-                self.g_rgb.data_ptr(), None, None, None, self.d_sigma.data_ptr(), self.d_rgb_s.data_ptr(),
-                cfg['n_sample'], R, st))
+                self.g_rgb.data_ptr(), _lib.ptr(g_depth), _lib.ptr(g_mask), None, self.d_sigma.data_ptr(),
+                self.d_rgb_s.data_ptr(), cfg['n_sample'], R, st))
         self._run('mlp_rad_bwd', lambda: F.mlp_backward(self.rad_in, self.rad_blob, self.rad_spec, self.d_rgb_s,
                                                         dW=self.g_rad, dx=self.d_rad_in, n_dev=nd,
                                                         act_saved=self.rad_act, y_saved=self.rgb_s))
