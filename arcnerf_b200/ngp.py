@@ -251,6 +251,22 @@ class NGPPipeline:
         return out
 
     @torch.no_grad()
+    def density_grid(self, n_grid, x_range=None, slab=16):
+        """Density at the voxel centres of an n_grid^3 lattice over the bounding box (the grid a mesh extraction runs
+        marching cubes on: Volume.get_volume_pts -> forward_pts, base_3d_model.py:343-366), for x slabs
+        [x_range[0], x_range[1]) -> (nx, n_grid, n_grid) fp32.  Ranks take disjoint slabs (dist.shard_range) and gather."""
+        x0, x1 = x_range if x_range is not None else (0, n_grid)
+        out = torch.empty((x1 - x0, n_grid, n_grid), dtype=torch.float32, device=self.dev)
+        lo, side = self.aabb[0], self.aabb[1] - self.aabb[0]
+        vs = side / n_grid
+        ax = [lo[a] + (torch.arange(n_grid, device=self.dev, dtype=torch.float32) + 0.5) * vs[a] for a in range(3)]
+        for a in range(x0, x1, slab):
+            b = min(x1, a + slab)
+            pts = torch.stack(torch.meshgrid(ax[0][a:b], ax[1], ax[2], indexing='ij'), -1).reshape(-1, 3)
+            out[a - x0:b - x0] = self.forward_pts(pts).view(b - a, n_grid, n_grid)
+        return out
+
+    @torch.no_grad()
     def get_est_opacity(self, dt, pts):
         """base_3d_model.py:368-389: opacity = density * dt (the instant-ngp convention)"""
         return self.forward_pts(pts) * dt
