@@ -632,4 +632,5 @@ class NGPPipeline:
     # number of library kernels one train_step enqueues (for bench.py's gpu_launches)
     LAUNCHES_FORWARD = 1 + 4 + 1 + 1 + 1 + 1          # aabb, march(4), grid, geo mlp (+density, +SH of the view direction), rad mlp, composite
     LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1 + 1 + 1   # loss clear, (composite fused with loss + its backward), rad bwd, geo bwd, grid bwd, step counter, table adam, heads adam+pack
+    LAUNCHES_REFRESH = 4 + 2 * 3 + 4                   # candidates (count, scan, select, points), 2 chunks x (unit, grid, geo mlp), apply (fill, splat, ema, threshold)
     LAUNCHES_TRAIN_PEER = LAUNCHES_TRAIN + 2           # + two flag barriers (the gradient clear is a memset, not a kernel of ours)

@@ -398,10 +398,14 @@ def main():
         orc.set_occupancy(synth.occupancy_volume('lego'))
         o, d, t, b = (x.numpy()[:args.ref_rays] for x in host[0])
         orc.train_step(o, d, t, b)                        # warm-up (page faults, Adam state)
-        n_cpu = 2
+        # about 12 s of CPU work: time one step, then run as many more as fit (bounded between 4 and 60 steps)
         t0 = time.perf_counter()
-        for i in range(n_cpu):
-            o, d, t, b = (x.numpy()[:args.ref_rays] for x in host[1 + i])
+        o, d, t, b = (x.numpy()[:args.ref_rays] for x in host[1])
+        orc.train_step(o, d, t, b)
+        one = time.perf_counter() - t0
+        n_cpu = int(min(60, max(4, 12.0 / max(one, 1e-3))))
+        for i in range(1, n_cpu):
+            o, d, t, b = (x.numpy()[:args.ref_rays] for x in host[(1 + i) % len(host)])
             orc.train_step(o, d, t, b)
         dt = time.perf_counter() - t0
         cpu_baseline = dict(value=args.ref_rays * n_cpu / dt, unit=UNIT, cores=threads, kind='port',
@@ -422,7 +426,8 @@ def main():
                         occupancy_refresh=('every %d steps inside the timed region: 524288 + 524288 voxels of 128^3 re-evaluated (steady-state VolumeBound.optimize), result not applied to the synthetic scene' % occ_every) if occ_every > 0 else 'off',
                         parallelism='dp%d' % world, gradient_exchange=EXCHANGE_NOTE[pipe.exchange]),
             e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=4, ms_per_step=ms_e2e / K, path=e2e_mode),
-            gpu_launches=(NGPPipeline.LAUNCHES_TRAIN_PEER if pipe.exchange == 'peer' else NGPPipeline.LAUNCHES_TRAIN) * K,
+            gpu_launches=(NGPPipeline.LAUNCHES_TRAIN_PEER if pipe.exchange == 'peer' else NGPPipeline.LAUNCHES_TRAIN) * K
+            + (NGPPipeline.LAUNCHES_REFRESH * (K // occ_every) if occ_every > 0 else 0),
             clocks=clock_info, roofline=roofline, cpu_baseline=cpu_baseline,
             render_ms_800x800=render_ms,
         )
