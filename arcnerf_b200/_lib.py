@@ -51,12 +51,12 @@ _SIGS = {
     'arcb200_mlp_fwd': [P, I, L, P, I, I, I, I, I, I, P, I, L, L, P, P],
     'arcb200_mlp_act_save_bytes': [L, I, I],
     'arcb200_mlp_fwd_ex': [P, I, L, P, I, I, I, I, I, I, P, I, L, P, P, L, P, P],
-    'arcb200_mlp_fwd_sh': [P, I, L, P, I, I, I, I, I, I, P, L, P, P, P, P, I, I, L, P, P],
+    'arcb200_mlp_fwd_sh': [P, I, L, P, I, I, I, I, I, I, P, L, P, P, P, P, I, I, P, L, P, P],
     'arcb200_mlp_bwd_ex': [P, I, L, P, I, I, I, I, I, I, P, L, F, P, I, L, P, P, P, I, L, P, P, I, L, F, L, P, P],
     'arcb200_mlp_bwd': [P, I, L, P, I, I, I, I, I, I, P, L, F, P, I, L, P, L, P, P],
     'arcb200_composite_fwd': [P, I, L, P, P, I, P, P, P, I, I, P, I, P, P, P, P, P, P, L, P],
     'arcb200_composite_bwd': [P, I, L, P, P, I, P, P, P, I, I, P, I, P, P, P, P, P, P, I, L, P],
-    'arcb200_composite_huber_train': [P, I, L, P, P, P, P, P, I, I, P, I, P, F, F, P, P, P, P, P, I, L, P],
+    'arcb200_composite_huber_train': [P, I, L, P, P, P, P, P, I, I, P, I, P, F, F, P, P, P, P, P, P, I, L, P],
     'arcb200_sdf_to_alpha': [P, P, P, P, F, I, P, L, I, P],
     'arcb200_sdf_to_alpha_bwd': [P, P, P, P, F, I, P, P, P, P, L, I, P],
     'arcb200_sample_cdf': [P, P, P, I, F, P, L, I, I, P],

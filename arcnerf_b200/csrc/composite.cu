@@ -290,8 +290,9 @@ composite_train_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int
                        const float *__restrict__ t, const float *__restrict__ noise, int add_inf_z, int white_bkg,
                        const float *__restrict__ bkg, int bkg_per_ray, const float *__restrict__ target, float delta_h,
                        float scale, float *__restrict__ rgb, float *__restrict__ g_rgb_out, float *__restrict__ loss_sum,
-                       float *__restrict__ d_geo, float *__restrict__ d_rad) {
+                       float *__restrict__ d_geo, float *__restrict__ d_rad, int32_t *__restrict__ step_counter) {
     arc_pdl_sync();
+    if (step_counter && blockIdx.x == 0 && threadIdx.x == 0) *step_counter += 1;    // device-resident optimiser step count
     const uint32_t ray = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31u;
     __shared__ float block_loss[8];
@@ -569,12 +570,13 @@ int arcb200_composite_bwd(const int32_t *offsets, int dense_p, int64_t capacity,
 
 // Fused training pass over the rays: rgb = composite(sigma, radiance, t) as arcb200_composite_fwd, loss_sum[0] += weight *
 // mean(huber_delta(rgb - target)) as arcb200_huber_loss, and d_geo / d_rad as arcb200_composite_bwd fed with that loss
-// gradient - one kernel instead of three (density input; rgb, g_rgb_out optional outputs).
+// gradient - one kernel instead of three (density input; rgb, g_rgb_out optional outputs).  step_counter (optional device
+// int32) is incremented once: the optimiser step count that arcb200_adam_step reads through step_dev.
 int arcb200_composite_huber_train(const int32_t *offsets, int dense_p, int64_t capacity, const int32_t *pmax_dev,
                                   const float *geo, const float *rad, const float *t, const float *noise, int add_inf_z,
                                   int white_bkg, const float *bkg, int bkg_per_ray, const float *target, float delta,
                                   float weight, float *rgb, float *g_rgb_out, float *loss_sum, float *d_geo, float *d_rad,
-                                  int max_samples_per_ray, int64_t n_rays, void *stream) {
+                                  int32_t *step_counter, int max_samples_per_ray, int64_t n_rays, void *stream) {
     ARC_REQUIRE(n_rays >= 0 && n_rays < (1ll << 27), "composite_huber_train: n_rays out of range");
     if (n_rays == 0) return ARCB200_OK;
     ARC_REQUIRE(geo && rad && t && target && d_geo && delta > 0.f, "composite_huber_train: null input or non-positive delta");
@@ -585,7 +587,7 @@ int arcb200_composite_huber_train(const int32_t *offsets, int dense_p, int64_t c
     }
     arc_launch(composite_train_kernel, arc_blocks(n_rays * 32, 256), 256, 0, (cudaStream_t)stream, (uint32_t)n_rays, offsets,
                dense_p, capacity, pmax_dev, geo, rad, t, noise, add_inf_z, white_bkg, bkg, bkg_per_ray, target, delta,
-               weight / (float)(n_rays * 3), rgb, g_rgb_out, loss_sum, d_geo, d_rad);
+               weight / (float)(n_rays * 3), rgb, g_rgb_out, loss_sum, d_geo, d_rad, step_counter);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }

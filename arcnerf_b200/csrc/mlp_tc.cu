@@ -240,6 +240,7 @@ struct FwdExtra {
     const int32_t *sh_index;
     int sh_col;
     int sh_remap;
+    float *zero_scalar;      // optional: one float cleared by this launch (the step's loss accumulator)
 };
 // Optional extras of the backward: saved hidden activations / outputs instead of re-computation, and an extra
 // gradient on output channel 0 that arrives through exp(): g0[row] * exp(clamp(x0[row], +-clip)).
@@ -280,6 +281,7 @@ mlp_fwd_kernel(int64_t n, const int32_t *__restrict__ n_dev, const TIN *__restri
     tc05::fence_after_sync();
     arc_pdl_sync();      // barriers and tensor memory are set up; from here on inputs of earlier kernels are read
     if (n_dev) { const int64_t nd = *n_dev; n = nd < n ? (nd > 0 ? nd : 0) : n; }
+    if (ex.zero_scalar && blockIdx.x == 0 && tid == 0) *ex.zero_scalar = 0.0f;
     const uint32_t tmem = sh->tmem_base;
     if (tid == 0) {
         tc05::mbar_expect_tx(&sh->mbar_w, cfg.w_bytes);
@@ -873,19 +875,21 @@ int arcb200_mlp_fwd_ex(const void *X, int x_is_half, int64_t ldx, const void *bl
 }
 
 // As arcb200_mlp_fwd_ex with an fp16 output, plus the degree-4 spherical-harmonics encoding of a per-row direction
-// (dirs (n_dirs,3) fp32, row i uses dirs[index[i]] or dirs[i]) written to output columns [sh_col, sh_col+16): what
+// (dirs (n_dirs,3) fp32, row i uses dirs[index[i]] or dirs[i]) written to output columns [sh_col, sh_col+16) (and,
+// optionally, one float cleared: the loss accumulator that a later kernel of the step adds into): what
 // FusedMLPGeoNet followed by SHEmbedder and the `[feat, sh]` concatenation of fuse_radiance_inputs (mode 'fv',
 // encoder_mlp_network.py:93-118) leave behind, in one launch.  Same values as arcb200_sh_fwd(degree 4, remap).
 int arcb200_mlp_fwd_sh(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
                        int out_dim, int hidden_act, int out_act, void *Y, int64_t ldy, void *act_save, float *exp0_out,
-                       const float *sh_dirs, const int32_t *sh_index, int sh_col, int sh_remap, int64_t n,
-                       const int32_t *n_dev, void *stream) {
+                       const float *sh_dirs, const int32_t *sh_index, int sh_col, int sh_remap, float *zero_scalar,
+                       int64_t n, const int32_t *n_dev, void *stream) {
     ARC_REQUIRE(sh_dirs != nullptr, "mlp_fwd_sh: null direction pointer");
     FwdExtra fex;
     memset(&fex, 0, sizeof(fex));
     fex.act_save = (uint8_t *)act_save;
     fex.exp0_out = exp0_out;
     fex.sh_dirs = sh_dirs; fex.sh_index = sh_index; fex.sh_col = sh_col; fex.sh_remap = sh_remap;
+    fex.zero_scalar = zero_scalar;
     return mlp_fwd_impl(X, x_is_half, ldx, blob, in_dim, width, n_hidden, out_dim, hidden_act, out_act, Y, 1, ldy, fex, n, n_dev,
                         stream);
 }

@@ -171,7 +171,8 @@ def mlp_act_save_buffer(n, spec, device):
 def mlp_forward(x, blob, spec, out_dtype=torch.float32, out=None, out_col=0, n_dev=None, act_save=None, exp0_out=None,
                 sh=None):
     """sh = (dirs (n_dirs,3) fp32, index (N,) int32 | None, column, remap): also write the degree-4 SH encoding of each row's
-    direction into `out[:, column:column+16]` (fp16 `out` only) - the radiance head's `[feat, sh]` input in one launch"""
+    direction into `out[:, column:column+16]` (fp16 `out` only) - the radiance head's `[feat, sh]` input in one launch; an
+    optional fifth element is a 1-element float tensor that the launch clears (the step's loss accumulator)"""
     _cuda(x, 'x'), _cuda(blob, 'blob')
     if x.dtype not in (torch.float16, torch.float32) or x.dim() != 2 or x.shape[1] < spec.in_dim or x.stride(1) != 1:
         raise RuntimeError('x must be (N, >=%d) float16/float32 with unit column stride' % spec.in_dim)
@@ -179,12 +180,13 @@ def mlp_forward(x, blob, spec, out_dtype=torch.float32, out=None, out_col=0, n_d
     if out is None:
         out = torch.empty((n, spec.out_dim), dtype=out_dtype, device=x.device)
     if sh is not None:
-        dirs, index, col, remap = sh
+        dirs, index, col, remap = sh[:4]
+        zero_scalar = sh[4] if len(sh) > 4 else None
         if out.dtype != torch.float16 or out_col != 0:
             raise RuntimeError('the fused SH encoding needs an fp16 output written from column 0')
         _lib.call('arcb200_mlp_fwd_sh', x.data_ptr(), int(x.dtype == torch.float16), x.stride(0), blob.data_ptr(), *spec.dims(),
                   spec.hidden_act, spec.out_act, out.data_ptr(), out.stride(0), _lib.ptr(act_save), _lib.ptr(exp0_out),
-                  dirs.data_ptr(), _lib.ptr(index), int(col), int(bool(remap)), n, _lib.ptr(n_dev), _stream())
+                  dirs.data_ptr(), _lib.ptr(index), int(col), int(bool(remap)), _lib.ptr(zero_scalar), n, _lib.ptr(n_dev), _stream())
         return out
     _lib.call('arcb200_mlp_fwd_ex', x.data_ptr(), int(x.dtype == torch.float16), x.stride(0), blob.data_ptr(), *spec.dims(),
               spec.hidden_act, spec.out_act, out.data_ptr() + out_col * out.element_size(),

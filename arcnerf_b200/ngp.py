@@ -347,7 +347,7 @@ class NGPPipeline:
             nxt.ready = torch.cuda.Event()
             nxt.ready.record()
 
-    def field_forward(self, rays_d):
+    def field_forward(self, rays_d, clear_loss=False):
         """encode -> geometry head -> density | [feat, SH] -> radiance head, on the packed samples"""
         C, nd = self.capacity, self.n_dev
         self._run('grid_fwd', lambda: F.grid_forward(self.unit, self.table_h, self.geom, n_dev=nd, out=self.enc))
@@ -357,7 +357,9 @@ class NGPPipeline:
         fuse_sh = self.cfg['sh_degree'] == 4
         self._run('mlp_geo_fwd', lambda: F.mlp_forward(self.enc, self.geo_blob, self.geo_spec, out=self.rad_in, out_col=0,
                                                        n_dev=nd, act_save=self.geo_act if tr else None, exp0_out=self.sigma,
-                                                       sh=(rays_d, self.ray_id, self.cfg['w_feat'], True) if fuse_sh else None))
+                                                       sh=(rays_d, self.ray_id, self.cfg['w_feat'], True, self.loss if clear_loss else None) if fuse_sh else None))
+        if clear_loss and not fuse_sh:
+            _lib.call('arcb200_fill_f32', self.loss.data_ptr(), 0.0, 1, _lib.current_stream())
         if not fuse_sh:
             self._run('sh_fwd', lambda: F.sh_forward(rays_d, self.cfg['sh_degree'], index=self.ray_id, remap=True, out=self.rad_in,
                                                      out_col=self.cfg['w_feat'], n_dev=nd))
@@ -403,11 +405,13 @@ class NGPPipeline:
                                                         g0=self.d_sigma, x0=self.rad_in, clip=cfg['trunc_exp_clip']))
         self._run('grid_bwd', lambda: F.grid_backward(self.unit, self.d_enc, self.geom, grad_table=self.g_table, n_dev=nd))
 
-    def optimizer_step(self):
+    def optimizer_step(self, counted=False):
+        """counted: the device step counter was already advanced by this step's compositing launch"""
         cfg = self.cfg
         self.step_count += 1
         gs = 1.0 / self.world_size
-        _lib.call('arcb200_counter_add', self.step_dev.data_ptr(), 1, _lib.current_stream())
+        if not counted:
+            _lib.call('arcb200_counter_add', self.step_dev.data_ptr(), 1, _lib.current_stream())
         kw = dict(beta1=cfg['beta1'], beta2=cfg['beta2'], eps=cfg['eps'], weight_decay=cfg['weight_decay'], grad_scale=gs,
                   step_dev=self.step_dev)
         self._run('adam_table', lambda: F.adam_step(self.table, self.m_table, self.v_table, self.g_table, self.step_count,
@@ -429,15 +433,15 @@ class NGPPipeline:
         self.sample(rays_o, rays_d)
         if next_rays is not None:
             self.prefetch(*next_rays)
-        self._step_core(R, rays_d, target, bkg)
+        self._step_core(R, rays_d, target, bkg, count_step=optimize)
         if optimize:
             if self.world_size > 1:
-                self.exchange_and_step()
+                self.exchange_and_step(counted=True)
             else:
-                self.optimizer_step()
+                self.optimizer_step(counted=True)
         return self.loss
 
-    def exchange_and_step(self):
+    def exchange_and_step(self, counted=False):
         """Data-parallel step on the mean gradient over ranks - what DDP + Adam deliver in the reference
         (common/trainer/basic_trainer.py:192-202).
         'peer': barrier, then one kernel per parameter vector that sums the peers' gradients over NVLink, applies Adam
@@ -447,12 +451,13 @@ class NGPPipeline:
         if self.exchange != 'peer':
             import torch.distributed as dist
             self._run('all_reduce', lambda: dist.all_reduce(self.g_all))
-            self.optimizer_step()
+            self.optimizer_step(counted)
             return
         from .peer import adam_step_peer
         cfg, ar, W = self.cfg, self.arena, self.world_size
         self.step_count += 1
-        _lib.call('arcb200_counter_add', self.step_dev.data_ptr(), 1, _lib.current_stream())
+        if not counted:
+            _lib.call('arcb200_counter_add', self.step_dev.data_ptr(), 1, _lib.current_stream())
         kw = dict(beta1=cfg['beta1'], beta2=cfg['beta2'], eps=cfg['eps'], weight_decay=cfg['weight_decay'],
                   grad_scale=1.0 / W, step_dev=self.step_dev)
         nt, ng = self.table.numel(), self.geo_p.numel()
@@ -497,27 +502,28 @@ class NGPPipeline:
         return self.table
 
     # ------------------------------------------------------------------------------------------ replayed step
-    def _step_core(self, R, rays_d, target, bkg):
+    def _step_core(self, R, rays_d, target, bkg, count_step=True):
         """field forward -> compositing + Huber loss + compositing backward (one kernel) -> field backward, on the current
-        sample set; fills self.rgb, self.g_rgb, self.loss and the flat gradient buffer"""
-        self.field_forward(rays_d)
+        sample set; fills self.rgb, self.g_rgb, self.loss and the flat gradient buffer.  The loss accumulator is cleared by
+        the geometry head's launch and the device step counter advanced by the compositing launch (no launches of their own)."""
+        self.field_forward(rays_d, clear_loss=True)
         st = _lib.current_stream()
-        _lib.call('arcb200_fill_f32', self.loss.data_ptr(), 0.0, 1, st)
         bkg_per_ray = int(bkg is not None and bkg.shape[0] == R and R > 1)
         self._run('composite_train', lambda: _lib.call(
             'arcb200_composite_huber_train', self.offsets.data_ptr(), 0, self.capacity, self.pmax.data_ptr(),
             self.sigma.data_ptr(), self.rgb_s.data_ptr(), self.t.data_ptr(), None, 0, 0, _lib.ptr(bkg), bkg_per_ray,
             target.data_ptr(), self.cfg['huber_delta'], self.cfg['loss_weight'], self.rgb.data_ptr(), self.g_rgb.data_ptr(),
-            self.loss.data_ptr(), self.d_sigma.data_ptr(), self.d_rgb_s.data_ptr(), self.cfg['n_sample'], R, st))
+            self.loss.data_ptr(), self.d_sigma.data_ptr(), self.d_rgb_s.data_ptr(),
+            self.step_dev.data_ptr() if count_step else None, self.cfg['n_sample'], R, st))
         self.backward(rays_d, R, bkg, composite=False)
 
     def _step_body(self, R, rays_d, target, bkg):
         """everything of a training step after the sampler, on the current sample set and the current stream"""
         self._step_core(R, rays_d, target, bkg)
         if self.world_size > 1:
-            self.exchange_and_step()
+            self.exchange_and_step(counted=True)
         else:
-            self.optimizer_step()
+            self.optimizer_step(counted=True)
 
     def enable_graphs(self, n_rays):
         """Static input slots + one CUDA graph per sample-set parity for the post-sampler part of a step (20 launches
@@ -631,6 +637,6 @@ class NGPPipeline:
 
     # number of library kernels one train_step enqueues (for bench.py's gpu_launches)
     LAUNCHES_FORWARD = 1 + 4 + 1 + 1 + 1 + 1          # aabb, march(4), grid, geo mlp (+density, +SH of the view direction), rad mlp, composite
-    LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1 + 1 + 1   # loss clear, (composite fused with loss + its backward), rad bwd, geo bwd, grid bwd, step counter, table adam, heads adam+pack
+    LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1   # (composite fused with loss + its backward + step count), rad bwd, geo bwd, grid bwd, table adam, heads adam+pack
     LAUNCHES_REFRESH = 4 + 2 * 3 + 4                   # candidates (count, scan, select, points), 2 chunks x (unit, grid, geo mlp), apply (fill, splat, ema, threshold)
     LAUNCHES_TRAIN_PEER = LAUNCHES_TRAIN + 2           # + two flag barriers (the gradient clear is a memset, not a kernel of ours)

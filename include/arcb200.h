@@ -247,11 +247,12 @@ int arcb200_mlp_fwd_ex(const void *X, int x_is_half, int64_t ldx, const void *bl
                        float *exp0_out, int64_t n, const int32_t *n_dev, void *stream);
 /* arcb200_mlp_fwd_ex with an fp16 output, plus the degree-4 SH encoding of a per-row direction (row i: dirs[index[i]] or
  * dirs[i]) in output columns [sh_col, sh_col+16): FusedMLPGeoNet -> SHEmbedder (sh_encoder.py:104-123) -> the `[feat, sh]`
- * concatenation of fuse_radiance_inputs (encoder_mlp_network.py:93-118) in one launch. */
+ * concatenation of fuse_radiance_inputs (encoder_mlp_network.py:93-118) in one launch.  zero_scalar (optional): one
+ * float cleared by the launch (the loss accumulator of the step). */
 int arcb200_mlp_fwd_sh(const void *X, int x_is_half, int64_t ldx, const void *blob, int in_dim, int width, int n_hidden,
                        int out_dim, int hidden_act, int out_act, void *Y, int64_t ldy, void *act_save, float *exp0_out,
-                       const float *sh_dirs, const int32_t *sh_index, int sh_col, int sh_remap, int64_t n,
-                       const int32_t *n_dev, void *stream);
+                       const float *sh_dirs, const int32_t *sh_index, int sh_col, int sh_remap, float *zero_scalar,
+                       int64_t n, const int32_t *n_dev, void *stream);
 /* Backward with extras.  act_saved: buffer written by arcb200_mlp_fwd_ex for the same X / weights / n - the forward is
  * then not re-computed, and y_saved (n,out_dim; fp16 if ys_is_half else fp32; leading dimension ldys) must hold the
  * network outputs whenever out_act != 0.  g0/x0: extra gradient on output channel 0 that arrives through exp():
@@ -293,12 +294,13 @@ int arcb200_composite_bwd(const int32_t *offsets, int dense_p, int64_t capacity,
                           int max_samples_per_ray, int64_t n_rays, void *stream);
 
 /* Fused training pass: arcb200_composite_fwd (density input) -> arcb200_huber_loss -> arcb200_composite_bwd in one
- * kernel; same arithmetic as the three calls.  rgb and g_rgb_out (n_rays,3) are optional outputs. */
+ * kernel; same arithmetic as the three calls.  rgb and g_rgb_out (n_rays,3) are optional outputs; step_counter (optional
+ * device int32) is incremented by one (the optimiser step count read through arcb200_adam_step's step_dev). */
 int arcb200_composite_huber_train(const int32_t *offsets, int dense_p, int64_t capacity, const int32_t *pmax_dev,
                                   const float *geo, const float *rad, const float *t, const float *noise, int add_inf_z,
                                   int white_bkg, const float *bkg, int bkg_per_ray, const float *target, float delta,
                                   float weight, float *rgb, float *g_rgb_out, float *loss_sum, float *d_geo, float *d_rad,
-                                  int max_samples_per_ray, int64_t n_rays, void *stream);
+                                  int32_t *step_counter, int max_samples_per_ray, int64_t n_rays, void *stream);
 /* Replaces sdf_to_alpha (arcnerf/models/neus_model.py:242-265).  sdf, slope, alpha (n_rays,p); zvals (n_rays,p+1);
  * scale s from s_dev (device float) when not NULL, else s_host. */
 int arcb200_sdf_to_alpha(const float *sdf, const float *zvals, const float *slope, const float *s_dev, float s_host,

@@ -198,11 +198,12 @@ def test_fused_composite_huber_train_equals_three_kernels(mode):
               dg1.data_ptr(), dr1.data_ptr(), 256, R, st)
     rgb2, g_rgb2, loss2 = torch.empty((R, 3), device=dev), torch.empty((R, 3), device=dev), torch.zeros(1, device=dev)
     dg2, dr2 = torch.full((N, ), 9.0, device=dev), torch.full((N, 3), 9.0, device=dev)
+    counter = torch.tensor([41], dtype=torch.int32, device=dev)
     _lib.call('arcb200_composite_huber_train', _lib.ptr(off_d), dense_p, N, pmax.data_ptr(), sig_d.data_ptr(), rad_d.data_ptr(),
               t_d.data_ptr(), None, 0, white, _lib.ptr(bkg_d), int(bkg is not None), tgt_d.data_ptr(), 0.1, 3000.0, rgb2.data_ptr(),
-              g_rgb2.data_ptr(), loss2.data_ptr(), dg2.data_ptr(), dr2.data_ptr(), 256, R, st)
+              g_rgb2.data_ptr(), loss2.data_ptr(), dg2.data_ptr(), dr2.data_ptr(), counter.data_ptr(), 256, R, st)
     torch.cuda.synchronize()
     assert torch.equal(rgb1, rgb2) and torch.equal(g_rgb1, g_rgb2)
     assert torch.equal(dg1, dg2) and torch.equal(dr1, dr2)
     assert abs(float(loss1) - float(loss2)) <= 2e-6 * abs(float(loss1))
-    assert float(dg2.abs().max()) > 0
+    assert float(dg2.abs().max()) > 0 and int(counter) == 42
