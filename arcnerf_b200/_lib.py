@@ -69,6 +69,8 @@ _SIGS = {
     'arcb200_fill_f32': [P, F, L, P],
     'arcb200_huber_loss': [P, P, F, F, P, P, L, P],
     'arcb200_mlp_adam_pack': [I, P, P, P, P, P, I, P, I, F, F, F, F, F, F, I, P, P],
+    'arcb200_freq_embed_fwd': [P, I, P, I, I, P, L, L, P],
+    'arcb200_freq_embed_bwd': [P, I, P, I, I, P, L, P, L, P],
     'arcb200_volume_refresh_scratch_bytes': [I],
     'arcb200_volume_refresh_candidates': [P, I, L, L, C.c_uint32, U64, U64, P, P, P, P, P],
     'arcb200_volume_refresh_apply': [P, P, L, F, F, I, P, P, P, P],

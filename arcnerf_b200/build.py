@@ -32,6 +32,7 @@ SOURCES = {
     'peer.cu': [],
     'zvals.cu': ['-fmad=false'],
     'volume_refresh.cu': [],
+    'freq.cu': ['-fmad=false'],
 }
 
 

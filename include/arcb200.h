@@ -357,6 +357,14 @@ int arcb200_mlp_adam_pack(int n_mlps, const int *shapes, float *const *p, float 
 int arcb200_huber_loss(const float *rgb, const float *target, float delta, float weight, float *g_rgb,
                        float *loss_sum, int64_t n_rays, void *stream);
 
+/* ---------------------------------------------------------------- frequency encoding (a11) ----
+ * FreqEmbedder.forward (arcnerf/models/base_modules/encoding/freq_encoder.py:66-88): out = [x | sin(x f_0) | cos(x f_0) |
+ * ...], bands given by the caller as a HOST array (2^k or the reference's linear rule), and its input gradient. */
+int arcb200_freq_embed_fwd(const float *x, int d, const float *freqs, int n_freqs, int include_input, float *out,
+                           int64_t ld_out, int64_t n, void *stream);
+int arcb200_freq_embed_bwd(const float *x, int d, const float *freqs, int n_freqs, int include_input, const float *g_out,
+                           int64_t ld_g, float *g_x, int64_t n, void *stream);
+
 /* ---------------------------------------------------------------- occupancy refresh of the volume bound (a6) ----
  * VolumeBound.optimize (obj_bound/volume_bound.py:160-212) + Volume.update_opafield_by_voxel_idx /
  * update_bitfield_by_opafield (arcnerf/geometry/volume.py:983-1018) without torch.randperm / where / unique / host
