@@ -84,6 +84,8 @@ _SIGS = {
     'arcb200_peer_close': [P],
     'arcb200_peer_free': [P],
     'arcb200_peer_barrier': [P, I, I, P, P, I, P],
+    'arcb200_grad_to_half': [P, P, L, L, L, F, P],
+    'arcb200_adam_step_peer16': [P, P, P, I, I, L, L, P, P, P, F, I, F, F, F, F, F, F, P, P],
     'arcb200_adam_step_peer': [P, P, I, L, L, P, P, P, I, F, F, F, F, F, F, P, P],
 }
 _RESTYPE = {

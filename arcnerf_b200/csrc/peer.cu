@@ -35,6 +35,13 @@ __device__ __forceinline__ float4 ld_peer4(const float *p, size_t k4) {
     return __ldcg(reinterpret_cast<const float4 *>(p) + k4);
 }
 
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {
+    a = fminf(fmaxf(a, -65504.0f), 65504.0f);          // saturate instead of overflowing to inf
+    b = fminf(fmaxf(b, -65504.0f), 65504.0f);
+    __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t *>(&h);
+}
+
 __device__ __forceinline__ void acc4(float4 &a, const float4 &b) { a.x += b.x; a.y += b.y; a.z += b.z; a.w += b.w; }
 
 // W > 0: world size known at compile time (all peer loads of one element group are in flight together);
@@ -106,6 +113,120 @@ __global__ void adam_peer_kernel(size_t lo, size_t hi, float *__restrict__ p, fl
         if (want_half)
             for (int w = 0; w < world; ++w) peers.half_out[w][k] = __float2half_rn(pp);
     }
+}
+
+// ---- half-precision gradient exchange ---------------------------------------------------------------------------
+// The reference's hash-grid gradients are fp16 to begin with (tcnn accumulates dL/dparams in __half with a loss scale of
+// 128 and hands torch a float copy, tinycudann/modules.py:93-96,141), so what DDP averages has fp16 precision per rank.
+// Here every rank keeps its fp32-accumulated gradient, but what TRAVELS is a loss-scaled fp16 copy of the part other
+// ranks own: half the NVLink bytes of the fp32 exchange.  The owner adds its own fp32 slice and the peers' fp16 slices
+// in fp32.
+
+// g16 = half(g32 * scale) outside [keep_lo, keep_hi) (the slice this rank owns and reads in fp32); g32 is cleared there.
+__global__ void grad_to_half_kernel(size_t n, size_t keep_lo, size_t keep_hi, float *__restrict__ g32,
+                                    __half *__restrict__ g16, float scale) {
+    arc_pdl_sync();
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t n8 = n / 8;
+    for (size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < n8; k += stride) {
+        const size_t e = k * 8;
+        if (e >= keep_lo && e < keep_hi) continue;                  // keep_lo / keep_hi are multiples of 8
+        float4 a = __ldcs(reinterpret_cast<const float4 *>(g32) + 2 * k), b = __ldcs(reinterpret_cast<const float4 *>(g32) + 2 * k + 1);
+        uint4 w;
+        w.x = pack_h2(a.x * scale, a.y * scale); w.y = pack_h2(a.z * scale, a.w * scale);
+        w.z = pack_h2(b.x * scale, b.y * scale); w.w = pack_h2(b.z * scale, b.w * scale);
+        reinterpret_cast<uint4 *>(g16)[k] = w;
+        reinterpret_cast<float4 *>(g32)[2 * k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        reinterpret_cast<float4 *>(g32)[2 * k + 1] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    for (size_t e = n8 * 8 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += stride) {
+        if (e >= keep_lo && e < keep_hi) continue;
+        g16[e] = __float2half_rn(fminf(fmaxf(g32[e] * scale, -65504.0f), 65504.0f));
+        g32[e] = 0.f;
+    }
+}
+
+struct Peer16List {
+    const __half *grad16[kMaxWorld];   // every rank's fp16 gradient copy (entry `rank` is unused)
+    __half *half_out[kMaxWorld];
+};
+
+// Adam over [lo, hi) on  own fp32 gradient + sum over the other ranks of their fp16 gradient / scale;  the own gradient
+// slice is cleared, the updated fp16 working copy goes to every rank.  Eight elements per thread and trip.
+template <int W>
+__global__ void adam_peer16_kernel(size_t lo, size_t hi, float *__restrict__ p, float *__restrict__ m, float *__restrict__ v,
+                                   float *__restrict__ g_own, const __grid_constant__ Peer16List peers, int world, int rank,
+                                   float inv_scale, AdamHyper h, const int32_t *__restrict__ step_dev) {
+    arc_pdl_sync();
+    if (step_dev) bias_from_step(h, max(*step_dev, 1));
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    const size_t k_lo = lo / 8, k_hi = hi / 8;
+    const int nw = W > 0 ? W : world;
+    for (size_t k = k_lo + (size_t)blockIdx.x * blockDim.x + threadIdx.x; k < k_hi; k += stride) {
+        uint4 part[W > 0 ? W : kMaxWorld];
+        #pragma unroll
+        for (int w = 0; w < (W > 0 ? W : kMaxWorld); ++w)
+            if (w < nw && w != rank) part[w] = __ldcg(reinterpret_cast<const uint4 *>(peers.grad16[w]) + k);
+        float g[8];
+        {
+            const float4 a = reinterpret_cast<const float4 *>(g_own)[2 * k], b = reinterpret_cast<const float4 *>(g_own)[2 * k + 1];
+            g[0] = a.x; g[1] = a.y; g[2] = a.z; g[3] = a.w; g[4] = b.x; g[5] = b.y; g[6] = b.z; g[7] = b.w;
+        }
+        float pv[8], mv[8], vv[8];
+        #pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const float4 a = reinterpret_cast<const float4 *>(p)[2 * k + q], b = reinterpret_cast<const float4 *>(m)[2 * k + q],
+                         c = reinterpret_cast<const float4 *>(v)[2 * k + q];
+            pv[4 * q] = a.x; pv[4 * q + 1] = a.y; pv[4 * q + 2] = a.z; pv[4 * q + 3] = a.w;
+            mv[4 * q] = b.x; mv[4 * q + 1] = b.y; mv[4 * q + 2] = b.z; mv[4 * q + 3] = b.w;
+            vv[4 * q] = c.x; vv[4 * q + 1] = c.y; vv[4 * q + 2] = c.z; vv[4 * q + 3] = c.w;
+        }
+        float s[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        #pragma unroll
+        for (int w = 0; w < (W > 0 ? W : kMaxWorld); ++w) {
+            if (w >= nw || w == rank) continue;
+            const uint32_t wd[4] = {part[w].x, part[w].y, part[w].z, part[w].w};
+            #pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&wd[q]));
+                s[2 * q] += f.x; s[2 * q + 1] += f.y;
+            }
+        }
+        uint32_t hw[4];
+        #pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            adam_one(pv[q], mv[q], vv[q], g[q] + s[q] * inv_scale, h);
+        }
+        #pragma unroll
+        for (int q = 0; q < 4; ++q) hw[q] = pack_h2(pv[2 * q], pv[2 * q + 1]);
+        #pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            reinterpret_cast<float4 *>(p)[2 * k + q] = make_float4(pv[4 * q], pv[4 * q + 1], pv[4 * q + 2], pv[4 * q + 3]);
+            reinterpret_cast<float4 *>(m)[2 * k + q] = make_float4(mv[4 * q], mv[4 * q + 1], mv[4 * q + 2], mv[4 * q + 3]);
+            reinterpret_cast<float4 *>(v)[2 * k + q] = make_float4(vv[4 * q], vv[4 * q + 1], vv[4 * q + 2], vv[4 * q + 3]);
+            reinterpret_cast<float4 *>(g_own)[2 * k + q] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        const uint4 pk = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+        #pragma unroll
+        for (int w = 0; w < (W > 0 ? W : kMaxWorld); ++w)
+            if (w < nw) reinterpret_cast<uint4 *>(peers.half_out[w])[k] = pk;
+    }
+    for (size_t e = k_hi * 8 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; e < hi; e += stride) {
+        float s = 0.f;
+        for (int w = 0; w < world; ++w)
+            if (w != rank) s += __half2float(__ldcg(peers.grad16[w] + e));
+        float pp = p[e], mm = m[e], vv = v[e];
+        adam_one(pp, mm, vv, g_own[e] + s * inv_scale, h);
+        p[e] = pp; m[e] = mm; v[e] = vv; g_own[e] = 0.f;
+        for (int w = 0; w < world; ++w) peers.half_out[w][e] = __float2half_rn(pp);
+    }
+}
+
+template <int W>
+void launch_adam_peer16(unsigned blocks, cudaStream_t st, size_t lo, size_t hi, float *p, float *m, float *v, float *g_own,
+                        const Peer16List &pl, int world, int rank, float inv_scale, const AdamHyper &h,
+                        const int32_t *step_dev) {
+    arc_launch(adam_peer16_kernel<W>, blocks, 256, 0, st, lo, hi, p, m, v, g_own, pl, world, rank, inv_scale, h, step_dev);
 }
 
 __device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
@@ -261,6 +382,62 @@ int arcb200_adam_step_peer(const void *const *grads, void *const *half_out, int 
         case 4: launch_adam_peer<4>((unsigned)blocks, st, lo, hi, p, m, v, pl, world, h, step_dev); break;
         case 8: launch_adam_peer<8>((unsigned)blocks, st, lo, hi, p, m, v, pl, world, h, step_dev); break;
         default: launch_adam_peer<0>((unsigned)blocks, st, lo, hi, p, m, v, pl, world, h, step_dev); break;
+    }
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// Loss-scaled fp16 copy of the gradient for the exchange: g16[i] = half(g32[i] * scale) for i outside [keep_lo, keep_hi)
+// (multiples of 8: the slice this rank owns, which it reads in fp32 itself); g32 is cleared where it was converted.
+int arcb200_grad_to_half(float *g32, void *g16, int64_t n, int64_t keep_lo, int64_t keep_hi, float scale, void *stream) {
+    ARC_REQUIRE(n >= 0 && keep_lo >= 0 && keep_hi >= keep_lo && (keep_lo & 7) == 0 && ((keep_hi & 7) == 0 || keep_hi >= n),
+                "grad_to_half: bad range");
+    if (n == 0) return ARCB200_OK;
+    ARC_REQUIRE(g32 && g16 && (((uintptr_t)g32 | (uintptr_t)g16) & 15u) == 0, "grad_to_half: null or misaligned pointer");
+    long long blocks = (n / 8 + 255) / 256;
+    const long long cap = (long long)arc_sm_count() * 16;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    arc_launch(grad_to_half_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, (size_t)n, (size_t)keep_lo, (size_t)keep_hi, g32,
+               (__half *)g16, scale);
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// arcb200_adam_step_peer with the half-precision exchange: the gradient of [lo, hi) (lo % 8 == 0) is g_own (this rank's
+// fp32 vector, cleared over the range afterwards) + sum over the OTHER ranks w of grads16[w] / scale (their fp16 copies from
+// arcb200_grad_to_half, peer loads), times grad_scale.  Everything else as arcb200_adam_step_peer.
+int arcb200_adam_step_peer16(float *g_own, const void *const *grads16, void *const *half_out, int world, int rank,
+                             int64_t lo, int64_t hi, float *p, float *m, float *v, float scale, int step, float lr,
+                             float beta1, float beta2, float eps, float weight_decay, float grad_scale,
+                             const int32_t *step_dev, void *stream) {
+    ARC_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, "adam_step_peer16: world %d rank %d out of range", world, rank);
+    ARC_REQUIRE(lo >= 0 && hi >= lo && (lo & 7) == 0, "adam_step_peer16: bad range [%lld, %lld)", (long long)lo, (long long)hi);
+    if (hi == lo) return ARCB200_OK;
+    ARC_REQUIRE(g_own && grads16 && half_out && p && m && v && scale > 0.f && (step >= 1 || step_dev), "adam_step_peer16: null pointer, scale or step");
+    if (step < 1) step = 1;
+    ARC_REQUIRE((((uintptr_t)p | (uintptr_t)m | (uintptr_t)v | (uintptr_t)g_own) & 15u) == 0, "adam_step_peer16: misaligned buffer");
+    Peer16List pl;
+    for (int w = 0; w < kMaxWorld; ++w) {
+        pl.grad16[w] = (w < world && w != rank) ? (const __half *)grads16[w] : nullptr;
+        pl.half_out[w] = w < world ? (__half *)half_out[w] : nullptr;
+    }
+    for (int w = 0; w < world; ++w) {
+        ARC_REQUIRE(w == rank || (pl.grad16[w] && ((uintptr_t)pl.grad16[w] & 15u) == 0), "adam_step_peer16: grads16[%d] null or misaligned", w);
+        ARC_REQUIRE(pl.half_out[w] && ((uintptr_t)pl.half_out[w] & 15u) == 0, "adam_step_peer16: half_out[%d] null or misaligned", w);
+    }
+    const AdamHyper h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, grad_scale, step);
+    long long blocks = ((hi - lo) / 8 + 255) / 256;
+    const long long cap = (long long)arc_sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    cudaStream_t st = (cudaStream_t)stream;
+    const float inv = 1.0f / scale;
+    switch (world) {
+        case 2: launch_adam_peer16<2>((unsigned)blocks, st, lo, hi, p, m, v, g_own, pl, world, rank, inv, h, step_dev); break;
+        case 4: launch_adam_peer16<4>((unsigned)blocks, st, lo, hi, p, m, v, g_own, pl, world, rank, inv, h, step_dev); break;
+        case 8: launch_adam_peer16<8>((unsigned)blocks, st, lo, hi, p, m, v, g_own, pl, world, rank, inv, h, step_dev); break;
+        default: launch_adam_peer16<0>((unsigned)blocks, st, lo, hi, p, m, v, g_own, pl, world, rank, inv, h, step_dev); break;
     }
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;

@@ -106,8 +106,9 @@ class NGPPipeline:
                  world_size=1, rank=0, exchange='auto', **overrides):
         """world_size > 1: data-parallel over the ranks of torch.distributed's default group.  exchange = 'peer' (the
         gradient exchange fused into the Adam kernel over NVLink peer memory, csrc/peer.cu; ranks on one node),
-        'nccl' (one all-reduce of the flat gradient buffer, then the single-GPU Adam), or 'auto' (= 'peer' unless the
-        environment variable ARCB200_EXCHANGE says otherwise)."""
+        'peer16' (the same with the hash-table gradient travelling as a loss-scaled fp16 copy - the precision tcnn's
+        gradients have when the reference hands them to DDP - and summed in fp32), 'nccl' (one all-reduce of the flat
+        gradient buffer, then the single-GPU Adam), or 'auto' (= 'peer16' unless ARCB200_EXCHANGE says otherwise)."""
         cfg = dict(NGP_DEFAULTS)
         cfg.update(overrides)
         self.cfg = cfg
@@ -134,10 +135,10 @@ class NGPPipeline:
         nt, ng, nr = self.table.numel(), self.geo_p.numel(), self.rad_p.numel()
         self.rank = int(rank)
         if exchange == 'auto':
-            exchange = os.environ.get('ARCB200_EXCHANGE', 'peer')
+            exchange = os.environ.get('ARCB200_EXCHANGE', 'peer16')
         self.exchange = exchange if self.world_size > 1 else 'none'
         self.arena = None
-        if self.exchange == 'peer':
+        if self.exchange in ('peer', 'peer16'):
             import torch.distributed as dist
             from .peer import PeerArena, slice_bounds
 
@@ -146,7 +147,10 @@ class NGPPipeline:
                 dist.all_gather_object(out, handle)
                 return out
             self.rank = dist.get_rank()
-            self.arena = PeerArena({'grad': (nt + ng + nr) * 4, 'table_h': nt * 2}, dev, self.rank, self.world_size, share)
+            regions = {'grad': (nt + ng + nr) * 4, 'table_h': nt * 2}
+            if self.exchange == 'peer16':
+                regions['grad16'] = nt * 2
+            self.arena = PeerArena(regions, dev, self.rank, self.world_size, share)
             self.table_h = self.arena.local('table_h', torch.float16)
             F.cast_f16(self.table, self.table_h)
             self.slice = slice_bounds(nt, self.rank, self.world_size)
@@ -448,7 +452,7 @@ class NGPPipeline:
         and broadcasts the fp16 working copy (hash table: this rank's slice only; the two small heads: redundantly on
         every rank, same summation order, so the replicas stay identical), barrier, clear the own gradients.
         'nccl': ONE all-reduce of the flat gradient buffer (48.8 MB), then the single-GPU Adam kernels."""
-        if self.exchange != 'peer':
+        if self.exchange not in ('peer', 'peer16'):
             import torch.distributed as dist
             self._run('all_reduce', lambda: dist.all_reduce(self.g_all))
             self.optimizer_step(counted)
@@ -465,10 +469,22 @@ class NGPPipeline:
             self._peer_ptrs = (ar.pointers('grad'), ar.pointers('grad', nt * 4), ar.pointers('grad', (nt + ng) * 4),
                                ar.pointers('table_h'))
         g_t, g_g, g_r, th = self._peer_ptrs
-        self._run('peer_barrier', ar.barrier)
         lo, hi = self.slice
-        self._run('adam_table_peer', lambda: adam_step_peer(g_t, th, W, lo, hi, self.table, self.m_table, self.v_table,
-                                                            self.step_count, cfg['lr'], **kw))
+        half = self.exchange == 'peer16'
+        if half:
+            from .peer import adam_step_peer16, grad_to_half
+            if not hasattr(self, '_g16'):
+                self._g16 = self.arena.local('grad16', torch.float16)
+                self._g16_ptrs = ar.pointers('grad16')
+            self._run('grad_to_half', lambda: grad_to_half(self.g_table, self._g16, lo, hi, cfg.get('exchange_scale', 128.0)))
+        self._run('peer_barrier', ar.barrier)
+        if half:
+            self._run('adam_table_peer', lambda: adam_step_peer16(self.g_table, self._g16_ptrs, th, W, self.rank, lo, hi,
+                                                                  self.table, self.m_table, self.v_table, self.step_count,
+                                                                  cfg['lr'], scale=cfg.get('exchange_scale', 128.0), **kw))
+        else:
+            self._run('adam_table_peer', lambda: adam_step_peer(g_t, th, W, lo, hi, self.table, self.m_table, self.v_table,
+                                                                self.step_count, cfg['lr'], **kw))
 
         if getattr(self, '_mlp_opt_peer', None) is None:
             self._mlp_opt_peer = F.MlpAdamPack((self.geo_spec, self.rad_spec), (self.geo_p, self.rad_p),
@@ -481,13 +497,16 @@ class NGPPipeline:
 
         def close():
             ar.barrier()
-            self.g_all.zero_()
+            if half:
+                self.g_all[nt:].zero_()          # the heads' gradients (40 KB); the table part was cleared on the way
+            else:
+                self.g_all.zero_()
         self._run('peer_barrier+clear', close)
 
     def gather_master_table(self):
         """'peer' exchange keeps the fp32 master of the hash table sharded (each rank owns self.slice); this collects
         the full fp32 table on every rank (checkpointing; not on the step path)."""
-        if self.exchange != 'peer':
+        if self.exchange not in ('peer', 'peer16'):
             return self.table
         import torch.distributed as dist
         from .peer import slice_bounds

@@ -95,6 +95,20 @@ def adam_step_peer(grads, half_out, world, lo, hi, p, m, v, step, lr, beta1=0.9,
               float(grad_scale), _lib.ptr(step_dev), _lib.current_stream())
 
 
+def grad_to_half(g32, g16, keep_lo, keep_hi, scale=128.0):
+    """fp16 loss-scaled copy of the gradient outside [keep_lo, keep_hi); clears g32 there"""
+    _lib.call('arcb200_grad_to_half', g32.data_ptr(), g16.data_ptr(), g32.numel(), int(keep_lo), int(keep_hi), float(scale),
+              _lib.current_stream())
+
+
+def adam_step_peer16(g_own, grads16, half_out, world, rank, lo, hi, p, m, v, step, lr, scale=128.0, beta1=0.9, beta2=0.999,
+                     eps=1e-8, weight_decay=0.0, grad_scale=1.0, step_dev=None):
+    """grads16 / half_out: ctypes pointer arrays from PeerArena.pointers"""
+    _lib.call('arcb200_adam_step_peer16', g_own.data_ptr(), grads16, half_out, int(world), int(rank), int(lo), int(hi),
+              p.data_ptr(), m.data_ptr(), v.data_ptr(), float(scale), int(step), float(lr), float(beta1), float(beta2), float(eps),
+              float(weight_decay), float(grad_scale), _lib.ptr(step_dev), _lib.current_stream())
+
+
 def slice_bounds(n, rank, world, quantum=1024):
     """[lo, hi) of rank's slice of an n-element vector; slices start on multiples of `quantum` elements"""
     per = _round_up((n + world - 1) // world, quantum)

@@ -111,6 +111,7 @@ def make_batches(n_batches, seed):
 EXCHANGE_NOTE = {
     'none': 'single GPU',
     'peer': 'fused into the Adam kernel: peer loads of the gradient slices + peer stores of the fp16 table over NVLink (csrc/peer.cu)',
+    'peer16': 'fused into the Adam kernel over NVLink peer memory (csrc/peer.cu): the hash-table gradient travels as a loss-scaled fp16 copy (the precision tcnn hands to DDP in the reference), summed in fp32 with the owner\'s own fp32 slice; fp16 table slices stored back to every rank',
     'nccl': 'one NCCL all-reduce of the flat fp32 gradient buffer per step, then Adam on every rank',
 }
 
@@ -426,7 +427,7 @@ def main():
                         occupancy_refresh=('every %d steps inside the timed region: 524288 + 524288 voxels of 128^3 re-evaluated (steady-state VolumeBound.optimize), result not applied to the synthetic scene' % occ_every) if occ_every > 0 else 'off',
                         parallelism='dp%d' % world, gradient_exchange=EXCHANGE_NOTE[pipe.exchange]),
             e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=4, ms_per_step=ms_e2e / K, path=e2e_mode),
-            gpu_launches=(NGPPipeline.LAUNCHES_TRAIN_PEER if pipe.exchange == 'peer' else NGPPipeline.LAUNCHES_TRAIN) * K
+            gpu_launches=(NGPPipeline.LAUNCHES_TRAIN + {'peer': 2, 'peer16': 3}.get(pipe.exchange, 0)) * K
             + (NGPPipeline.LAUNCHES_REFRESH * (K // occ_every) if occ_every > 0 else 0),
             clocks=clock_info, roofline=roofline, cpu_baseline=cpu_baseline,
             render_ms_800x800=render_ms,

@@ -422,6 +422,15 @@ int arcb200_peer_barrier(void *const *flags, int world, int rank, void *epoch, i
 int arcb200_adam_step_peer(const void *const *grads, void *const *half_out, int world, int64_t lo, int64_t hi,
                            float *p, float *m, float *v, int step, float lr, float beta1, float beta2, float eps,
                            float weight_decay, float grad_scale, const int32_t *step_dev, void *stream);
+/* Half-precision gradient exchange (what travels over NVLink is a loss-scaled fp16 copy, as precise as the fp16 gradients
+ * tcnn hands to DDP in the reference, tinycudann/modules.py:93-96,141): arcb200_grad_to_half makes the copy of everything
+ * outside the slice this rank owns (and clears the fp32 gradient there); arcb200_adam_step_peer16 is
+ * arcb200_adam_step_peer on  g_own (fp32, cleared over the range)  +  sum over the other ranks of grads16[w] / scale. */
+int arcb200_grad_to_half(float *g32, void *g16, int64_t n, int64_t keep_lo, int64_t keep_hi, float scale, void *stream);
+int arcb200_adam_step_peer16(float *g_own, const void *const *grads16, void *const *half_out, int world, int rank,
+                             int64_t lo, int64_t hi, float *p, float *m, float *v, float scale, int step, float lr,
+                             float beta1, float beta2, float eps, float weight_decay, float grad_scale,
+                             const int32_t *step_dev, void *stream);
 
 #ifdef __cplusplus
 }

@@ -114,7 +114,7 @@ def _two_rank_worker(rank, world, port, out_dir):
     params = init_params(dict(NGP_DEFAULTS), seed=3, grid_scale=0.5)
     n = 1024
     res = {}
-    for mode in ('nccl', 'peer'):
+    for mode in ('nccl', 'peer', 'peer16'):
         pipe = NGPPipeline(max_rays=n, capacity=1 << 17, device='cuda:%d' % rank, world_size=world, exchange=mode,
                            params={k: v.clone() for k, v in params.items()}, lr=1e-2)
         pipe.set_occupancy(synth.occupancy_volume('lego'))
@@ -131,24 +131,25 @@ def _two_rank_worker(rank, world, port, out_dir):
                          rad=pipe.rad_p.clone(), loss=losses)
     ok = True
     msg = []
-    for k in ('table', 'table_h', 'geo', 'rad'):
-        # the hash-grid backward accumulates with float atomics (run-to-run order differs), and Adam turns a sign flip
-        # of a near-zero gradient into a +-lr step: compare by the fraction of entries that moved apart
-        a, b = res['nccl'][k].float(), res['peer'][k].float()
-        far = float(((a - b).abs() > 2e-3).float().mean())
-        if far > 2e-3:
+    for mode_b in ('peer', 'peer16'):
+        for k in ('table', 'table_h', 'geo', 'rad'):
+            # the hash-grid backward accumulates with float atomics (run-to-run order differs), and Adam turns a sign flip
+            # of a near-zero gradient into a +-lr step: compare by the fraction of entries that moved apart
+            a, b = res['nccl'][k].float(), res[mode_b][k].float()
+            far = float(((a - b).abs() > 2e-3).float().mean())
+            if far > 2e-3:
+                ok = False
+                msg.append('%s %s differs: fraction beyond 2e-3 = %.3e, max |d| %.3e' % (mode_b, k, far, float((a - b).abs().max())))
+        if not np.allclose(res['nccl']['loss'], res[mode_b]['loss'], rtol=2e-3):
             ok = False
-            msg.append('%s differs: fraction beyond 2e-3 = %.3e, max |d| %.3e' % (k, far, float((a - b).abs().max())))
-    if not np.allclose(res['nccl']['loss'], res['peer']['loss'], rtol=2e-3):
-        ok = False
-        msg.append('losses differ %s %s' % (res['nccl']['loss'], res['peer']['loss']))
-    # replicas agree across ranks
-    th = res['peer']['table_h'].float()
-    other = [torch.empty_like(th) for _ in range(world)]
-    dist.all_gather(other, th)
-    if not all(torch.equal(o, th) for o in other):
-        ok = False
-        msg.append('fp16 tables differ between ranks')
+            msg.append('%s losses differ %s %s' % (mode_b, res['nccl']['loss'], res[mode_b]['loss']))
+        # replicas agree across ranks
+        th = res[mode_b]['table_h'].float()
+        other = [torch.empty_like(th) for _ in range(world)]
+        dist.all_gather(other, th)
+        if not all(torch.equal(o, th) for o in other):
+            ok = False
+            msg.append('%s fp16 tables differ between ranks' % mode_b)
     with open(os.path.join(out_dir, 'rank%d.txt' % rank), 'w') as f:
         f.write('OK' if ok else 'FAIL ' + '; '.join(msg))
     dist.barrier()
@@ -162,3 +163,55 @@ def test_two_ranks_peer_exchange_matches_all_reduce(tmp_path):
     mp.spawn(_two_rank_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
     for r in range(2):
         assert open(tmp_path / ('rank%d.txt' % r)).read() == 'OK'
+
+
+@pytest.mark.parametrize('world', [2, 3, 8])
+def test_half_precision_exchange_kernels(world):
+    """grad_to_half + adam_step_peer16 on emulated ranks (buffers on one device) against the fp32 sum-then-Adam path fed
+    with the same fp16-rounded peer gradients"""
+    from arcnerf_b200 import functional as F
+    from arcnerf_b200.peer import adam_step_peer16, grad_to_half, slice_bounds
+    n = 40000 + 8 * 3
+    g = torch.Generator(device='cuda').manual_seed(world)
+    grads = [torch.randn(n, device='cuda', generator=g) * 1e-3 for _ in range(world)]
+    grads[0][5] = 1e9                                             # saturates instead of overflowing
+    p0 = torch.randn(n, device='cuda', generator=g)
+    m0 = torch.randn(n, device='cuda', generator=g) * 0.1
+    v0 = torch.rand(n, device='cuda', generator=g) * 0.01
+    scale = 128.0
+    bounds = [slice_bounds(n, r, world, quantum=1024) for r in range(world)]
+    g16 = [torch.full((n, ), 3.0, dtype=torch.float16, device='cuda') for _ in range(world)]
+    g32 = [x.clone() for x in grads]
+    for r in range(world):
+        grad_to_half(g32[r], g16[r], bounds[r][0], bounds[r][1], scale)
+    torch.cuda.synchronize()
+    for r in range(world):
+        lo, hi = bounds[r]
+        assert torch.equal(g32[r][lo:hi], grads[r][lo:hi]) and float(g32[r][:lo].abs().sum() + g32[r][hi:].abs().sum()) == 0.0
+        ref16 = (grads[r] * scale).clamp(-65504, 65504).half()
+        assert torch.equal(g16[r][:lo], ref16[:lo]) and torch.equal(g16[r][hi:], ref16[hi:])
+        assert bool((g16[r][lo:hi] == 3.0).all())                 # the own slice is not converted
+    halves = [torch.full((n, ), 7.0, dtype=torch.float16, device='cuda') for _ in range(world)]
+    p_all, h_ref = p0.clone(), torch.empty(n, dtype=torch.float16, device='cuda')
+    for r in range(world):
+        lo, hi = bounds[r]
+        if hi == lo:
+            continue
+        p, m, v = p0.clone(), m0.clone(), v0.clone()
+        adam_step_peer16(g32[r], _ptrs(g16), _ptrs(halves), world, r, lo, hi, p, m, v, 2, 1e-2, scale=scale, grad_scale=1.0 / world)
+        # reference: own fp32 + peers' fp16 values (summed in rank order, then / scale) -> single-GPU Adam
+        s = torch.zeros(hi - lo, device='cuda')
+        for w in range(world):
+            if w != r:
+                s += g16[w][lo:hi].float()
+        gsum = grads[r][lo:hi] + s * (1.0 / scale)
+        pr, mr, vr = p0[lo:hi].clone(), m0[lo:hi].clone(), v0[lo:hi].clone()
+        hr = torch.empty(hi - lo, dtype=torch.float16, device='cuda')
+        F.adam_step(pr, mr, vr, gsum, 2, 1e-2, p_half=hr, grad_scale=1.0 / world, zero_grad=False)
+        torch.cuda.synchronize()
+        assert torch.equal(p[lo:hi], pr) and torch.equal(m[lo:hi], mr) and torch.equal(v[lo:hi], vr)
+        assert torch.equal(p[:lo], p0[:lo]) and torch.equal(p[hi:], p0[hi:])
+        assert float(g32[r][lo:hi].abs().sum()) == 0.0            # own slice cleared after use
+        h_ref[lo:hi] = hr
+    for h in halves:
+        assert torch.equal(h, h_ref)
