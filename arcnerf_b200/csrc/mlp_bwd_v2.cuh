@@ -146,11 +146,10 @@ mlp_bwd_v2_kernel(int64_t n, const int32_t *__restrict__ n_dev, const __half *__
                     const uint32_t g_tile = (l == cfg.n_mm - 1) ? g_addr : h_addr + (uint32_t)(l * h_bytes);
                     const uint32_t in_tile = (l == 0) ? x_addr : h_addr + (uint32_t)((l - 1) * h_bytes);
                     const bool acc = (started >> l) & 1u;
-                    if (ex.debug_skip & 1) { }
-                    else if (plan.wg_t[l]) issue_wgrad_mm(tmem + cols.wg_col[l], in_tile, g_tile, plan.wg_m[l], plan.wg_n[l], acc);
+                    if (plan.wg_t[l]) issue_wgrad_mm(tmem + cols.wg_col[l], in_tile, g_tile, plan.wg_m[l], plan.wg_n[l], acc);
                     else issue_wgrad_mm(tmem + cols.wg_col[l], g_tile, in_tile, plan.wg_m[l], plan.wg_n[l], acc);
                     started |= 1u << l;
-                    if ((l > 0 || dX != nullptr) && !(ex.debug_skip & 2))
+                    if (l > 0 || dX != nullptr)
                         issue_dgrad_mm(tmem + (uint32_t)s * 64, g_tile, w_addr + cfg.w_off[l], cfg.K[l], cfg.N[l]);
                     tc05::mma_commit(&sh->slot[s].mma_done);
                     layer[s] = (l == 0) ? cfg.n_mm - 1 : l - 1;
@@ -263,7 +262,7 @@ mlp_bwd_v2_kernel(int64_t n, const int32_t *__restrict__ n_dev, const __half *__
                     mbar_arrive(&sb->g_ready);
                 } else if (dX != nullptr) {
                     for_each_acc_pair(act_tmem, cfg.K[0] / 16, [&](int cb, const uint32_t (&rr)[16]) {
-                        if (!valid || (ex.debug_skip & 8)) return;
+                        if (!valid) return;
                         float v[16];
                         #pragma unroll
                         for (int k = 0; k < 16; ++k) v[k] = __uint_as_float(rr[k]) * inv_scale;
@@ -283,7 +282,7 @@ mlp_bwd_v2_kernel(int64_t n, const int32_t *__restrict__ n_dev, const __half *__
         const uint32_t my_tmem = tmem + ((uint32_t)((warp & 3) * 32) << 16);
         const int w4 = warp & 3;
         for (int l = 0; l < cfg.n_mm; ++l) {
-            if ((l % NWG) != wg || !((started >> l) & 1u) || (ex.debug_skip & 4)) continue;
+            if ((l % NWG) != wg || !((started >> l) & 1u)) continue;
             const int M = plan.wg_m[l], Nn = plan.wg_n[l];
             const int row = (M == 128) ? wtid : (w4 * 16 + lane);
             const bool owner = (M == 128) || (lane < 16);

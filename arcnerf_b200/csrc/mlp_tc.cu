@@ -254,7 +254,6 @@ struct BwdExtra {
     int64_t ldx0;
     int x0_is_half;
     float clip;
-    int debug_skip;       // timing experiments only (ARCB200_MLP_DEBUG_SKIP): 1 no wgrad MMAs, 2 no dgrad MMAs, 4 no flush, 8 no dX store
 };
 
 // ---------------------------------------------------------------------------------------------- forward
@@ -931,8 +930,6 @@ int arcb200_mlp_bwd_ex(const void *X, int x_is_half, int64_t ldx, const void *bl
     BwdExtra bex;
     bex.act_saved = (const uint8_t *)act_saved; bex.y_saved = y_saved; bex.ldys = ldys; bex.y_is_half = ys_is_half;
     bex.g0 = g0; bex.x0 = x0; bex.ldx0 = ldx0; bex.x0_is_half = x0_is_half; bex.clip = clip;
-    bex.debug_skip = 0;
-    if (const char *e = getenv("ARCB200_MLP_DEBUG_SKIP")) bex.debug_skip = atoi(e);
     if (n == 0) return ARCB200_OK;
     MlpCfg c;
     ARC_REQUIRE(make_cfg(c, in_dim, width, n_hidden, out_dim, hidden_act, out_act) >= 0, "mlp_bwd: unsupported shape");

@@ -125,7 +125,12 @@ __global__ void refresh_points_kernel(uint32_t n_cand, uint32_t n_grid, Pcg32 rn
         #pragma unroll
         for (int a = 0; a < 3; ++a) p[a] = 0.5f * (aabb[a] + aabb[3 + a]);
     } else {
-        rng.advance((uint64_t)i * 3);
+        // per-candidate generator state from a 64-bit mix of (call state, candidate) - a jump-ahead of i*3 draws would cost
+        // a 64-step multiply chain per thread, and the jitter only has to be uniform inside the voxel
+        uint64_t zz = rng.state + 0x9e3779b97f4a7c15ull * (uint64_t)(i + 1);
+        zz = (zz ^ (zz >> 30)) * 0xbf58476d1ce4e5b9ull;
+        zz = (zz ^ (zz >> 27)) * 0x94d049bb133111ebull;
+        rng.state = zz ^ (zz >> 31);
         const uint32_t c[3] = {(uint32_t)v / (n_grid * n_grid), ((uint32_t)v / n_grid) % n_grid, (uint32_t)v % n_grid};
         #pragma unroll
         for (int a = 0; a < 3; ++a) {
