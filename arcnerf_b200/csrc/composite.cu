@@ -311,12 +311,16 @@ composite_train_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int
         for (int q = 0; q < kMaxChunks / 32; ++q) carries[q] = 1.0f;
         float carry = 1.0f, t_bkg = 1.0f;
         float ar = 0.f, ag = 0.f, ab = 0.f, aw = 0.f;
+        // loads run three chunks ahead of their use: a long ray (hundreds of samples) is what the kernel's duration hangs on,
+        // and with one chunk of look-ahead every trip would wait most of an L2 round trip
         Item cur = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, (int32_t)lane, n, m);
+        Item n1 = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, (int32_t)lane + 32, n, m);
+        Item n2 = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, (int32_t)lane + 64, n, m);
         for (int32_t c = 0; c < n_chunks; ++c) {
             const int32_t base = c << 5;
             const int32_t i = base + (int32_t)lane;
             const bool on = i < m;
-            const Item nxt = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, i + 32, n, m);
+            const Item n3 = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, i + 96, n, m);
             float delta, dens;
             const float alpha = on ? item_alpha<false>(cur, i, n, delta, dens) : 0.0f;
             const float f = on ? (1.0f - alpha + 1e-10f) : 1.0f;
@@ -332,7 +336,7 @@ composite_train_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int
             if (k_bkg >= base && k_bkg < base + 32) t_bkg = __shfl_sync(ARC_FULL_MASK, T, k_bkg - base);
             carry *= __shfl_sync(ARC_FULL_MASK, incl, 31);
             if (k_bkg == base + 32) t_bkg = carry;
-            cur = nxt;
+            cur = n1; n1 = n2; n2 = n3;
         }
         ar = warp_sum(ar); ag = warp_sum(ag); ab = warp_sum(ab); aw = warp_sum(aw);
         float b0 = 0.f, b1 = 0.f, b2 = 0.f;
@@ -368,13 +372,16 @@ composite_train_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int
 
         // pass 2: reverse, suffix sums of w_j * v_j
         float suffix = 0.0f;
-        cur = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, ((n_chunks - 1) << 5) + (int32_t)lane, n, m);
+        const int32_t last_i = ((n_chunks - 1) << 5) + (int32_t)lane;
+        cur = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, last_i, n, m);
+        n1 = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, last_i - 32, n, m);
+        n2 = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, last_i - 64, n, m);
         for (int32_t c = n_chunks - 1; c >= 0; --c) {
             const int32_t base = c << 5;
             const int32_t i = base + (int32_t)lane;
             const bool on = i < m;
             const int64_t s = sg.start + i;
-            const Item nxt = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, i - 32, n, m);
+            const Item n3 = fetch_item<false, true>(geo, t, noise, rad, nullptr, sg.start, i - 96, n, m);
             float delta = 0.f, dens = 0.f;
             const float alpha = on ? item_alpha<false>(cur, i, n, delta, dens) : 0.0f;
             const float f = on ? (1.0f - alpha + 1e-10f) : 1.0f;
@@ -403,7 +410,7 @@ composite_train_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int
                 if (d_rad) { d_rad[3 * s] = w * gr; d_rad[3 * s + 1] = w * gg; d_rad[3 * s + 2] = w * gb; }
             }
             suffix += __shfl_sync(ARC_FULL_MASK, sfx, 0);
-            cur = nxt;
+            cur = n1; n1 = n2; n2 = n3;
         }
         for (int32_t i = m + (int32_t)lane; i < n; i += 32) {
             const int64_t s = sg.start + i;

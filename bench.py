@@ -132,7 +132,7 @@ def stage_work(name, n_samples, n_rays, n_table_params, world=1):
         return 'hbm', 20.0 * n_samples + 20.0 * n_rays
     if name == 'composite_bwd':
         return 'hbm', 36.0 * n_samples + 20.0 * n_rays
-    if name == 'march_packed':
+    if name == 'march_packed':                   # latency-bound by design (a warp walks its ray); bytes given for reference only
         return 'hbm', 24.0 * n_rays + 8.0 * n_samples
     if name in ('mlp_geo_fwd',):
         return 'tensor', 6144.0 * n_samples
