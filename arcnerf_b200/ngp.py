@@ -150,7 +150,22 @@ class NGPPipeline:
             regions = {'grad': (nt + ng + nr) * 4, 'table_h': nt * 2}
             if self.exchange == 'peer16':
                 regions['grad16'] = nt * 2
-            self.arena = PeerArena(regions, dev, self.rank, self.world_size, share)
+            # peer mapping needs every rank to see every GPU of the node (a launcher that hides devices per process, or GPUs
+            # without P2P, makes cudaIpcOpenMemHandle fail): all ranks then agree to use the NCCL all-reduce instead
+            err = None
+            try:
+                self.arena = PeerArena(regions, dev, self.rank, self.world_size, share)
+            except RuntimeError as e:
+                err = e
+            ok = torch.tensor([0 if err is not None else 1], dtype=torch.int32, device=dev)
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            if int(ok.item()) == 0:
+                if self.rank == 0:
+                    import sys
+                    sys.stderr.write('arcnerf_b200: peer-memory exchange unavailable (%s); using the NCCL all-reduce\n'
+                                     % (err if err is not None else 'another rank could not map the arenas'))
+                self.arena, self.exchange = None, 'nccl'
+        if self.arena is not None:
             self.table_h = self.arena.local('table_h', torch.float16)
             F.cast_f16(self.table, self.table_h)
             self.slice = slice_bounds(nt, self.rank, self.world_size)

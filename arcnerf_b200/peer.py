@@ -39,10 +39,16 @@ class PeerArena:
         self.nbytes = off
         with torch.cuda.device(self.device):
             base, handle = C.c_void_p(), (C.c_ubyte * 64)()
-            _lib.call('arcb200_peer_alloc', self.nbytes, C.byref(base), handle)
+            alloc_err = None
+            try:
+                _lib.call('arcb200_peer_alloc', self.nbytes, C.byref(base), handle)
+            except RuntimeError as e:                       # still take part in the exchange: the others are waiting in it
+                alloc_err = e
             self.base = base.value
-            handles = exchange(bytes(handle))
+            handles = exchange(None if alloc_err is not None else bytes(handle))
             assert len(handles) == world
+            if alloc_err is not None or any(h is None for h in handles):
+                raise RuntimeError('peer arena allocation failed on a rank: %s' % (alloc_err or 'see that rank'))
             self.bases = []
             for w, h in enumerate(handles):
                 if w == rank:
