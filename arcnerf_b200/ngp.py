@@ -192,6 +192,10 @@ class NGPPipeline:
         half = cfg['side'] / 2.0
         self.aabb = torch.tensor([[-half] * 3, [half] * 3], dtype=torch.float32, device=dev)   # (2,3) min; max
         self.volume = torch.ones((n, n, n), dtype=torch.bool, device=dev)
+        # occupancy='bitfield' (overrides): march through the Morton-ordered bit field of BitfieldBound instead of the bool
+        # volume of VolumeBound (sparse_volume_sampling_bit, arcnerf/ops/bitfield_func.py:17-61); 256 KB instead of 2 MB
+        self.use_bits = cfg.get('occupancy', 'volume') == 'bitfield'
+        self.bits = torch.full((n * n * n // 8, ), 255, dtype=torch.uint8, device=dev) if self.use_bits else None
         self.dt = float(np.float32(cfg['side'] * math.sqrt(3.0)) / np.float32(cfg['n_sample']))   # diag / n_sample
         self.rng = _lib.Rng()
         self.timer = None
@@ -247,6 +251,9 @@ class NGPPipeline:
         v = torch.as_tensor(volume_bool).to(self.dev, torch.bool).contiguous()
         assert v.shape == self.volume.shape
         self.volume.copy_(v)
+        if self.use_bits:
+            from . import synth
+            self.bits.copy_(torch.from_numpy(synth.volume_to_bitfield(v.cpu().numpy())).to(self.dev))
 
     # ------------------------------------------------------------------------------------------ occupancy maintenance
     @torch.no_grad()
@@ -303,6 +310,23 @@ class NGPPipeline:
         `epoch_optim` steps; warm-up sweeps every voxel, afterwards 1/4 random + 1/4 occupied voxels.
         apply=False does all the work but leaves the sampler's volume as it is (benchmarks on a fixed synthetic scene)."""
         bound = getattr(self, 'bound', None)
+        if self.use_bits:
+            # BitfieldBound: density grid + Morton bit field, the instant-ngp rule (bitfield_bound.py:130-189)
+            if bound is None:
+                from .plugin.obj_bound import BitfieldBound
+                cfg = self.cfg
+                bound = BitfieldBound(dict(bitfield=dict(n_grid=cfg['n_grid'], side=cfg['side']),
+                                           epoch_optim=cfg.get('epoch_optim', 16),
+                                           epoch_optim_warmup=cfg.get('epoch_optim_warmup', 256),
+                                           near_distance=cfg['near_distance'], opa_thres=cfg.get('opa_thres', 0.01)))
+                self.bound = bound = bound.to(self.dev)
+                bound.density_bitfield.copy_(self.bits)
+            bound.optimize(cur_epoch, self.cfg['n_sample'], self.get_est_opacity)
+            if apply:
+                self.bits.copy_(bound.density_bitfield)
+                for ss in self.sets:
+                    ss.key = None
+            return
         if bound is None:
             from .plugin.obj_bound import VolumeBound
             cfg = self.cfg
@@ -330,9 +354,9 @@ class NGPPipeline:
             'arcb200_aabb_intersection', rays_o.data_ptr(), rays_d.data_ptr(), self.aabb.data_ptr(),
             ss.near.data_ptr(), ss.far.data_ptr(), None, ss.hit.data_ptr(), R, 1, st))
         self._run('march_packed', lambda: _lib.call(
-            'arcb200_march_packed', 0, rays_o.data_ptr(), rays_d.data_ptr(), ss.near.data_ptr(),
+            'arcb200_march_packed', int(self.use_bits), rays_o.data_ptr(), rays_d.data_ptr(), ss.near.data_ptr(),
             ss.far.data_ptr(), cfg['n_sample'], self.dt, self.aabb.data_ptr(), cfg['n_grid'],
-            self.volume.data_ptr(), cfg['near_distance'], R, self.rng.state, self.rng.inc,
+            (self.bits if self.use_bits else self.volume).data_ptr(), cfg['near_distance'], R, self.rng.state, self.rng.inc,
             ss.scratch.data_ptr(), ss.counts.data_ptr(), ss.offsets.data_ptr(), ss.meta.data_ptr(),
             self.capacity, ss.t.data_ptr(), None, ss.ray_id.data_ptr(), ss.unit.data_ptr(), st))
         self.rng.advance()

@@ -170,3 +170,33 @@ def test_occupancy_refresh_through_volume_bound():
     t = torch.rand((512, 3), device='cuda')
     loss = pipe.train_step(torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda(), t)
     assert torch.isfinite(loss).all()
+
+
+def test_bitfield_occupancy_gives_the_same_samples_and_step():
+    """occupancy='bitfield' (sparse_volume_sampling_bit on the Morton bit field) and the bool volume describe the same
+    scene: identical packed samples, identical forward, identical training step; the BitfieldBound refresh runs."""
+    from arcnerf_b200 import synth
+    from arcnerf_b200.ngp import NGP_DEFAULTS, NGPPipeline, init_params
+    params = init_params(dict(NGP_DEFAULTS), seed=5, grid_scale=0.5)
+    occ = synth.occupancy_volume('lego')
+    pipes = []
+    for kind in ('volume', 'bitfield'):
+        p = NGPPipeline(max_rays=1024, capacity=1 << 17, params={k: v.clone() for k, v in params.items()}, occupancy=kind)
+        p.set_occupancy(occ)
+        pipes.append(p)
+    o, d = synth.train_ray_batch(1024, seed=4)
+    o, d = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+    t = torch.rand((1024, 3), device='cuda')
+    outs = [p.forward(o, d, None) for p in pipes]
+    a, b = pipes
+    n = int(a.meta[0])
+    assert n == int(b.meta[0]) and n > 0 and torch.equal(a.counts, b.counts)
+    assert torch.equal(a.t[:n], b.t[:n]) and torch.equal(a.ray_id[:n], b.ray_id[:n]) and torch.equal(a.unit[:n], b.unit[:n])
+    for x, y in zip(outs[0], outs[1]):
+        assert torch.equal(x, y)
+    la, lb = float(a.train_step(o, d, t)), float(b.train_step(o, d, t))
+    assert abs(la - lb) <= 1e-5 * abs(la)
+    b.update_occupancy(16)                                   # warm-up refresh through BitfieldBound
+    count, ratio = b.bound.get_bitfield_count()
+    assert 0.0 < ratio <= 1.0 and torch.equal(b.bits, b.bound.density_bitfield)
+    assert torch.isfinite(b.train_step(o, d, t)).all()
