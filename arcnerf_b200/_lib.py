@@ -87,8 +87,10 @@ _SIGS = {
     'arcb200_grad_to_half': [P, P, L, L, L, F, P],
     'arcb200_adam_step_peer16': [P, P, P, I, I, L, L, P, P, P, F, I, F, F, F, F, F, F, P, P],
     'arcb200_adam_step_peer': [P, P, I, L, L, P, P, P, I, F, F, F, F, F, F, P, P],
+    'arcb200_probe_gather': [P, L, I, I, I, C.c_uint32, P, P],
 }
 _RESTYPE = {
+    'arcb200_probe_gather': C.c_longlong,
     'arcb200_last_error': C.c_char_p,
     'arcb200_rng_init': None,
     'arcb200_rng_advance': None,

@@ -33,6 +33,7 @@ SOURCES = {
     'zvals.cu': ['-fmad=false'],
     'volume_refresh.cu': [],
     'freq.cu': ['-fmad=false'],
+    'probe.cu': [],
 }
 
 

@@ -15,10 +15,17 @@
 // persistent grid-stride loop over tiles.  Per layer: one elected thread issues K/16 tcgen05.mma
 // (M=128, N=layer width), commits to an mbarrier; all threads then pull their accumulator row out of TMEM
 // (tcgen05.ld 32x32b), apply the activation and write the fp16 row back into the shared-memory operand tile of
-// the next layer.  The backward kernel re-computes the forward activations (tensor-core FLOPs are cheaper than
-// an HBM round trip for them), chains the data gradients the same way and accumulates the weight gradients
-// dW = G^T . H over ALL tiles of the CTA in TMEM (batch = contraction dimension, operands read MN-major from the
-// very same tiles), flushing them once per CTA with fp32 atomics.
+// the next layer.
+// Backward, two kernels:
+//   * mlp_bwd_v2_kernel (mlp_bwd_v2.cuh) - the training path of the NGP step: fp16 inputs, ReLU hidden layers of width 64 and
+//     hidden activations SAVED by the forward (`act_save`, reloaded into the operand tiles by bulk copies, nothing is
+//     re-computed).  One CTA per SM with four tile slots and a control warp that issues every MMA; weight-gradient
+//     accumulators shared by all slots in TMEM.  arcb200_mlp_bwd_ex selects it whenever those conditions hold.
+//   * mlp_bwd_kernel (below) - every other configuration reachable through the plugin API (fp32 inputs, other widths or
+//     activations, no saved activations): one tile per CTA, re-computes the forward activations on the tensor cores unless
+//     they were saved, chains the data gradients the same way and accumulates the weight gradients dW = G^T . H over ALL
+//     tiles of the CTA in TMEM (batch = contraction dimension, operands read MN-major from the very same tiles), flushing
+//     them once per CTA with fp32 atomics.
 #include "common.cuh"
 #include "tc05.cuh"
 #include "adam.cuh"

@@ -16,6 +16,7 @@
 // gradient nor write your table" after it.  Flags are epoch counters that only grow, kept in the shared arena.
 #include "adam.cuh"
 #include <string.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -244,10 +245,12 @@ __device__ __forceinline__ unsigned long long global_ns() {
 }
 
 // One block, one thread per rank.  epoch[0] += 1; publish it into slot `rank` of every rank's flag array, then wait
-// until every slot of the own array has reached it.  A wait longer than timeout_ns gives up and raises status[0]
-// (the step's results are then invalid, but the GPU is not left spinning).
+// until every slot of the own array has reached it.  A wait longer than timeout_ns raises status[0] and - unless the
+// caller asked for the probing mode (fatal == 0, tests) - traps: the step that follows would sum gradients a peer has not
+// finished and update the replicas differently on every rank, so a rank that fell out of step must end the job, not
+// continue (the trap surfaces as a launch failure at the next synchronisation; the GPU is not left spinning).
 __global__ void peer_barrier_kernel(const __grid_constant__ FlagList fl, int world, int rank,
-                                    unsigned long long *epoch, int32_t *status, unsigned long long timeout_ns) {
+                                    unsigned long long *epoch, int32_t *status, unsigned long long timeout_ns, int fatal) {
     arc_pdl_sync();
     __shared__ unsigned long long target;
     if (threadIdx.x == 0) {
@@ -265,6 +268,8 @@ __global__ void peer_barrier_kernel(const __grid_constant__ FlagList fl, int wor
         while (ld_acquire_sys(mine) < e) {
             if (global_ns() - t0 > timeout_ns) {
                 atomicExch(status, 1);
+                __threadfence_system();
+                if (fatal) __trap();
                 break;
             }
             __nanosleep(64);
@@ -327,7 +332,11 @@ int arcb200_peer_free(void *ptr) {
 
 // Flag barrier between the ranks of a node on `stream` (see the file header).  flags[w]: rank w's flag array
 // (>= 16 uint64, zero-initialised, in peer-mapped memory), as mapped in THIS process; epoch: this rank's device
-// counter (uint64, starts at 0, private); status: device int32 raised to 1 when a wait exceeded timeout_ms.
+// counter (uint64, starts at 0, private); status: device int32 raised to 1 when a wait exceeded the timeout.
+// timeout_ms > 0: that many milliseconds, FATAL (the kernel traps after raising status: a step computed from gradients a peer
+// has not finished must not be applied); timeout_ms == 0: the default, ARCB200_PEER_TIMEOUT_MS from the environment or
+// 600 000 ms (host work of minutes between steps - checkpoints, evaluation - is normal), fatal; timeout_ms < 0: -timeout_ms
+// milliseconds, NOT fatal (status only; for probing).
 int arcb200_peer_barrier(void *const *flags, int world, int rank, void *epoch, int32_t *status, int timeout_ms,
                          void *stream) {
     ARC_REQUIRE(flags && epoch && status, "peer_barrier: null pointer");
@@ -336,9 +345,15 @@ int arcb200_peer_barrier(void *const *flags, int world, int rank, void *epoch, i
     FlagList fl;
     for (int w = 0; w < kMaxWorld; ++w) fl.flags[w] = w < world ? (unsigned long long *)flags[w] : nullptr;
     for (int w = 0; w < world; ++w) ARC_REQUIRE(fl.flags[w] != nullptr, "peer_barrier: flags[%d] is null", w);
-    if (timeout_ms <= 0) timeout_ms = 20000;
+    int fatal = 1;
+    if (timeout_ms < 0) { fatal = 0; timeout_ms = -timeout_ms; }
+    if (timeout_ms == 0) {
+        const char *e = getenv("ARCB200_PEER_TIMEOUT_MS");
+        const long v = e ? atol(e) : 0;
+        timeout_ms = v > 0 && v < 2000000000L ? (int)v : 600000;
+    }
     arc_launch(peer_barrier_kernel, 1, 32, 0, (cudaStream_t)stream, fl, world, rank, (unsigned long long *)epoch, status,
-                                                           (unsigned long long)timeout_ms * 1000000ull);
+                                                           (unsigned long long)timeout_ms * 1000000ull, fatal);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }

@@ -157,13 +157,17 @@ class NGPPipeline:
                 self.arena = PeerArena(regions, dev, self.rank, self.world_size, share)
             except RuntimeError as e:
                 err = e
-            ok = torch.tensor([0 if err is not None else 1], dtype=torch.int32, device=dev)
+            ok = torch.tensor([0 if err is not None else 1], dtype=torch.int32, device=dev if dist.get_backend() != 'gloo' else 'cpu')
             dist.all_reduce(ok, op=dist.ReduceOp.MIN)
             if int(ok.item()) == 0:
                 if self.rank == 0:
                     import sys
                     sys.stderr.write('arcnerf_b200: peer-memory exchange unavailable (%s); using the NCCL all-reduce\n'
                                      % (err if err is not None else 'another rank could not map the arenas'))
+                if self.arena is not None:       # mapped here, but another rank could not: give the mappings and the arena back
+                    self.arena.close(sync_ranks=dist.barrier)
+                else:
+                    dist.barrier()
                 self.arena, self.exchange = None, 'nccl'
         if self.arena is not None:
             self.table_h = self.arena.local('table_h', torch.float16)
@@ -211,6 +215,7 @@ class NGPPipeline:
         e = lambda shape, dt: torch.empty(shape, dtype=dt, device=dev)
         self.sets = [SampleSet(R, C, self.cfg['n_sample'], dev), SampleSet(R, C, self.cfg['n_sample'], dev)]
         self.cur = 0
+        self.forward_serial = 0     # number of sample sets made current so far (stale-activation guard of the autograd wrapper)
         self.side_stream = torch.cuda.Stream(device=dev)
         self.enc = e((C, self.enc_dim), f16)
         self.rad_in = torch.zeros((C, self.rad_in_dim), dtype=f16, device=dev)
@@ -376,6 +381,7 @@ class NGPPipeline:
                 other.ready = None
             self._sample_into(other, rays_o, rays_d)
         self.cur = 1 - self.cur
+        self.forward_serial += 1
 
     def prefetch(self, rays_o, rays_d):
         """Sample the NEXT ray batch on the side stream while the current one is in the field kernels.  The set being
@@ -554,9 +560,13 @@ class NGPPipeline:
         pad = torch.zeros(per, dtype=torch.float32, device=self.dev)
         lo, hi = self.slice
         pad[:hi - lo] = self.table[lo:hi]
+        if dist.get_backend() == 'gloo':            # gloo gathers host tensors only
+            pad = pad.cpu()
         outs = [torch.empty_like(pad) for _ in range(self.world_size)]
         dist.all_gather(outs, pad)
         self.table.copy_(torch.cat(outs)[:nt])
+        if self.arena is not None:
+            self.arena.check()                      # the host is synchronised here anyway: a timed-out barrier is reported
         return self.table
 
     # ------------------------------------------------------------------------------------------ replayed step
@@ -654,6 +664,7 @@ class NGPPipeline:
             self._upload_and_sample(p, batch)
         ss.ready = None
         self.cur = p
+        self.forward_serial += 1
         if next_batch is not None:
             gate = self._gate_events[p]
             gate.record()                      # the side stream may touch slot 1-p once everything queued so far is done

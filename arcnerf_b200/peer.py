@@ -50,13 +50,20 @@ class PeerArena:
             if alloc_err is not None or any(h is None for h in handles):
                 raise RuntimeError('peer arena allocation failed on a rank: %s' % (alloc_err or 'see that rank'))
             self.bases = []
-            for w, h in enumerate(handles):
-                if w == rank:
-                    self.bases.append(self.base)
-                    continue
-                p = C.c_void_p()
-                _lib.call('arcb200_peer_open', (C.c_ubyte * 64).from_buffer_copy(h), C.byref(p))
-                self.bases.append(p.value)
+            try:
+                for w, h in enumerate(handles):
+                    if w == rank:
+                        self.bases.append(self.base)
+                        continue
+                    p = C.c_void_p()
+                    _lib.call('arcb200_peer_open', (C.c_ubyte * 64).from_buffer_copy(h), C.byref(p))
+                    self.bases.append(p.value)
+            except RuntimeError:
+                for w, b in enumerate(self.bases):          # unmap what was mapped before the failure
+                    if w != rank and b:
+                        _lib.call('arcb200_peer_close', b)
+                self.bases = None
+                raise
         self._bytes = torch.as_tensor(_DevMem(self.base, self.nbytes), device=self.device)
         self.epoch = torch.zeros(1, dtype=torch.int64, device=self.device)
         self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
@@ -73,7 +80,8 @@ class PeerArena:
         return (C.c_void_p * self.world)(*[b + off for b in self.bases])
 
     def barrier(self, timeout_ms=0):
-        """flag barrier between the ranks, on the current stream (nothing blocks on the host)"""
+        """flag barrier between the ranks, on the current stream (nothing blocks on the host).  A rank that waits longer than
+        the timeout (default ARCB200_PEER_TIMEOUT_MS or 10 minutes) ends the job: the kernel traps, see arcb200_peer_barrier"""
         _lib.call('arcb200_peer_barrier', self._flag_ptrs, self.world, self.rank, self.epoch.data_ptr(),
                   self.status.data_ptr(), int(timeout_ms), _lib.current_stream())
 
@@ -82,15 +90,23 @@ class PeerArena:
         if int(self.status.item()) != 0:
             raise RuntimeError('peer barrier timed out on rank %d: the ranks are not executing the same steps' % self.rank)
 
-    def close(self):
+    def close(self, sync_ranks=None):
+        """Unmap the peers' arenas and free the own one.  sync_ranks: a callable that returns once EVERY rank has unmapped
+        (e.g. torch.distributed.barrier) - the own allocation is only released after it, so that no peer still has it
+        mapped; without it the own arena is left to the process exit."""
         if getattr(self, 'bases', None) is None:
             return
         torch.cuda.synchronize(self.device)
         self._bytes = None
         for w, b in enumerate(self.bases):
-            if w != self.rank:
+            if w != self.rank and b:
                 _lib.call('arcb200_peer_close', b)
         self.bases = None
+        if sync_ranks is not None:
+            sync_ranks()
+            if self.base:
+                _lib.call('arcb200_peer_free', self.base)
+                self.base = None
 
 
 def adam_step_peer(grads, half_out, world, lo, hi, p, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8,

@@ -30,13 +30,13 @@ class _RenderFn(torch.autograd.Function):
         R = rays_o.shape[0]
         rgb, depth, mask = pipe.forward(rays_o, rays_d, bkg)
         ctx.model, ctx.R, ctx.bkg, ctx.rays_d = model, R, bkg, rays_d
-        ctx.set_key = id(pipe.sets[pipe.cur])
+        ctx.set_key = pipe.forward_serial            # counts every sample() of the pipeline: two alternating sets would alias
         return rgb.clone(), depth.clone(), mask.clone(), pipe.counts[:R].clone()
 
     @staticmethod
     def backward(ctx, g_rgb, g_depth, g_mask, _g_counts):
         pipe, R = ctx.model.pipe, ctx.R
-        if ctx.set_key != id(pipe.sets[pipe.cur]):
+        if ctx.set_key != pipe.forward_serial:
             raise RuntimeError('backward through a chunk whose samples were overwritten by a later forward: '
                                'differentiate one chunk at a time (training batches fit one chunk)')
         pipe.g_all.zero_()

@@ -149,12 +149,11 @@ def run_reference_arm(args, rank, world):
     """CPU implementation of the same step (oracle port) on the host cores; rank 0 only."""
     if rank != 0:
         return
-    from arcnerf_b200 import synth
-    from arcnerf_b200.ngp import NGP_DEFAULTS, init_params
-    from oracle.ngp import NGPOracle
+    from arcnerf_b200 import synth                       # numpy-only input generators; the product library is not loaded
+    from oracle.ngp import NGP_CONFIG, NGPOracle, init_params
     threads = os.cpu_count() or 1
     torch.set_num_threads(threads)
-    cfg = dict(NGP_DEFAULTS)
+    cfg = dict(NGP_CONFIG)
     params = init_params(cfg, seed=1337)
     orc = NGPOracle({k: v.numpy() for k, v in params.items()}, cfg, threads=threads)
     orc.set_occupancy(synth.occupancy_volume('lego'))
@@ -174,7 +173,7 @@ def run_reference_arm(args, rank, world):
                 dtype='fp16 storage / fp32 accumulate (CPU emulation)', data='synthetic',
                 config=dict(workload=WORKLOAD, rays_per_step=sample_rays),
                 cpu_baseline=dict(value=value, unit=UNIT, cores=threads, kind='port',
-                                  sample='%d steps of %d rays (bounded sample of the 4096-ray step) through oracle/ngp.py: '
+                                  sample='%d steps of %d rays (the GPU arm steps 4096 rays) through oracle/ngp.py: '
                                          'C sampler + torch-CPU hash grid / MLPs / ray_marching + torch Adam' % (args.steps, sample_rays)),
                 e2e=dict(value=value, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0))
     print(json.dumps(line))
@@ -189,7 +188,7 @@ def main():
     ap.add_argument('--steps', type=int, default=50)
     ap.add_argument('--warmup', type=int, default=10)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--ref-rays', type=int, default=1024, help='rays per step of the CPU arm (bounded sample)')
+    ap.add_argument('--ref-rays', type=int, default=N_RAYS, help='rays per step of the CPU arm (default: the same 4096-ray step as the GPU arm)')
     ap.add_argument('--no-render', action='store_true')
     ap.add_argument('--occ-every', type=int, default=16, help='occupancy refresh period in steps (0 = never); the reference config uses 16')
     ap.add_argument('--no-cpu-baseline', action='store_true')
@@ -390,11 +389,10 @@ def main():
     # ---- CPU baseline (rank 0, N = 1 only): bounded sample of the same step through the oracle port
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        from arcnerf_b200.ngp import NGP_DEFAULTS, init_params
-        from oracle.ngp import NGPOracle
+        from oracle.ngp import NGP_CONFIG, NGPOracle, init_params
         threads = os.cpu_count() or 1
         torch.set_num_threads(threads)
-        cfg = dict(NGP_DEFAULTS)
+        cfg = dict(NGP_CONFIG)
         orc = NGPOracle({k: v.numpy() for k, v in init_params(cfg, seed=1337).items()}, cfg, threads=threads)
         orc.set_occupancy(synth.occupancy_volume('lego'))
         o, d, t, b = (x.numpy()[:args.ref_rays] for x in host[0])
@@ -404,13 +402,13 @@ def main():
         o, d, t, b = (x.numpy()[:args.ref_rays] for x in host[1])
         orc.train_step(o, d, t, b)
         one = time.perf_counter() - t0
-        n_cpu = int(min(60, max(4, 12.0 / max(one, 1e-3))))
+        n_cpu = int(min(60, max(3, 12.0 / max(one, 1e-3))))
         for i in range(1, n_cpu):
             o, d, t, b = (x.numpy()[:args.ref_rays] for x in host[(1 + i) % len(host)])
             orc.train_step(o, d, t, b)
         dt = time.perf_counter() - t0
         cpu_baseline = dict(value=args.ref_rays * n_cpu / dt, unit=UNIT, cores=threads, kind='port',
-                            sample='%d steps of %d rays (bounded sample of the 4096-ray step), oracle/ngp.py: C sampler + '
+                            sample='%d steps of %d rays (the GPU arm steps 4096 rays), oracle/ngp.py: C sampler + '
                                    'torch-CPU hash grid / MLPs / ray_marching + torch Adam over the 12.2 M-parameter table'
                                    % (n_cpu, args.ref_rays))
 

@@ -411,8 +411,10 @@ int arcb200_peer_open(const unsigned char *handle /* 64 bytes */, void **ptr_out
 int arcb200_peer_close(void *ptr);
 int arcb200_peer_free(void *ptr);
 /* Flag barrier between ranks on `stream`: flags[w] = rank w's flag array (16 uint64, zeroed) as mapped in this
- * process; epoch = private device uint64 (starts at 0); status = device int32 set to 1 if a wait exceeded
- * timeout_ms (<= 0: 20 s) - the kernel then gives up instead of spinning forever. */
+ * process; epoch = private device uint64 (starts at 0); status = device int32 set to 1 if a wait exceeded the
+ * timeout.  timeout_ms > 0: fatal after that many ms (status is raised, then the kernel traps - a step built on a peer's
+ * unfinished gradient must not be applied, the job ends with a launch failure at the next synchronisation);
+ * timeout_ms == 0: default = ARCB200_PEER_TIMEOUT_MS or 600 000 ms, fatal; timeout_ms < 0: |timeout_ms| ms, status only. */
 int arcb200_peer_barrier(void *const *flags, int world, int rank, void *epoch, int32_t *status, int timeout_ms,
                          void *stream);
 /* Adam over elements [lo, hi) (lo % 4 == 0) of a flat parameter vector on the gradient summed over grads[0..world)
@@ -431,6 +433,14 @@ int arcb200_adam_step_peer16(float *g_own, const void *const *grads16, void *con
                              int64_t lo, int64_t hi, float *p, float *m, float *v, float scale, int step, float lr,
                              float beta1, float beta2, float eps, float weight_decay, float grad_scale,
                              const int32_t *step_dev, void *stream);
+
+/* ---- measurement aid (csrc/probe.cu) ---------------------------------------------------------------------------------
+ * Random-gather bandwidth of a device table: n_threads (rounded up to 256) threads issue trips * 8 independent loads of
+ * req_bytes (4, 8 or 16) at uniformly random entries of `table` (n_bytes) and write one checksum each to sink
+ * (n_threads uint32).  The roof the hash-grid kernels are compared with; no counterpart in the reference.
+ * Returns the number of requests issued, negative on error. */
+long long arcb200_probe_gather(const void *table, int64_t n_bytes, int req_bytes, int n_threads, int trips, uint32_t seed,
+                               uint32_t *sink, void *stream);
 
 #ifdef __cplusplus
 }

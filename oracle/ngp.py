@@ -22,6 +22,38 @@ from .sampler import Sampler
 PY = 2654435761
 PZ = 805459861
 
+# The reference's NGP configuration (configs/models/nerf_ngp.yaml + configs/expr/NeRF/lego/nerf_lego_nerf_ngp.yaml); the same
+# values as arcnerf_b200.ngp.NGP_DEFAULTS (tests/test_oracle_ngp.py checks that), kept here so that the timed CPU arm of
+# bench.py never imports the product package.
+NGP_CONFIG = dict(
+    n_levels=16, n_features=2, log2_hashmap_size=19, base_res=16, max_res=2048,
+    geo_width=64, geo_hidden=1, w_feat=16, rad_width=64, rad_hidden=2, sh_degree=4,
+    n_grid=128, side=2.0, n_sample=1024, near_distance=0.2,
+    lr=1e-1, beta1=0.9, beta2=0.999, eps=1e-15, weight_decay=1e-6,
+    huber_delta=0.1, loss_weight=3000.0, trunc_exp_clip=15.0,
+)
+
+
+def init_params(cfg, seed=1337, grid_scale=1e-4):
+    """Random-init parameters in the reference's layouts, byte-identical to arcnerf_b200.ngp.init_params (same torch CPU
+    generator, same draw order) but with the level geometry taken from oracle.fields.grid_geometry: hash table
+    U(-grid_scale, grid_scale) (tcnn grid.h:1353-1356), MLP matrices xavier-uniform (fully_fused_mlp.cu:859-885)."""
+    import math
+    g = torch.Generator().manual_seed(seed)
+    pls = float(torch.exp(torch.log(torch.tensor(cfg['max_res'] / cfg['base_res'])) / (float(cfg['n_levels']) - 1)))
+    geom = fields.grid_geometry(cfg['n_levels'], cfg['log2_hashmap_size'], cfg['base_res'], pls)
+    n_table = int(geom[0][-1]) * cfg['n_features']
+    table = (torch.rand(n_table, generator=g) * 2 - 1) * grid_scale
+
+    def mlp(in_dim, width, hidden, out_dim):
+        in_pad, out_pad = (in_dim + 15) // 16 * 16, (out_dim + 15) // 16 * 16
+        shapes = [(width, in_pad)] + [(width, width)] * (hidden - 1) + [(out_pad, width)]
+        return torch.cat([(torch.rand(o * i, generator=g) * 2 - 1) * math.sqrt(6.0 / (i + o)) for o, i in shapes])
+
+    geo = mlp(cfg['n_levels'] * cfg['n_features'], cfg['geo_width'], cfg['geo_hidden'], cfg['w_feat'])
+    rad = mlp(cfg['w_feat'] + cfg['sh_degree'] ** 2, cfg['rad_width'], cfg['rad_hidden'], 3)
+    return dict(table=table, geo=geo, rad=rad)
+
 
 class TorchGrid:
     """torch-CPU restatement of the hash-grid encode / table gradient (same arithmetic as fields.grid_encode with

@@ -71,3 +71,15 @@ def test_ngp_oracle_step():
     assert abs(fd - an) <= 0.1 * abs(an) + 1.0
     l0 = orc2.train_step(o, d, tgt, bkg)
     assert np.isfinite(l0) and not np.array_equal(orc2.rad_p, params['rad'])
+
+
+def test_oracle_config_and_init_match_the_product():
+    """bench.py's CPU arm takes its configuration and initial parameters from oracle/ (it must not import the product); they have
+    to be the same values and bytes the GPU arm uses."""
+    import torch
+    from arcnerf_b200.ngp import NGP_DEFAULTS, init_params as product_init
+    from oracle.ngp import NGP_CONFIG, init_params as oracle_init
+    assert NGP_CONFIG == NGP_DEFAULTS
+    a, b = product_init(dict(NGP_DEFAULTS), seed=5), oracle_init(dict(NGP_CONFIG), seed=5)
+    for k in ('table', 'geo', 'rad'):
+        assert torch.equal(a[k], b[k]), k

@@ -99,23 +99,32 @@ def test_peer_barrier_single_rank_and_timeout():
     # two 'ranks' sharing one flag array layout, but rank 1 never arrives
     other = torch.zeros(32, dtype=torch.int64, device='cuda')
     fp2 = _ptrs([flags, other])
-    _lib.call('arcb200_peer_barrier', fp2, 2, 0, epoch.data_ptr(), status.data_ptr(), 50, _lib.current_stream())
+    _lib.call('arcb200_peer_barrier', fp2, 2, 0, epoch.data_ptr(), status.data_ptr(), -50, _lib.current_stream())   # < 0: probing mode, no trap
     torch.cuda.synchronize()
     assert int(status) == 1 and int(other[0]) == 4
 
 
-def _two_rank_worker(rank, world, port, out_dir):
+def _two_rank_worker(rank, world, port, out_dir, one_device):
+    """one_device: both ranks on GPU 0 (a 1-GPU lease).  Two processes can IPC-map each other's arenas on one device and the
+    GPU time-slices their kernels, so the arena mapping, the flag barriers and both peer exchange modes run exactly as on
+    two GPUs; only NCCL refuses two ranks on one device, so the process group (handle exchange, the all-reduce of the
+    checked alternative) is gloo there."""
     import torch.distributed as dist
     os.environ['MASTER_ADDR'], os.environ['MASTER_PORT'] = '127.0.0.1', str(port)
-    torch.cuda.set_device(rank)
-    dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
+    os.environ.setdefault('ARCB200_PEER_TIMEOUT_MS', '30000')       # a stuck barrier fails the test instead of hanging it
+    dev = 0 if one_device else rank
+    torch.cuda.set_device(dev)
+    if one_device:
+        dist.init_process_group('gloo', rank=rank, world_size=world)
+    else:
+        dist.init_process_group('nccl', rank=rank, world_size=world, device_id=torch.device('cuda', rank))
     from arcnerf_b200 import synth
     from arcnerf_b200.ngp import NGP_DEFAULTS, NGPPipeline, init_params
     params = init_params(dict(NGP_DEFAULTS), seed=3, grid_scale=0.5)
     n = 1024
     res = {}
     for mode in ('nccl', 'peer', 'peer16'):
-        pipe = NGPPipeline(max_rays=n, capacity=1 << 17, device='cuda:%d' % rank, world_size=world, exchange=mode,
+        pipe = NGPPipeline(max_rays=n, capacity=1 << 17, device='cuda:%d' % dev, world_size=world, exchange=mode,
                            params={k: v.clone() for k, v in params.items()}, lr=1e-2)
         pipe.set_occupancy(synth.occupancy_volume('lego'))
         losses = []
@@ -125,7 +134,8 @@ def _two_rank_worker(rank, world, port, out_dir):
             dv = [torch.from_numpy(x).cuda() for x in (o, d, t)]
             losses.append(float(pipe.train_step(*dv)))
         torch.cuda.synchronize()
-        if pipe.arena is not None:
+        if mode != 'nccl':
+            assert pipe.arena is not None and pipe.exchange == mode, 'peer arena was not mapped: fell back to %s' % pipe.exchange
             pipe.arena.check()
         res[mode] = dict(table=pipe.gather_master_table().clone(), table_h=pipe.table_h.clone(), geo=pipe.geo_p.clone(),
                          rad=pipe.rad_p.clone(), loss=losses)
@@ -144,7 +154,7 @@ def _two_rank_worker(rank, world, port, out_dir):
             ok = False
             msg.append('%s losses differ %s %s' % (mode_b, res['nccl']['loss'], res[mode_b]['loss']))
         # replicas agree across ranks
-        th = res[mode_b]['table_h'].float()
+        th = res[mode_b]['table_h'].float().cpu()
         other = [torch.empty_like(th) for _ in range(world)]
         dist.all_gather(other, th)
         if not all(torch.equal(o, th) for o in other):
@@ -156,11 +166,13 @@ def _two_rank_worker(rank, world, port, out_dir):
     dist.destroy_process_group()
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason='needs two GPUs on one node')
 def test_two_ranks_peer_exchange_matches_all_reduce(tmp_path):
+    """two processes, IPC-mapped arenas, flag barriers, 'peer' and the default 'peer16' exchange against the all-reduce path;
+    on a 1-GPU lease both ranks share device 0"""
     import torch.multiprocessing as mp
     port = 29500 + (os.getpid() % 400)
-    mp.spawn(_two_rank_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    one_device = torch.cuda.device_count() < 2
+    mp.spawn(_two_rank_worker, args=(2, port, str(tmp_path), one_device), nprocs=2, join=True)
     for r in range(2):
         assert open(tmp_path / ('rank%d.txt' % r)).read() == 'OK'
 
