@@ -14,10 +14,13 @@ arithmetic, each function citing the lines it follows:
     encodings/spherical_harmonics.h:46-152   kernel_sh
     src/fully_fused_mlp.cu:315-557,658-671   layer order, weight layout, no biases, fp16 storage
     encodings/identity.h:46-69      input padding with ones
-PARITY PINNING: the reference ships no golden vectors for these and tiny-cuda-nn cannot be
-executed here; this part of the oracle is therefore "parity unpinned" against tiny-cuda-nn itself.  It is
-cross-checked where the reference has runnable code of its own: the SH basis against ArcNerf's torch SHEmbedder
-(sh_encoder.py:126-199) and the trilinear weights against Volume (tests/golden/make_golden_torch.py).
+PARITY PINNING: pinned against tiny-cuda-nn itself.  The reference's own tiny-cuda-nn sources are built for sm_100 by
+`make -C oracle tcnn` (oracle/tcnn_harness.cu -> oracle/_ref/libtcnnref.so), executed on a B200 by
+tests/golden/make_golden_tcnn.py, and the outputs are committed as tests/golden/tcnn_golden.npz; tests/test_oracle_tcnn.py
+checks every function below against that file (grid forward in fp16-accumulate mode is BIT-EXACT with the level scales the
+device computed; gradients, double backward, SH and the MLPs within the tolerances stated there), and
+tests/test_tcnn_parity_gpu.py checks the CUDA path against the same file.  The SH basis is additionally checked against
+ArcNerf's torch SHEmbedder (sh_encoder.py:126-199) and the trilinear weights against Volume (tests/golden/make_golden_torch.py).
 """
 import numpy as np
 

@@ -25,6 +25,12 @@ def build(ref=True):
     subprocess.check_call(['make', '-s', '-C', _HERE, 'oracle'])
     if ref and os.path.isdir('/root/reference/arcnerf/ops/include'):
         subprocess.check_call(['make', '-s', '-C', _HERE, 'ref'])
+        # the reference's device kernels for sm_100 (run only on the GPU box, by scripts/ref_kernels_on_box.py)
+        subprocess.check_call(['make', '-s', '-C', _HERE, 'ref_dev'])
+        # tiny-cuda-nn for sm_100 takes about 15 minutes from scratch: only on request (the golden vectors it produced are
+        # committed, tests never need the library itself)
+        if os.environ.get('ARCB200_BUILD_TCNN') == '1':
+            subprocess.check_call(['make', '-s', '-j4', '-C', _HERE, 'tcnn'])
 
 
 def have_ref():

@@ -9,6 +9,7 @@
 // write the golden vectors that pin oracle/fields.py and the CUDA path (hash grid, SH, FullyFusedMLP), and
 // to time the reference's kernels on the same B200.
 #include <tiny-cuda-nn/cpp_api.h>
+#include <tiny-cuda-nn/encodings/grid.h>
 #include <cuda_runtime.h>
 #include <cstdint>
 #include <cstdio>
@@ -16,6 +17,11 @@
 #include <string>
 
 using namespace tcnn::cpp;
+
+__global__ void device_scales_kernel(int n_levels, float log2_per_level_scale, uint32_t base_resolution, float *out) {
+    const int l = threadIdx.x;
+    if (l < n_levels) out[l] = tcnn::grid_scale((uint32_t)l, log2_per_level_scale, base_resolution);
+}
 
 namespace {
 thread_local std::string g_err;
@@ -90,5 +96,11 @@ int tcnnref_backward_backward_input(void *m, void *stream, void *ctx, unsigned n
 }
 
 void tcnnref_free_temporary_memory() { free_temporary_memory(); }
+
+// The level scales as kernel_grid computes them per thread (grid.h:270-271 -> grid_scale, :195-200): the device's exp2f is not
+// bit-identical to the host's, so the golden file records what the kernels actually used.
+void tcnnref_device_grid_scales(int n_levels, float log2_per_level_scale, int base_resolution, float *out_dev) {
+    device_scales_kernel<<<1, 64>>>(n_levels, log2_per_level_scale, (uint32_t)base_resolution, out_dev);
+}
 
 }  // extern "C"

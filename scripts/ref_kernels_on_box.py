@@ -114,10 +114,11 @@ def sampler_part(out):
         near = np.full((n, 1), 0.0, np.float32); far = np.full((n, 1), 20.0, np.float32)
         z = torch.zeros((n, c['n_pts']), device='cuda'); m = torch.zeros((n, c['n_pts']), dtype=torch.uint8, device='cuda')
         bits = cu(c['bits'])
+        near_d, far_d, mab_d, ab_d = cu(near), cu(far), cu(c['min_aabb']), cu(c['aabb'])     # keep the device copies alive
         ref['multivol'].arcrefdev_reset_rng()
         ref['multivol'].arcrefdev_sparse_sampling_in_multivol_bitfield(
-            n, P(o), P(d), P(cu(near)), P(cu(far)), c['n_pts'], C.c_float(c['cone']), C.c_float(c['smin']), C.c_float(c['smax']),
-            P(cu(c['min_aabb'])), P(cu(c['aabb'])), c['n_grid'], c['n_cascade'], P(bits), C.c_int64(bits.numel()),
+            n, P(o), P(d), P(near_d), P(far_d), c['n_pts'], C.c_float(c['cone']), C.c_float(c['smin']), C.c_float(c['smax']),
+            P(mab_d), P(ab_d), c['n_grid'], c['n_cascade'], P(bits), C.c_int64(bits.numel()),
             C.c_float(c['near_distance']), int(inclusive), P(z), P(m))
         torch.cuda.synchronize()
         oz, omk = orc.sparse_sampling_in_multivol_bitfield(c['o'], c['d'], near, far, c['n_pts'], c['cone'], c['smin'], c['smax'],

@@ -130,6 +130,11 @@ def main(out_path):
                          'log2_hashmap_size': g['log2_hashmap_size'], 'base_resolution': g['base_res'],
                          'per_level_scale': pls})
     G['grid_n_params'] = np.array(enc.n_params)
+    # the per-level scales exactly as tcnn's kernels compute them on the device (exp2f there is not the host's)
+    sc = torch.zeros(g['n_levels'], dtype=torch.float32, device='cuda')
+    T.lib.tcnnref_device_grid_scales(g['n_levels'], C.c_float(float(np.log2(np.float32(pls)))), g['base_res'], C.c_void_p(sc.data_ptr()))
+    torch.cuda.synchronize()
+    G['grid_device_scales'] = sc.cpu().numpy()
     G['grid_per_level_scale'] = np.array(pls)
     assert enc.p16 and enc.o16 and enc.n_out == 32
     init = enc.initial_params(1337)
@@ -172,8 +177,14 @@ def main(out_path):
         torch.cuda.synchronize()
         G['mlp_%s_fwd' % name] = y.cpu().numpy()
         G['mlp_%s_inference' % name] = net.inference(xin, params).cpu().numpy()
+        net.free(ctx)
+        # backward on gate-stable rows (see tcnn_cases.mlp_inputs_gate_stable)
+        xs = cu(tc.mlp_inputs_gate_stable(in_dim, width, n_hidden, out_dim, params.float().cpu().numpy(), seed=500 + k))
+        ctx, ys = net.forward(xs, params, input_grad=True)
+        torch.cuda.synchronize()
+        G['mlp_%s_stable_fwd' % name] = ys.cpu().numpy()
         gy = cu(tc.mlp_dy(net.n_out, out_dim, seed=400 + k))
-        dx, dp = net.backward(ctx, xin, params, y, gy)
+        dx, dp = net.backward(ctx, xs, params, ys, gy)
         G['mlp_%s_dLdx' % name] = dx.cpu().numpy()
         G['mlp_%s_dLdp' % name] = dp.float().cpu().numpy()
         net.free(ctx)

@@ -49,8 +49,9 @@ def grid_dy(n=N_GRID_PTS, dim=32, seed=103):
 
 
 def grid_v(n=N_GRID_PTS, seed=104):
-    """dL/d(dL/dx) of the double backward"""
-    return np.random.RandomState(seed).normal(0.0, 1.0, (n, 3)).astype(np.float32)
+    """dL/d(dL/dx) of the double backward; small, so that tcnn's fp16 table gradient (x loss scale 128 x level scale up to
+    2047) stays below the fp16 maximum"""
+    return (np.random.RandomState(seed).normal(0.0, 1.0, (n, 3)) * 1e-3).astype(np.float32)
 
 
 def sh_dirs(n=N_GRID_PTS, seed=105):
@@ -77,6 +78,32 @@ def mlp_params(in_dim, width, n_hidden, out_dim, seed):
 
 def mlp_inputs(in_dim, n=N_MLP_ROWS, seed=0):
     return np.random.RandomState(seed).uniform(-1.0, 1.0, (n, in_dim)).astype(np.float32)
+
+
+def mlp_inputs_gate_stable(in_dim, width, n_hidden, out_dim, params, n=N_MLP_ROWS, seed=0, margin=0.02):
+    """Rows whose hidden pre-activations all stay `margin` away from zero: tcnn accumulates in fp16, so a ReLU whose argument
+    is within its rounding error of zero can be open in one implementation and shut in the other, which changes whole rows of
+    the gradients.  Backward parity is checked on rows where that cannot happen (the forward is checked on unfiltered rows).
+    Plain float64 forward on fp16-rounded weights and inputs padded with ones, no library involved."""
+    rs = np.random.RandomState(seed)
+    in_pad = (in_dim + 15) // 16 * 16
+    shapes = [(width, in_pad)] + [(width, width)] * (n_hidden - 1)
+    mats, off = [], 0
+    for o, i in shapes:
+        mats.append(params[off:off + o * i].reshape(o, i).astype(np.float16).astype(np.float64))
+        off += o * i
+    rows = []
+    while sum(len(r) for r in rows) < n:
+        x = rs.uniform(-1.0, 1.0, (8 * n, in_dim)).astype(np.float32)
+        h = np.ones((x.shape[0], in_pad))
+        h[:, :in_dim] = x.astype(np.float16).astype(np.float64)
+        ok = np.ones(x.shape[0], bool)
+        for w in mats:
+            z = h @ w.T
+            ok &= np.abs(z).min(1) > margin
+            h = np.maximum(z, 0).astype(np.float16).astype(np.float64)
+        rows.append(x[ok])
+    return np.concatenate(rows)[:n]
 
 
 def mlp_dy(out_pad, out_dim, n=N_MLP_ROWS, seed=0):
