@@ -20,45 +20,12 @@
 // Roofline: a pure gather - per sample 8 corners x L levels x F fp16 (512 B at L=16, F=2) out of a table that
 // is L2-resident on B200 (24.4 MB fp16 << 126 MB L2).  HBM sees only 12 B in + 2*L*F B out per sample.
 #include "common.cuh"
+#include "grid_math.cuh"
 #include <math.h>
 
 namespace {
 
-constexpr int kMaxLevels = 32;
-
-struct GridLevel {
-    uint32_t offset;   // first entry of this level in the flat table
-    uint32_t size;     // entries in this level
-    uint32_t res;      // vertices per axis
-    float scale;
-    uint32_t hashed;   // 1: coherent-prime hash, 0: dense stride index
-    uint32_t mask;     // size-1 when size is a power of two, else 0
-};
-struct GridGeom {
-    GridLevel lv[kMaxLevels];
-    uint32_t n_levels;
-};
-
-__device__ __forceinline__ uint32_t entry_index(const GridLevel &g, uint32_t x, uint32_t y, uint32_t z) {
-    uint32_t idx;
-    if (g.hashed) idx = x ^ (y * 2654435761u) ^ (z * 805459861u);
-    else idx = x + y * g.res + z * (g.res * g.res);
-    if (g.mask) return idx & g.mask;
-    return idx < g.size ? idx : idx % g.size;
-}
-
-struct Cell {
-    uint32_t gx, gy, gz;
-    float fx, fy, fz;
-};
-__device__ __forceinline__ Cell locate(const GridLevel &g, float x, float y, float z) {
-    Cell c;
-    float px = fmaf(x, g.scale, 0.5f), py = fmaf(y, g.scale, 0.5f), pz = fmaf(z, g.scale, 0.5f);
-    const float flx = floorf(px), fly = floorf(py), flz = floorf(pz);
-    c.gx = (uint32_t)(int)flx; c.gy = (uint32_t)(int)fly; c.gz = (uint32_t)(int)flz;
-    c.fx = px - flx; c.fy = py - fly; c.fz = pz - flz;
-    return c;
-}
+using namespace gridmath;
 
 template <int F>
 __device__ __forceinline__ void load_entry(const __half *__restrict__ level_table, uint32_t idx, float (&out)[F]);
@@ -340,25 +307,6 @@ unsigned tile_blocks(int64_t n) {
     long long want = (n + kTileSamples - 1) / kTileSamples;
     const long long cap = (long long)arc_sm_count() * 16;
     return (unsigned)(want < cap ? (want > 0 ? want : 1) : cap);
-}
-
-int pack_geom(GridGeom &geom, int n_levels, const uint32_t *offsets, const float *scales, const uint32_t *resolutions) {
-    if (n_levels < 1 || n_levels > kMaxLevels) return -1;
-    geom.n_levels = (uint32_t)n_levels;
-    for (int l = 0; l < n_levels; ++l) {
-        GridLevel &g = geom.lv[l];
-        g.offset = offsets[l];
-        g.size = offsets[l + 1] - offsets[l];
-        g.res = resolutions[l];
-        g.scale = scales[l];
-        // the reference's index loop (grid.h:170-187): dense while the running stride fits the level
-        uint32_t stride = 1;
-        for (int dim = 0; dim < 3 && stride <= g.size; ++dim) stride *= g.res;
-        g.hashed = g.size < stride ? 1u : 0u;
-        g.mask = (g.size & (g.size - 1)) == 0 ? g.size - 1 : 0u;
-        if (g.size == 0) return -1;
-    }
-    return 0;
 }
 
 }  // namespace

@@ -30,6 +30,7 @@
 #include "tc05.cuh"
 #include "adam.cuh"
 #include "sh.cuh"
+#include "grid_math.cuh"
 #include <string.h>
 #include <stdlib.h>
 
@@ -735,6 +736,7 @@ static unsigned mlp_grid(K kernel, int64_t n, size_t smem_bytes, uint32_t tmem_c
 }
 
 #include "mlp_bwd_v2.cuh"
+#include "field_fused.cuh"
 
 }  // namespace
 
@@ -986,6 +988,57 @@ int arcb200_mlp_bwd_ex(const void *X, int x_is_half, int64_t ldx, const void *bl
     else LAUNCH_BWD_T(512);
 #undef LAUNCH_BWD_T
 #undef LAUNCH_BWD
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// Fused field forward of the NGP foreground model (csrc/field_fused.cuh): positions in the unit cube -> density and colour
+// of every sample in ONE launch: hash-grid encode (16 levels x 2 features) -> geometry head 32-64-16 with the TruncExp
+// density on channel 0 -> [feature(16) | SH degree 4 of the view direction] -> radiance head 32-64-64-3 with a sigmoid.
+// Same values as arcb200_grid_fwd + arcb200_mlp_fwd_sh + arcb200_mlp_fwd_ex run one after the other.  Replaces
+// Base3dModel._forward_pts_dir for the NGP configuration (arcnerf/models/base_3d_model.py:233-254: geo_net(pts) then
+// radiance_net(pts, view_dirs, None, feat), i.e. tcnn_fusedmlp_module.py:81-111,177-192).
+//   unit (n,3) fp32; table_half + level geometry as for arcb200_grid_fwd (must be 16 levels x 2 features);
+//   geo_blob / rad_blob: packed weights of the 32-64-16 (ReLU, none) and 32-64-64-3 (ReLU, sigmoid) networks;
+//   dirs (n_rays,3) fp32 with ray_id (n) int32, or ray_id NULL and dirs (n,3); sh_remap as in arcb200_sh_fwd;
+//   sigma (n) fp32, rgb (n,3) fp32: outputs.  Optional outputs for the backward kernels (all or none may be NULL):
+//   enc_out (n,32) fp16, rad_in_out (n,32) fp16, geo_act / rad_act (arcb200_mlp_act_save_bytes each), zero_scalar (one
+//   float cleared by the launch).  n_dev: optional device row count.
+int arcb200_field_fwd(const float *unit, const void *table_half, int n_levels, int n_features, const uint32_t *offsets,
+                      const float *scales, const uint32_t *resolutions, const void *geo_blob, const void *rad_blob,
+                      const float *dirs, const int32_t *ray_id, int sh_remap, void *enc_out, void *rad_in_out, void *geo_act,
+                      void *rad_act, float *sigma, float *rgb, float *zero_scalar, int64_t n, const int32_t *n_dev,
+                      void *stream) {
+    ARC_REQUIRE(n >= 0 && n < (1ll << 31) - 256, "field_fwd: n out of range");
+    if (n == 0) return ARCB200_OK;
+    ARC_REQUIRE(unit && table_half && offsets && scales && resolutions && geo_blob && rad_blob && dirs && sigma && rgb,
+                "field_fwd: null pointer");
+    ARC_REQUIRE(n_levels == 16 && n_features == 2, "field_fwd: the fused kernel is built for 16 levels x 2 features (got %d x %d)",
+                n_levels, n_features);
+    ARC_REQUIRE((((uintptr_t)geo_blob | (uintptr_t)rad_blob | (uintptr_t)enc_out | (uintptr_t)rad_in_out | (uintptr_t)geo_act |
+                  (uintptr_t)rad_act) & 15u) == 0, "field_fwd: blobs and saved tensors must be 16-byte aligned");
+    gridmath::GridGeom geom;
+    ARC_REQUIRE(gridmath::pack_geom(geom, n_levels, offsets, scales, resolutions) == 0, "field_fwd: bad level geometry");
+    MlpCfg geo, rad;
+    make_cfg(geo, 32, 64, 1, 16, ACT_RELU, ACT_NONE);
+    make_cfg(rad, 32, 64, 2, 3, ACT_RELU, ACT_SIGMOID);
+    FieldFwdArgs a;
+    a.unit = unit; a.table = (const __half *)table_half; a.geo_blob = (const uint8_t *)geo_blob; a.rad_blob = (const uint8_t *)rad_blob;
+    a.dirs = dirs; a.ray_id = ray_id; a.sh_remap = sh_remap; a.enc_out = (__half *)enc_out; a.rad_in_out = (__half *)rad_in_out;
+    a.geo_act = (uint8_t *)geo_act; a.rad_act = (uint8_t *)rad_act; a.sigma = sigma; a.rgb = rgb; a.zero_scalar = zero_scalar;
+    const size_t smem = field_fwd_smem(geo, rad);
+    int rc = set_smem(field_fwd_kernel, smem);
+    if (rc != ARCB200_OK) return rc;
+    static thread_local int per_sm = 0;
+    if (per_sm == 0) {
+        int occ = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, field_fwd_kernel, kFieldThreads, smem) != cudaSuccess || occ < 1) { cudaGetLastError(); occ = 1; }
+        per_sm = occ > 8 ? 8 : occ;                    // 64 TMEM columns per CTA: eight CTAs fit an SM's tensor memory
+        if (const char *e = getenv("ARCB200_FIELD_CTAS_PER_SM")) { const int v = atoi(e); if (v > 0 && v < per_sm) per_sm = v; }
+    }
+    const int64_t tiles = (n + kRows - 1) / kRows, cap = (int64_t)arc_sm_count() * per_sm;
+    arc_launch(field_fwd_kernel, (unsigned)(tiles < cap ? tiles : cap), kFieldThreads, smem, (cudaStream_t)stream, n, n_dev, geom, geo,
+               rad, a);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }

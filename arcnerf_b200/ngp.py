@@ -203,6 +203,10 @@ class NGPPipeline:
         self.dt = float(np.float32(cfg['side'] * math.sqrt(3.0)) / np.float32(cfg['n_sample']))   # diag / n_sample
         self.rng = _lib.Rng()
         self.timer = None
+        # the fused field forward covers exactly the reference's NGP configuration (ARCB200_FUSED_FWD=0: separate launches)
+        self.fused_fwd = (os.environ.get('ARCB200_FUSED_FWD', '1') == '1' and cfg['n_levels'] == 16 and cfg['n_features'] == 2
+                          and (cfg['geo_width'], cfg['geo_hidden'], cfg['w_feat']) == (64, 1, 16)
+                          and (cfg['rad_width'], cfg['rad_hidden'], cfg['sh_degree']) == (64, 2, 4))
         self._alloc()
 
     def _run(self, name, fn):
@@ -399,6 +403,18 @@ class NGPPipeline:
     def field_forward(self, rays_d, clear_loss=False):
         """encode -> geometry head -> density | [feat, SH] -> radiance head, on the packed samples"""
         C, nd = self.capacity, self.n_dev
+        cfg = self.cfg
+        if self.fused_fwd:
+            # one launch: encode -> geometry head (+ density) -> [feat | SH] -> radiance head (csrc/field_fused.cuh)
+            tr = self.training
+            nl, nf, off, sc, rs = self.geom._args()
+            self._run('field_fwd', lambda: _lib.call(
+                'arcb200_field_fwd', self.unit.data_ptr(), self.table_h.data_ptr(), nl, nf, off, sc, rs, self.geo_blob.data_ptr(),
+                self.rad_blob.data_ptr(), rays_d.data_ptr(), self.ray_id.data_ptr(), 1, self.enc.data_ptr() if tr else None,
+                self.rad_in.data_ptr() if tr else None, self.geo_act.data_ptr() if tr else None,
+                self.rad_act.data_ptr() if tr else None, self.sigma.data_ptr(), self.rgb_s.data_ptr(),
+                self.loss.data_ptr() if clear_loss else None, C, nd.data_ptr(), _lib.current_stream()))
+            return
         self._run('grid_fwd', lambda: F.grid_forward(self.unit, self.table_h, self.geom, n_dev=nd, out=self.enc))
         # geometry head writes its W_feat outputs straight into the radiance input row; SH fills the rest
         # (the density sigma = TruncExp(channel 0) comes out of the same kernel's epilogue)
@@ -705,7 +721,7 @@ class NGPPipeline:
         return rgb, depth, acc
 
     # number of library kernels one train_step enqueues (for bench.py's gpu_launches)
-    LAUNCHES_FORWARD = 1 + 4 + 1 + 1 + 1 + 1          # aabb, march(4), grid, geo mlp (+density, +SH of the view direction), rad mlp, composite
+    LAUNCHES_FORWARD = 1 + 4 + 1 + 1                  # aabb, march(4), fused field forward (encode + both heads), composite
     LAUNCHES_TRAIN = LAUNCHES_FORWARD + 1 + 1 + 1 + 1 + 1   # (composite fused with loss + its backward + step count), rad bwd, geo bwd, grid bwd, table adam, heads adam+pack
     LAUNCHES_REFRESH = 4 + 2 * 3 + 4                   # candidates (count, scan, select, points), 2 chunks x (unit, grid, geo mlp), apply (fill, splat, ema, threshold)
     LAUNCHES_TRAIN_PEER = LAUNCHES_TRAIN + 2           # + two flag barriers (the gradient clear is a memset, not a kernel of ours)

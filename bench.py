@@ -120,6 +120,8 @@ EXCHANGE_NOTE = {
 def stage_work(name, n_samples, n_rays, n_table_params, world=1):
     if name == 'grid_fwd':
         return 'hbm', 588.0 * n_samples          # 12 B in + 16 levels * 8 corners * 4 B gathered + 64 B out
+    if name == 'field_fwd':                      # the gathers bound it (L1/L2 sector rate); MLP flops 20480/sample ride along
+        return 'hbm', (588.0 + 16.0) * n_samples  # encode bytes + sigma, rgb out
     if name == 'grid_bwd':
         return 'hbm', 588.0 * n_samples          # 12 B + 64 B in + 16*8 entries of 4 B updated
     if name == 'adam_table':

@@ -434,6 +434,21 @@ int arcb200_adam_step_peer16(float *g_own, const void *const *grads16, void *con
                              float beta1, float beta2, float eps, float weight_decay, float grad_scale,
                              const int32_t *step_dev, void *stream);
 
+/* ---- fused field forward (csrc/field_fused.cuh) -----------------------------------------------------------------------
+ * The NGP foreground model's per-sample network in one launch: hash-grid encode (16 levels x 2 features) -> geometry head
+ * 32-64-16 (TruncExp density on channel 0) -> [feature | SH degree 4 of the view direction] -> radiance head 32-64-64-3
+ * (sigmoid).  Replaces Base3dModel._forward_pts_dir for the NGP configuration (arcnerf/models/base_3d_model.py:233-254 ->
+ * FusedMLPGeoNet.forward / FusedMLPRadianceNet.forward, tcnn_fusedmlp_module.py:81-111,177-192); same values as
+ * arcb200_grid_fwd + arcb200_mlp_fwd_sh + arcb200_mlp_fwd_ex in sequence.  unit (n,3) fp32; dirs (n_rays,3) with ray_id (n)
+ * int32, or ray_id NULL and dirs (n,3); outputs sigma (n), rgb (n,3) fp32.  Optional (NULL to skip) outputs kept for the
+ * backward kernels: enc_out (n,32) fp16, rad_in_out (n,32) fp16, geo_act / rad_act (arcb200_mlp_act_save_bytes), and
+ * zero_scalar, one float the launch clears. */
+int arcb200_field_fwd(const float *unit, const void *table_half, int n_levels, int n_features, const uint32_t *offsets,
+                      const float *scales, const uint32_t *resolutions, const void *geo_blob, const void *rad_blob,
+                      const float *dirs, const int32_t *ray_id, int sh_remap, void *enc_out, void *rad_in_out, void *geo_act,
+                      void *rad_act, float *sigma, float *rgb, float *zero_scalar, int64_t n, const int32_t *n_dev,
+                      void *stream);
+
 /* ---- measurement aid (csrc/probe.cu) ---------------------------------------------------------------------------------
  * Random-gather bandwidth of a device table: n_threads (rounded up to 256) threads issue trips * 8 independent loads of
  * req_bytes (4, 8 or 16) at uniformly random entries of `table` (n_bytes) and write one checksum each to sink

@@ -200,3 +200,39 @@ def test_bitfield_occupancy_gives_the_same_samples_and_step():
     count, ratio = b.bound.get_bitfield_count()
     assert 0.0 < ratio <= 1.0 and torch.equal(b.bits, b.bound.density_bitfield)
     assert torch.isfinite(b.train_step(o, d, t)).all()
+
+
+def test_fused_field_forward_equals_separate_launches():
+    """arcb200_field_fwd (encode + both heads in one launch) against arcb200_grid_fwd + arcb200_mlp_fwd_sh + arcb200_mlp_fwd_ex:
+    same arithmetic, so every output and every tensor saved for the backward is identical"""
+    pipe, _, o, d, tgt, bkg = setup(900, 11)
+    assert pipe.fused_fwd
+    o_d, d_d = dev(o), dev(d)
+    out = {}
+    for fused in (True, False):
+        pipe.fused_fwd = fused
+        pipe.rng = type(pipe.rng)()                 # same start jitter for both passes
+        for ss in pipe.sets:
+            ss.key = None
+        for buf in (pipe.enc, pipe.rad_in, pipe.sigma, pipe.rgb_s, pipe.geo_act, pipe.rad_act):
+            buf.zero_()
+        pipe.forward(o_d, d_d, dev(bkg))
+        torch.cuda.synchronize()
+        n = int(pipe.meta[0])
+        tiles = (n + 127) // 128
+        out[fused] = dict(enc=pipe.enc[:n].clone(), rad_in=pipe.rad_in[:n].clone(), sigma=pipe.sigma[:n].clone(),
+                          rgb_s=pipe.rgb_s[:n].clone(), rgb=pipe.rgb[:900].clone(),
+                          # saved activations: rows of the last tile beyond n differ by design (the fused kernel encodes padding rows)
+                          geo_act=pipe.geo_act[:(tiles - 1) * 128 * 64 * 2].clone(),
+                          rad_act=pipe.rad_act[:(tiles - 1) * 2 * 128 * 64 * 2].clone())
+    assert n > 128 * 20
+    for k in out[True]:
+        assert torch.equal(out[True][k], out[False][k]), k
+
+
+def test_fused_field_forward_inference_writes_no_training_tensors():
+    pipe, _, o, d, tgt, bkg = setup(300, 12)
+    pipe.enc.fill_(7.0); pipe.rad_in.fill_(7.0)
+    pipe.render(dev(o), dev(d), dev(bkg)[:1])
+    torch.cuda.synchronize()
+    assert float(pipe.enc.min()) == 7.0 and float(pipe.rad_in.min()) == 7.0
