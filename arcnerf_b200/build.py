@@ -14,7 +14,7 @@ OBJ_DIR = os.path.join(HERE, 'csrc', '_obj')
 LIB_PATH = os.path.join(HERE, 'libarcb200.so')
 
 ARCH = ['-gencode', 'arch=compute_100a,code=sm_100a']
-COMMON = ['-O3', '-std=c++17', '-lineinfo', '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr']
+COMMON = ['-O3', '-std=c++17', '-lineinfo', '-Xcompiler', '-fPIC', '--expt-relaxed-constexpr'] + os.environ.get('ARCB200_NVCC_EXTRA', '').split()
 
 # Per-file extra flags.  The ray/occupancy kernels must not contract multiplies and adds (bit-exact
 # parity of sample positions with the oracle); the rest follow the default (fmad on).

@@ -1029,18 +1029,22 @@ int arcb200_field_fwd(const float *unit, const void *table_half, int n_levels, i
     const size_t smem = field_fwd_smem(geo, rad);
     int rc = set_smem(field_fwd_kernel, smem);
     if (rc != ARCB200_OK) return rc;
-    static thread_local int per_sm = 0;
-    if (per_sm == 0) {
-        int occ = 0;
-        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, field_fwd_kernel, kFieldThreads, smem) != cudaSuccess || occ < 1) { cudaGetLastError(); occ = 1; }
-        per_sm = occ > 8 ? 8 : occ;                    // 64 TMEM columns per CTA: eight CTAs fit an SM's tensor memory
-        if (const char *e = getenv("ARCB200_FIELD_CTAS_PER_SM")) { const int v = atoi(e); if (v > 0 && v < per_sm) per_sm = v; }
-    }
-    const int64_t tiles = (n + kRows - 1) / kRows, cap = (int64_t)arc_sm_count() * per_sm;
+    // one persistent CTA per SM (512 threads: 8 layer warps + 8 gather warps)
+    const int64_t tiles = (n + kRows - 1) / kRows, cap = (int64_t)arc_sm_count();
     arc_launch(field_fwd_kernel, (unsigned)(tiles < cap ? tiles : cap), kFieldThreads, smem, (cudaStream_t)stream, n, n_dev, geom, geo,
                rad, a);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
+
+#ifdef ARCB200_PROF
+// debug builds: read and clear the phase clocks of the fused forward (16 uint64)
+int arcb200_debug_field_prof(unsigned long long *out16) {
+    ARC_CUDA(cudaMemcpyFromSymbol(out16, g_field_prof, sizeof(unsigned long long) * 16));
+    unsigned long long z[16] = {0};
+    ARC_CUDA(cudaMemcpyToSymbol(g_field_prof, z, sizeof(z)));
+    return ARCB200_OK;
+}
+#endif
 
 }  // extern "C"
