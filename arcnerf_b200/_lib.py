@@ -88,6 +88,10 @@ _SIGS = {
     'arcb200_adam_step_peer16': [P, P, P, I, I, L, L, P, P, P, F, I, F, F, F, F, F, F, P, P],
     'arcb200_adam_step_peer': [P, P, I, L, L, P, P, P, I, F, F, F, F, F, F, P, P],
     'arcb200_probe_gather': [P, L, I, I, I, C.c_uint32, P, P],
+    'arcb200_nerf_mlp_sizes': [I, I, I, I, I, I, I, P],
+    'arcb200_nerf_mlp_pack': [I, I, I, I, I, I, I, P, P, P, P, P],
+    'arcb200_nerf_mlp_fwd': [I, I, I, I, I, I, I, P, P, P, P, P, L, P, P, L, P],
+    'arcb200_nerf_mlp_bwd': [I, I, I, I, I, I, I, P, P, P, P, P, P, P, P, L, P, L, P],
     'arcb200_field_fwd': [P, P, I, I, P, P, P, P, P, P, P, I, P, P, P, P, P, P, P, L, P, P],
 }
 _RESTYPE = {

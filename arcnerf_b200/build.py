@@ -34,6 +34,7 @@ SOURCES = {
     'volume_refresh.cu': [],
     'freq.cu': ['-fmad=false'],
     'probe.cu': [],
+    'dense_chain.cu': [],
 }
 
 

@@ -449,6 +449,29 @@ int arcb200_field_fwd(const float *unit, const void *table_half, int n_levels, i
                       void *rad_act, float *sigma, float *rgb, float *zero_scalar, int64_t n, const int32_t *n_dev,
                       void *stream);
 
+/* ---- vanilla-NeRF network pair as one dense-layer chain (csrc/dense_chain.cu) ----------------------------------------------
+ * GeoNet (D hidden layers of width W = 256 with ReLU, input embedding re-concatenated after layer `skip` (-1: none), last
+ * layer 1 + W outputs) + RadianceNet (mode 'vf': [view embedding | feature] -> W_rad -> 3, sigmoid) with the frequency
+ * embeddings (d_x inputs x n_freq_x bands, 3 x n_freq_v, log sampling, input included) computed inside the kernels.
+ * Replaces arcnerf/models/base_modules/geo_rad_model/linear_network_module.py:17-197,234-335 (torch.nn.Linear stacks) and
+ * encoding/freq_encoder.py:10-88 as used by NeRF (nerf_model.py:52-91) and the NeRF++ background (nerfpp_bkg_model.py:51-114).
+ * Flat fp32 parameter vector: geometry layers 0..D, each weight (out x in, row-major, the layer's full input width) followed
+ * by its bias, then the two radiance layers likewise - the reference's `layers.{i}.weight / bias` tensors in order.
+ * arcb200_nerf_mlp_sizes: out[0] parameters, out[1] / out[2] bytes of the forward / backward operand blobs, out[3] floats of
+ * the vector buffer, out[4] / out[5] fp16 columns per point of the forward / backward save buffers.
+ * arcb200_nerf_mlp_pack: parameters -> blobs + vectors (after every update).  _fwd: x (n,d_x), dirs (n,3) -> sigma (n) raw,
+ * rgb (n,3); save = NULL for inference or (out[4] x n_cap) fp16.  _bwd: d_sigma (n), d_rgb (n,3) -> d_params ACCUMULATED;
+ * bwd_save (out[5] x n_cap) fp16 and dsig16 (n_cap x 16) fp16 are scratch.  n_cap % 8 == 0. */
+int arcb200_nerf_mlp_sizes(int d_x, int n_freq_x, int n_freq_v, int W, int D, int skip, int W_rad, int64_t *out);
+int arcb200_nerf_mlp_pack(int d_x, int n_freq_x, int n_freq_v, int W, int D, int skip, int W_rad, const float *params,
+                          void *blob_fwd, void *blob_bwd, float *vec, void *stream);
+int arcb200_nerf_mlp_fwd(int d_x, int n_freq_x, int n_freq_v, int W, int D, int skip, int W_rad, const float *x,
+                         const float *dirs, const void *blob_fwd, const float *vec, void *save, int64_t n_cap, float *sigma,
+                         float *rgb, int64_t n, void *stream);
+int arcb200_nerf_mlp_bwd(int d_x, int n_freq_x, int n_freq_v, int W, int D, int skip, int W_rad, const void *blob_bwd,
+                         const float *vec, const void *fwd_save, const float *rgb, const float *d_sigma, const float *d_rgb,
+                         void *bwd_save, void *dsig16, int64_t n_cap, float *d_params, int64_t n, void *stream);
+
 /* ---- measurement aid (csrc/probe.cu) ---------------------------------------------------------------------------------
  * Random-gather bandwidth of a device table: n_threads (rounded up to 256) threads issue trips * 8 independent loads of
  * req_bytes (4, 8 or 16) at uniformly random entries of `table` (n_bytes) and write one checksum each to sink
