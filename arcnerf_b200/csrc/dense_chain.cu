@@ -76,6 +76,7 @@ struct ChainArgs {
     const float *d_sigma;      // backward in (n)
     const float *d_rgb;        // backward in (n,3)
     __half *dsig16;            // backward out (n,16): column 0 = d_sigma (operand of the sigma-row weight gradient)
+    float loss_scale;          // backward: gradients travel through the fp16 tiles multiplied by this (undone by the weight-gradient flush)
     int64_t n, n_cap;
 };
 
@@ -228,9 +229,9 @@ dense_chain_kernel(const __grid_constant__ Program prog, const ChainArgs a) {
                     #pragma unroll
                     for (int k = 0; k < 3; ++k) {
                         const float y = __ldg(a.rgb + grow * 3 + k);
-                        v[k] = __ldg(a.d_rgb + grow * 3 + k) * y * (1.0f - y);
+                        v[k] = __ldg(a.d_rgb + grow * 3 + k) * y * (1.0f - y) * a.loss_scale;
                     }
-                    dsig = __ldg(a.d_sigma + grow);
+                    dsig = __ldg(a.d_sigma + grow) * a.loss_scale;
                 }
                 const uint4 w = pack8(v), z = make_uint4(0u, 0u, 0u, 0u);
                 *tile_word(tile, r, 0) = w;
@@ -378,6 +379,7 @@ struct WgArgs {
     int n_out_valid, k_valid;
     float *dW; int64_t ldw;                      // fp32 (N x K) block inside a larger matrix
     float *db;                                   // fp32 (N) or null
+    float out_scale;                             // multiplies everything that is flushed (1 / loss scale)
     int64_t n;
 };
 
@@ -505,7 +507,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) dense_wgrad_kernel(const WgArgs
                     float *dst = a.dW + (size_t)row * a.ldw + cb * 16;
                     #pragma unroll
                     for (int k = 0; k < 16; ++k)
-                        if (cb * 16 + k < a.k_valid) atomicAdd(dst + k, __uint_as_float(q[k]));
+                        if (cb * 16 + k < a.k_valid) atomicAdd(dst + k, __uint_as_float(q[k]) * a.out_scale);
                 }
             }
         }
@@ -517,7 +519,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) dense_wgrad_kernel(const WgArgs
                 for (int k = 0; k < 8; ++k) atomicAdd(&db_s[cg * 8 + k], colsum[k]);
             }
             __syncthreads();
-            if (tid < a.N && tid < a.n_out_valid) atomicAdd(a.db + tid, db_s[tid]);
+            if (tid < a.N && tid < a.n_out_valid) atomicAdd(a.db + tid, db_s[tid] * a.out_scale);
         }
     }
     tc05::fence_before_sync();
@@ -742,10 +744,10 @@ static int build_all(Built &b, int d_x, int n_freq_x, int n_freq_v, int W, int D
 }
 
 static int launch_wgrad(const __half *dz, int64_t ldz, int N, int n_out_valid, const __half *act, int64_t lda, int K, int k_valid,
-                        float *dW, int64_t ldw, float *db, int64_t n, cudaStream_t st) {
+                        float *dW, int64_t ldw, float *db, float out_scale, int64_t n, cudaStream_t st) {
     WgArgs w;
     w.dz = dz; w.ldz = ldz; w.N = N; w.act = act; w.lda = lda; w.K = K; w.n_out_valid = n_out_valid; w.k_valid = k_valid;
-    w.dW = dW; w.ldw = ldw; w.db = db; w.n = n;
+    w.dW = dW; w.ldw = ldw; w.db = db; w.out_scale = out_scale; w.n = n;
     const int Mp = (N + 127) / 128 * 128;
     const size_t smem = 128 + 1024 + (size_t)kWgStages * kWgRows * (Mp + K) * 2;
     int rc = set_max_smem(dense_wgrad_kernel, smem);
@@ -819,12 +821,14 @@ int arcb200_nerf_mlp_fwd(NERF_ARCH_ARGS, const float *x, const float *dirs, cons
 
 // Backward: d_sigma (n), d_rgb (n,3) fp32 -> d_params (flat fp32, ACCUMULATED; the caller zeroes it).  fwd_save / rgb: what
 // arcb200_nerf_mlp_fwd left behind for the same inputs; bwd_save: fp16 scratch of (backward save columns) x n_cap; dsig16:
-// fp16 scratch (n_cap, 16).  No gradient w.r.t. the inputs is produced (NeRF does not need it).
+// fp16 scratch (n_cap, 16).  loss_scale: the gradients pass through fp16 tiles multiplied by it and are divided by it on the way
+// out (128 is what the reference's tcnn path uses; values below 6e-5 would otherwise lose bits).  No gradient w.r.t. the inputs
+// is produced (NeRF does not need it).
 // Replaces autograd through the torch Linear stacks of the reference.
 int arcb200_nerf_mlp_bwd(NERF_ARCH_ARGS, const void *blob_bwd, const float *vec, const void *fwd_save, const float *rgb,
-                         const float *d_sigma, const float *d_rgb, void *bwd_save, void *dsig16, int64_t n_cap, float *d_params,
-                         int64_t n, void *stream) {
-    ARC_REQUIRE(n >= 0 && n_cap >= n, "nerf_mlp_bwd: bad sizes");
+                         const float *d_sigma, const float *d_rgb, float loss_scale, void *bwd_save, void *dsig16, int64_t n_cap,
+                         float *d_params, int64_t n, void *stream) {
+    ARC_REQUIRE(n >= 0 && n_cap >= n && loss_scale > 0.f, "nerf_mlp_bwd: bad sizes or loss scale");
     if (n == 0) return ARCB200_OK;
     Built b;
     ARC_REQUIRE(build_all(b, NERF_ARCH_PASS) == 0, "nerf_mlp_bwd: unsupported architecture");
@@ -835,7 +839,7 @@ int arcb200_nerf_mlp_bwd(NERF_ARCH_ARGS, const void *blob_bwd, const float *vec,
     ChainArgs a;
     memset(&a, 0, sizeof(a));
     a.blob = (const uint8_t *)blob_bwd; a.vec = vec; a.save = (__half *)bwd_save; a.fwd_save = (const __half *)fwd_save;
-    a.rgb = const_cast<float *>(rgb); a.d_sigma = d_sigma; a.d_rgb = d_rgb; a.dsig16 = (__half *)dsig16; a.n = n; a.n_cap = n_cap;
+    a.rgb = const_cast<float *>(rgb); a.d_sigma = d_sigma; a.d_rgb = d_rgb; a.dsig16 = (__half *)dsig16; a.loss_scale = loss_scale; a.n = n; a.n_cap = n_cap;
     const size_t smem = chain_smem(b.B);
     int rc = set_max_smem(dense_chain_kernel<true>, smem);
     if (rc != ARCB200_OK) return rc;
@@ -855,7 +859,7 @@ int arcb200_nerf_mlp_bwd(NERF_ARCH_ARGS, const void *blob_bwd, const float *vec,
     auto dZ = [&](int i) { return bcol(b.B.layer[2 + (D - 1 - i)].save_col); };
     float *g = d_params;
     const int l_r0 = D + 1, l_r1 = D + 2;
-#define WG(...) do { rc = launch_wgrad(__VA_ARGS__, n, st); if (rc != ARCB200_OK) return rc; } while (0)
+#define WG(...) do { rc = launch_wgrad(__VA_ARGS__, 1.0f / loss_scale, n, st); if (rc != ARCB200_OK) return rc; } while (0)
     // colour layer (3 x W_rad)
     WG(dz_rgb, 16, 16, 3, H(D + 1), A.W_rad, A.W_rad, A.W_rad, g + A.w_off[l_r1], A.W_rad, g + A.b_off[l_r1]);
     // radiance hidden layer (W_rad x (embed_v + W)): view columns, then feature columns

@@ -23,13 +23,15 @@ class _ChainFn(torch.autograd.Function):
         n = x.shape[0]
         sigma = torch.empty((n,), dtype=torch.float32, device=x.device)
         rgb = torch.empty((n, 3), dtype=torch.float32, device=x.device)
-        need_grad = torch.is_grad_enabled() and flat.requires_grad
+        need_grad = ctx.needs_input_grad[3]          # (grad mode is off inside Function.forward; this is the caller's view)
         nets._pack_if_changed()
         n_cap = (n + 7) // 8 * 8
         save = torch.empty(nets.fwd_cols * n_cap, dtype=torch.float16, device=x.device) if need_grad else None
         _lib.call('arcb200_nerf_mlp_fwd', *nets.arch, x.data_ptr(), dirs.data_ptr(), nets.blob_fwd.data_ptr(), nets.vec.data_ptr(),
                   _lib.ptr(save), n_cap, sigma.data_ptr(), rgb.data_ptr(), n, _lib.current_stream())
         ctx.nets, ctx.n, ctx.n_cap = nets, n, n_cap
+        if nets.keep_save:
+            nets.last_save = (save, n_cap)
         ctx.save_for_backward(save, rgb)
         return sigma, rgb
 
@@ -44,7 +46,7 @@ class _ChainFn(torch.autograd.Function):
         dsig16 = torch.empty((n_cap, 16), dtype=torch.float16, device=dev)
         d_params = torch.zeros(nets.n_params, dtype=torch.float32, device=dev)
         _lib.call('arcb200_nerf_mlp_bwd', *nets.arch, nets.blob_bwd.data_ptr(), nets.vec.data_ptr(), save.data_ptr(), rgb.data_ptr(),
-                  g_sigma.data_ptr(), g_rgb.data_ptr(), bwd_save.data_ptr(), dsig16.data_ptr(), n_cap, d_params.data_ptr(), n,
+                  g_sigma.data_ptr(), g_rgb.data_ptr(), float(nets.loss_scale), bwd_save.data_ptr(), dsig16.data_ptr(), n_cap, d_params.data_ptr(), n,
                   _lib.current_stream())
         return None, None, None, d_params
 
@@ -78,6 +80,8 @@ class FusedNeRFNets(nn.Module):
         self.blob_bwd = torch.empty(bwd_bytes, dtype=torch.uint8, device=dev)
         self.vec = torch.zeros(n_vec, dtype=torch.float32, device=dev)
         self._packed_version = None
+        self.keep_save, self.last_save = False, None     # tests: keep the forward's saved activations for inspection
+        self.loss_scale = 128.0        # gradients cross the fp16 tiles multiplied by this (tinycudann/modules.py:141 uses the same)
 
     # ---- the reference's parameter tensors as views of the flat vector
     def layer_views(self):
@@ -111,6 +115,18 @@ class FusedNeRFNets(nn.Module):
         for i in range(2):
             rad['layers.%d.weight' % i], rad['layers.%d.bias' % i] = views[n_geo + i][0].clone(), views[n_geo + i][1].clone()
         return geo, rad
+
+    def saved_columns(self):
+        """name -> (first column, width) of the forward save buffer (region c starts at c * n_cap, row stride = width)"""
+        d_x, nfx, nfv, W, D, skip, W_rad = self.arch
+        xe_pad = (self.embed_x + 31) // 32 * 32
+        cols, c = {'xe': (0, xe_pad), 've': (xe_pad, 32)}, xe_pad + 32
+        for i in range(D):
+            cols['h%d' % i] = (c, W); c += W
+        cols['feat'] = (c, W); c += W
+        cols['hr'] = (c, W_rad); c += W_rad
+        assert c == self.fwd_cols
+        return cols
 
     def _pack_if_changed(self):
         v = self.flat._version

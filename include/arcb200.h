@@ -461,7 +461,8 @@ int arcb200_field_fwd(const float *unit, const void *table_half, int n_levels, i
  * the vector buffer, out[4] / out[5] fp16 columns per point of the forward / backward save buffers.
  * arcb200_nerf_mlp_pack: parameters -> blobs + vectors (after every update).  _fwd: x (n,d_x), dirs (n,3) -> sigma (n) raw,
  * rgb (n,3); save = NULL for inference or (out[4] x n_cap) fp16.  _bwd: d_sigma (n), d_rgb (n,3) -> d_params ACCUMULATED;
- * bwd_save (out[5] x n_cap) fp16 and dsig16 (n_cap x 16) fp16 are scratch.  n_cap % 8 == 0. */
+ * bwd_save (out[5] x n_cap) fp16 and dsig16 (n_cap x 16) fp16 are scratch; loss_scale multiplies the gradients inside the fp16
+ * tiles and is divided out again (128 in the reference's tcnn path).  n_cap % 8 == 0. */
 int arcb200_nerf_mlp_sizes(int d_x, int n_freq_x, int n_freq_v, int W, int D, int skip, int W_rad, int64_t *out);
 int arcb200_nerf_mlp_pack(int d_x, int n_freq_x, int n_freq_v, int W, int D, int skip, int W_rad, const float *params,
                           void *blob_fwd, void *blob_bwd, float *vec, void *stream);
@@ -470,7 +471,7 @@ int arcb200_nerf_mlp_fwd(int d_x, int n_freq_x, int n_freq_v, int W, int D, int 
                          float *rgb, int64_t n, void *stream);
 int arcb200_nerf_mlp_bwd(int d_x, int n_freq_x, int n_freq_v, int W, int D, int skip, int W_rad, const void *blob_bwd,
                          const float *vec, const void *fwd_save, const float *rgb, const float *d_sigma, const float *d_rgb,
-                         void *bwd_save, void *dsig16, int64_t n_cap, float *d_params, int64_t n, void *stream);
+                         float loss_scale, void *bwd_save, void *dsig16, int64_t n_cap, float *d_params, int64_t n, void *stream);
 
 /* ---- measurement aid (csrc/probe.cu) ---------------------------------------------------------------------------------
  * Random-gather bandwidth of a device table: n_threads (rounded up to 256) threads issue trips * 8 independent loads of
