@@ -25,6 +25,7 @@
 #include "tc05.cuh"
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
 
 namespace {
 
@@ -33,9 +34,9 @@ constexpr int kMaxLayers = 12;
 constexpr int kMaxChunks = 12;
 constexpr int kChunkK = 32;                 // input columns per weight chunk
 constexpr int kHCols = 256;                 // hidden region of the operand tile
-constexpr int kEpiThreads = 256;            // warps 0-3: tile 0 of the pair, warps 4-7: tile 1
-constexpr int kProducerWarp = 8, kMmaWarp = 9;
-constexpr int kThreads = 320;
+constexpr int kEpiPerTile = 256;            // warps 0-7: tile 0 of the pair, warps 8-15: tile 1; two warps per TMEM row quadrant
+constexpr int kProducerWarp = 16, kMmaWarp = 17;
+constexpr int kThreads = 576;
 constexpr int kMaxSlots = 6;
 constexpr uint32_t kSlotBytes = 256 * kChunkK * 2;
 
@@ -76,6 +77,7 @@ struct ChainArgs {
     const float *d_sigma;      // backward in (n)
     const float *d_rgb;        // backward in (n,3)
     __half *dsig16;            // backward out (n,16): column 0 = d_sigma (operand of the sigma-row weight gradient)
+    int dbg_skip;              // profiling builds only: bit 0 no bias add, bit 1 no operand-tile stores, bit 2 no TMEM loads
     float loss_scale;          // backward: gradients travel through the fp16 tiles multiplied by this (undone by the weight-gradient flush)
     int64_t n, n_cap;
 };
@@ -89,6 +91,11 @@ struct Ctl {
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *mbar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" :: "r"(tc05::smem_u32(mbar)) : "memory");
+}
+// Wait with back-off: the roles of this kernel wait for each other most of the time, and 100+ threads polling an mbarrier
+// keep the shared-memory pipeline busy with their probes while the other warps need it for their loads and stores.
+__device__ __forceinline__ void mbar_wait_sleep(uint64_t *mbar, uint32_t parity, unsigned ns) {
+    while (!tc05::mbar_try_wait(mbar, parity)) __nanosleep(ns);
 }
 __device__ __forceinline__ uint4 *tile_word(uint8_t *tile, int r, int cg) {
     return reinterpret_cast<uint4 *>(tile + (size_t)cg * (kRows * 16) + (size_t)r * 16);
@@ -108,14 +115,53 @@ __device__ __forceinline__ void unpack8(const uint4 &w, float *v) {
     }
 }
 
-// column c of the frequency embedding of a d-vector: [x | sin(x 2^0) | cos(x 2^0) | sin(x 2^1) | ...] (freq_encoder.py:78-84)
-__device__ __forceinline__ float embed_col(const float *x, int d, int c) {
-    const int part = c / d, ch = c - part * d;
-    if (part == 0) return x[ch];
-    const int k = (part - 1) >> 1;
-    const float arg = x[ch] * (float)(1u << k);
-    return ((part - 1) & 1) ? cosf(arg) : sinf(arg);
+// Frequency embedding of a d-vector, [x | sin(x 2^0) | cos(x 2^0) | sin(x 2^1) | ...] (freq_encoder.py:78-84), written as fp16
+// elements into row r of the operand tile starting at column group cg0; columns [embed, pad_cols) are zeroed.  One sincosf per
+// (band, channel).
+__device__ __forceinline__ void write_embedding(uint8_t *tile, int r, int cg0, const float *x, int d, int n_freq, int pad_cols, bool live) {
+    auto put = [&](int c, float v) {
+        *reinterpret_cast<__half *>(tile + (size_t)(cg0 + (c >> 3)) * (kRows * 16) + (size_t)r * 16 + (c & 7) * 2) = __float2half_rn(v);
+    };
+    const int embed = d * (2 * n_freq + 1);
+    for (int ch = 0; ch < d; ++ch) {
+        const float xv = live ? x[ch] : 0.f;
+        put(ch, xv);
+        float f = 1.0f;
+        for (int k = 0; k < n_freq; ++k, f *= 2.0f) {
+            float sn, cs;
+            sincosf(xv * f, &sn, &cs);
+            put((1 + 2 * k) * d + ch, live ? sn : 0.f);
+            put((2 + 2 * k) * d + ch, live ? cs : 0.f);
+        }
+    }
+    for (int c = embed; c < pad_cols; ++c) put(c, 0.f);
 }
+
+// Saved tensors (activations of the forward, gradients of the backward) keep the operand-tile layout in global memory: a
+// tensor of width N is a sequence of 128-row tiles of N * 256 bytes, each the image of the shared-memory tile (16-byte word of
+// row r and 8-column group cg at (cg * 128 + r) * 16).  A tile leaves shared memory as ONE bulk copy issued by a single
+// thread, the backward reads its masks as consecutive 16-byte words across a warp, and a 64-row half of a tile is exactly the
+// MN-major operand of the weight-gradient kernel.
+__device__ __forceinline__ size_t tiled_word(int64_t row, int N, int cg) {          // offset in halfs
+    return (size_t)(row >> 7) * (size_t)N * kRows + ((size_t)cg * kRows + (size_t)(row & 127)) * 8;
+}
+__device__ __forceinline__ void bulk_s2g(void *gmem_dst, const void *smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" :: "l"(gmem_dst), "r"(tc05::smem_u32(smem_src)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+#ifdef ARCB200_PROF
+// debug builds: cycles spent by the MMA thread waiting for weights [0] / for operand tiles [1] / in total [2], by the epilogue
+// thread 0 waiting for accumulators [3] / working [4], producer waiting for a free slot [5]; [6] pairs
+__device__ unsigned long long g_chain_prof[8];
+__device__ unsigned long long g_chain_layer_prof[16];   // epilogue work cycles of thread 0 per layer
+__device__ unsigned long long g_chain_load_prof[2];     // load phase of thread 0
+#define CHAIN_PROF(slot, expr) do { const long long t0__ = clock64(); expr; atomicAdd(&g_chain_prof[slot], (unsigned long long)(clock64() - t0__)); } while (0)
+#else
+#define CHAIN_PROF(slot, expr) do { expr; } while (0)
+#endif
 
 template <bool BWD>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -125,12 +171,13 @@ dense_chain_kernel(const __grid_constant__ Program prog, const ChainArgs a) {
     const uint32_t tile_bytes = (uint32_t)kRows * (kHCols + prog.aux_cols) * 2;
     uint8_t *tiles = smem + 256;
     uint8_t *ring = tiles + 2 * tile_bytes;
+    float *vec_s = reinterpret_cast<float *>(ring + (size_t)prog.n_slots * kSlotBytes);     // 2 x 256 floats: the layer's bias / row vector per tile
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int S = prog.n_slots;
 
     if (tid == 0) {
         for (int s = 0; s < S; ++s) { tc05::mbar_init(&ctl->w_full[s], 1); tc05::mbar_init(&ctl->w_empty[s], 1); }
-        for (int t = 0; t < 2; ++t) { tc05::mbar_init(&ctl->acc_full[t], 1); tc05::mbar_init(&ctl->h_ready[t], 128); }
+        for (int t = 0; t < 2; ++t) { tc05::mbar_init(&ctl->acc_full[t], 1); tc05::mbar_init(&ctl->h_ready[t], kEpiPerTile); }
         tc05::fence_mbar_init();
     }
     if (warp == kMmaWarp) tc05::tmem_alloc<512>(&ctl->tmem_base);
@@ -153,7 +200,7 @@ dense_chain_kernel(const __grid_constant__ Program prog, const ChainArgs a) {
                     const uint32_t bytes = (uint32_t)ly.N * kChunkK * 2;
                     for (int c = 0; c < ly.n_chunks; ++c, ++i) {
                         const int s = (int)(i % (uint32_t)S);
-                        tc05::mbar_wait(&ctl->w_empty[s], ((i / (uint32_t)S) & 1u) ^ 1u);
+                        CHAIN_PROF(5, mbar_wait_sleep(&ctl->w_empty[s], ((i / (uint32_t)S) & 1u) ^ 1u, 200));
                         tc05::mbar_expect_tx(&ctl->w_full[s], bytes);
                         tc05::bulk_g2s(ring + (size_t)s * kSlotBytes, a.blob + ly.w_off + (size_t)c * bytes, bytes, &ctl->w_full[s]);
                     }
@@ -164,6 +211,9 @@ dense_chain_kernel(const __grid_constant__ Program prog, const ChainArgs a) {
         // ================================================================ MMA issue: both tiles use every chunk
         if (lane == 0) {
             uint32_t i = 0, hph[2] = {0, 0};
+#ifdef ARCB200_PROF
+            const long long mma_t0 = clock64();
+#endif
             const uint32_t t_addr[2] = {tc05::smem_u32(tiles), tc05::smem_u32(tiles) + tile_bytes};
             const uint32_t ring_a = tc05::smem_u32(ring);
             for (int64_t pair = blockIdx.x; pair < n_pairs; pair += gridDim.x) {
@@ -172,13 +222,38 @@ dense_chain_kernel(const __grid_constant__ Program prog, const ChainArgs a) {
                     const uint32_t N = ly.N, idesc = tc05::make_idesc(128, N, 0, 0), w_lbo = N * 16;
                     for (int c = 0; c < ly.n_chunks; ++c, ++i) {
                         const int s = (int)(i % (uint32_t)S);
-                        tc05::mbar_wait(&ctl->w_full[s], (i / (uint32_t)S) & 1u);
+                        CHAIN_PROF(0, mbar_wait_sleep(&ctl->w_full[s], (i / (uint32_t)S) & 1u, 40));
                         const uint32_t w_a = ring_a + (uint32_t)s * kSlotBytes;
                         #pragma unroll
                         for (int t = 0; t < 2; ++t) {
                             if (c == 0) {                     // the tile's operand for this layer has been written
-                                tc05::mbar_wait(&ctl->h_ready[t], hph[t]);
+                                CHAIN_PROF(1, mbar_wait_sleep(&ctl->h_ready[t], hph[t], 40));
                                 hph[t] ^= 1u;
+                                if (a.save) {
+                                    // what the epilogue warps have just finished goes to global memory as whole tiles: the output of the
+                                    // previous layer (columns 0..N-1), the position embedding after the load phase, the view embedding
+                                    // after the layer that wrote it
+                                    const int64_t tile_idx = pair * 2 + t;
+                                    uint8_t *tile_s = tiles + (size_t)t * tile_bytes;
+                                    if (tile_idx * kRows < n) {
+                                        if (l == 0) {
+                                            if (!BWD) {
+                                                const int xe_pad = ((prog.embed_x + 31) / 32) * 32;
+                                                bulk_s2g(a.save + (size_t)prog.xe_col * a.n_cap + (size_t)tile_idx * xe_pad * kRows,
+                                                         tile_s + (size_t)(kHCols / 8) * (kRows * 16), (uint32_t)xe_pad * kRows * 2);
+                                            }
+                                        } else {
+                                            const Layer &pl = prog.layer[l - 1];
+                                            if (pl.save_col >= 0)
+                                                bulk_s2g(a.save + (size_t)pl.save_col * a.n_cap + (size_t)tile_idx * pl.N * kRows, tile_s,
+                                                         (uint32_t)pl.N * kRows * 2);
+                                            if (!BWD && (pl.flags & F_VIEW))
+                                                bulk_s2g(a.save + (size_t)prog.ve_col * a.n_cap + (size_t)tile_idx * 32 * kRows,
+                                                         tile_s + (size_t)(kHCols / 8) * (kRows * 16), 32u * kRows * 2);
+                                        }
+                                    }
+                                    bulk_commit();
+                                }
                             }
                             tc05::fence_after_sync();
                             #pragma unroll
@@ -187,16 +262,43 @@ dense_chain_kernel(const __grid_constant__ Program prog, const ChainArgs a) {
                                 const uint64_t db = tc05::make_desc(w_a + (uint32_t)k * 2 * w_lbo, w_lbo, 128);
                                 tc05::mma_f16_ss(tmem + (uint32_t)t * 256, da, db, idesc, (c > 0 || k > 0) ? 1u : 0u);
                             }
-                            if (c == ly.n_chunks - 1) tc05::mma_commit(&ctl->acc_full[t]);
+                            if (c == ly.n_chunks - 1) {
+                                // the epilogue of this layer overwrites the tile: the stores issued above must have read it
+                                if (a.save) bulk_wait_read_all();
+                                tc05::mma_commit(&ctl->acc_full[t]);
+                            }
                         }
                         tc05::mma_commit(&ctl->w_empty[s]);      // the chunk may be overwritten once these MMAs are done
                     }
                 }
+                if (BWD && a.save) {
+                    const Layer &pl = prog.layer[L - 1];
+                    for (int t = 0; t < 2; ++t) {
+                        mbar_wait_sleep(&ctl->h_ready[t], hph[t], 40);
+                        hph[t] ^= 1u;
+                        const int64_t tile_idx = pair * 2 + t;
+                        if (tile_idx * kRows < n && pl.save_col >= 0)
+                            bulk_s2g(a.save + (size_t)pl.save_col * a.n_cap + (size_t)tile_idx * pl.N * kRows, tiles + (size_t)t * tile_bytes,
+                                     (uint32_t)pl.N * kRows * 2);
+                    }
+                    bulk_commit();
+                    bulk_wait_read_all();
+                    mbar_arrive(&ctl->acc_full[0]);
+                    mbar_arrive(&ctl->acc_full[1]);
+                }
+#ifdef ARCB200_PROF
+                atomicAdd(&g_chain_prof[6], 1ull);
+#endif
             }
+#ifdef ARCB200_PROF
+            atomicAdd(&g_chain_prof[2], (unsigned long long)(clock64() - mma_t0));
+#endif
+            if (a.save) bulk_wait_all();
         }
     } else {
         // ================================================================ epilogue warps: thread = one row of one tile
-        const int t = warp >> 2;
+        // row r of tile t; the two warps of a row quadrant (half 0 / 1) split the columns of every layer
+        const int t = warp >> 3, half = (warp >> 2) & 1;
         const int r = (warp & 3) * 32 + lane;
         uint8_t *tile = tiles + (size_t)t * tile_bytes;
         const uint32_t acc = tmem + (uint32_t)t * 256 + ((uint32_t)((warp & 3) * 32) << 16);
@@ -206,22 +308,19 @@ dense_chain_kernel(const __grid_constant__ Program prog, const ChainArgs a) {
             const int64_t grow = (pair * 2 + t) * kRows + r;
             const bool live = grow < n;
             float dsig = 0.f;
-            // ---- the tile's first operand
-            if (!BWD) {
+#ifdef ARCB200_PROF
+            const long long ld_t0 = clock64();
+#endif
+            // ---- the tile's first operand (written by the half-0 thread of the row)
+            if (half != 0) {
+                if (BWD && live) dsig = __ldg(a.d_sigma + grow) * a.loss_scale;
+            } else if (!BWD) {
                 float x[4] = {0.f, 0.f, 0.f, 0.f};
-                if (live) for (int k = 0; k < prog.d_x; ++k) x[k] = __ldg(a.x + grow * prog.d_x + k);
-                for (int cg = 0; cg < prog.aux_cols / 8; ++cg) {
-                    float v[8];
+                if (live) {
                     #pragma unroll
-                    for (int k = 0; k < 8; ++k) {
-                        const int c = cg * 8 + k;
-                        v[k] = (live && c < prog.embed_x) ? embed_col(x, prog.d_x, c) : 0.f;
-                    }
-                    const uint4 w = pack8(v);
-                    *tile_word(tile, r, aux_cg0 + cg) = w;
-                    if (a.save && live && cg * 8 < ((prog.embed_x + 31) / 32) * 32)
-                        *reinterpret_cast<uint4 *>(a.save + (size_t)prog.xe_col * a.n_cap + grow * (((prog.embed_x + 31) / 32) * 32) + cg * 8) = w;
+                    for (int k = 0; k < 4; ++k) if (k < prog.d_x) x[k] = __ldg(a.x + grow * prog.d_x + k);
                 }
+                write_embedding(tile, r, aux_cg0, x, prog.d_x, prog.n_freq_x, prog.aux_cols, live);
             } else {
                 // gradient at the colour output through the sigmoid, padded to one 32-column chunk
                 float v[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
@@ -237,100 +336,163 @@ dense_chain_kernel(const __grid_constant__ Program prog, const ChainArgs a) {
                 *tile_word(tile, r, 0) = w;
                 *tile_word(tile, r, 1) = z; *tile_word(tile, r, 2) = z; *tile_word(tile, r, 3) = z;
                 if (live) {
-                    uint4 *d0 = reinterpret_cast<uint4 *>(a.save + grow * 16);          // region 0 of the backward save: (n,16)
-                    d0[0] = w; d0[1] = z;
+                    // region 0 of the backward save (width 16) and the d_sigma operand (width 16), tiled like every saved tensor
+                    *reinterpret_cast<uint4 *>(a.save + tiled_word(grow, 16, 0)) = w;
+                    *reinterpret_cast<uint4 *>(a.save + tiled_word(grow, 16, 1)) = z;
                     float s8[8] = {dsig, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                    uint4 *d1 = reinterpret_cast<uint4 *>(a.dsig16 + grow * 16);
-                    d1[0] = pack8(s8); d1[1] = z;
+                    *reinterpret_cast<uint4 *>(a.dsig16 + tiled_word(grow, 16, 0)) = pack8(s8);
+                    *reinterpret_cast<uint4 *>(a.dsig16 + tiled_word(grow, 16, 1)) = z;
                 }
             }
             tc05::fence_proxy_async();
             tc05::fence_before_sync();
             mbar_arrive(&ctl->h_ready[t]);
+#ifdef ARCB200_PROF
+            if (tid == 0) atomicAdd(&g_chain_load_prof[0], (unsigned long long)(clock64() - ld_t0));
+#endif
 
             for (int l = 0; l < L; ++l) {
                 const Layer &ly = prog.layer[l];
-                const int N = ly.N;
+                // every field the epilogue needs, read once: the inline-asm TMEM instructions are memory barriers for the
+                // compiler, which would otherwise fetch them again (indexed constant loads) in front of every 16 columns
+                const int N = ly.N, act = ly.act, flags = ly.flags, bias_off = ly.bias_off, vec_off = ly.vec_off,
+                          save_col = ly.save_col, mask_col = ly.mask_col;
                 float sigma_v = 0.f;
-                if (ly.flags & F_SIGMA) {
+                if ((flags & F_SIGMA) && half == 0) {
                     // density row of the last geometry layer on the CUDA cores while that layer's MMAs run: the operand tile is
                     // read-only until the accumulators are complete
-                    const float *sw = a.vec + ly.vec_off;
+                    const float *sw = a.vec + vec_off;
+                    float wl[8];                                   // lane j holds weights j, j + 32, ...: one coalesced read per warp
+                    #pragma unroll
+                    for (int q8 = 0; q8 < 8; ++q8) wl[q8] = __ldg(sw + q8 * 32 + lane);
                     float acc_s = __ldg(sw + kHCols);
-                    for (int cg = 0; cg < kHCols / 8; ++cg) {
-                        float h[8];
-                        unpack8(*tile_word(tile, r, cg), h);
-                        const float4 w0 = __ldg(reinterpret_cast<const float4 *>(sw) + 2 * cg), w1 = __ldg(reinterpret_cast<const float4 *>(sw) + 2 * cg + 1);
-                        acc_s = fmaf(h[0], w0.x, acc_s); acc_s = fmaf(h[1], w0.y, acc_s); acc_s = fmaf(h[2], w0.z, acc_s); acc_s = fmaf(h[3], w0.w, acc_s);
-                        acc_s = fmaf(h[4], w1.x, acc_s); acc_s = fmaf(h[5], w1.y, acc_s); acc_s = fmaf(h[6], w1.z, acc_s); acc_s = fmaf(h[7], w1.w, acc_s);
+                    #pragma unroll
+                    for (int q8 = 0; q8 < 8; ++q8) {
+                        #pragma unroll
+                        for (int g4 = 0; g4 < 4; ++g4) {
+                            float h[8];
+                            unpack8(*tile_word(tile, r, q8 * 4 + g4), h);
+                            #pragma unroll
+                            for (int k = 0; k < 8; ++k) acc_s = fmaf(h[k], __shfl_sync(0xffffffffu, wl[q8], g4 * 8 + k), acc_s);
+                        }
                     }
                     sigma_v = acc_s;
                 }
-                tc05::mbar_wait(&ctl->acc_full[t], accph);
+                // the layer's bias (forward) or row vector (backward) into shared memory while the MMAs of the layer run: one
+                // coalesced read per layer instead of a global load in front of every 16 columns of the epilogue
+                float *lv = vec_s + t * 256;
+                const int lv_off = bias_off >= 0 ? bias_off : ((BWD && (flags & F_RANK1)) ? vec_off : -1);
+                if (lv_off >= 0) {
+                    asm volatile("bar.sync %0, 256;" :: "r"(1 + t) : "memory");          // everyone is done with the previous layer's vector
+                    lv[r + 128 * half] = r + 128 * half < N ? __ldg(a.vec + lv_off + r + 128 * half) : 0.f;
+                    asm volatile("bar.sync %0, 256;" :: "r"(1 + t) : "memory");
+                }
+#ifdef ARCB200_PROF
+                const long long ep_t0 = clock64();
+#endif
+                if (lane == 0) mbar_wait_sleep(&ctl->acc_full[t], accph, 100);      // one lane polls for the warp
+                __syncwarp();
                 accph ^= 1u;
+#ifdef ARCB200_PROF
+                const long long ep_t1 = clock64();
+                if (tid == 0) atomicAdd(&g_chain_prof[3], (unsigned long long)(ep_t1 - ep_t0));
+#endif
                 tc05::fence_after_sync();
-                if ((ly.flags & F_SIGMA) && live) a.sigma[grow] = sigma_v;
-                const float *bias = ly.bias_off >= 0 ? a.vec + ly.bias_off : nullptr;
-                const __half *mask = (BWD && (ly.flags & F_MASK)) ? a.fwd_save + (size_t)ly.mask_col * a.n_cap + grow * N : nullptr;
-                const float *r1 = (BWD && (ly.flags & F_RANK1)) ? a.vec + ly.vec_off : nullptr;
-                __half *save = (a.save && ly.save_col >= 0) ? a.save + (size_t)ly.save_col * a.n_cap + grow * N : nullptr;
-                for (int cb = 0; cb < N / 16; cb += 2) {
+                if ((flags & F_SIGMA) && half == 0 && live) a.sigma[grow] = sigma_v;
+                const float *bias = bias_off >= 0 ? lv : nullptr;
+                const __half *mask = (BWD && (flags & F_MASK)) ? a.fwd_save + (size_t)mask_col * a.n_cap : nullptr;
+                const float *r1 = (BWD && (flags & F_RANK1)) ? lv : nullptr;
+                // 64 columns per trip: four TMEM loads and (backward) the eight mask words of the trip are in flight together
+                // this half's 16-column blocks: [cb_lo, cb_hi); two blocks (32 columns) per trip, their TMEM loads and (backward)
+                // mask words in flight together
+                const int nblk = N / 16, cb_lo = half * ((nblk + 1) / 2), cb_hi = half ? nblk : (nblk + 1) / 2;
+                for (int cb = cb_lo; cb < cb_hi; cb += 2) {
+#ifdef ARCB200_PROF
+                    if (a.dbg_skip & 8) break;
+#endif
+                    const int nb = (cb_hi - cb) < 2 ? (cb_hi - cb) : 2;
                     uint32_t q[2][16];
+                    uint4 mw[4];
+#ifdef ARCB200_PROF
+                    if (a.dbg_skip & 4) {
+                        #pragma unroll
+                        for (int k = 0; k < 16; ++k) { q[0][k] = (uint32_t)(k + cb); q[1][k] = (uint32_t)(k * 3 + cb); }
+                    } else
+#endif
+                    {
                     tc05::tmem_ld16(acc + (uint32_t)cb * 16, q[0]);
-                    if (cb + 1 < N / 16) tc05::tmem_ld16(acc + (uint32_t)cb * 16 + 16, q[1]);
+                    if (nb > 1) tc05::tmem_ld16(acc + (uint32_t)cb * 16 + 16, q[1]);
+                    }
+                    if (mask) {
+                        #pragma unroll
+                        for (int w = 0; w < 4; ++w)
+                            mw[w] = (live && w < 2 * nb) ? __ldg(reinterpret_cast<const uint4 *>(mask + tiled_word(grow, N, 2 * cb + w))) : make_uint4(0u, 0u, 0u, 0u);
+                    }
+#ifdef ARCB200_PROF
+                    const long long tp0 = clock64();
+#endif
                     tc05::tmem_ld_wait();
+#ifdef ARCB200_PROF
+                    const long long tp1 = clock64();
+                    if (tid == 0) atomicAdd(&g_chain_load_prof[1], (unsigned long long)(tp1 - tp0));
+#endif
                     #pragma unroll
                     for (int u = 0; u < 2; ++u) {
-                        if (cb + u >= N / 16) break;
+                        if (u >= nb) break;
                         const int c0 = (cb + u) * 16;
                         float v[16];
                         #pragma unroll
                         for (int k = 0; k < 16; ++k) v[k] = __uint_as_float(q[u][k]);
-                        if (bias) {
+                        if (bias
+#ifdef ARCB200_PROF
+                            && !(a.dbg_skip & 1)
+#endif
+                        ) {
+                            float4 b[4];
+                            #pragma unroll
+                            for (int k4 = 0; k4 < 4; ++k4) b[k4] = reinterpret_cast<const float4 *>(bias + c0)[k4];
                             #pragma unroll
                             for (int k4 = 0; k4 < 4; ++k4) {
-                                const float4 b = __ldg(reinterpret_cast<const float4 *>(bias + c0) + k4);
-                                v[4 * k4] += b.x; v[4 * k4 + 1] += b.y; v[4 * k4 + 2] += b.z; v[4 * k4 + 3] += b.w;
+                                v[4 * k4] += b[k4].x; v[4 * k4 + 1] += b[k4].y; v[4 * k4 + 2] += b[k4].z; v[4 * k4 + 3] += b[k4].w;
                             }
                         }
                         if (r1) {
                             #pragma unroll
                             for (int k4 = 0; k4 < 4; ++k4) {
-                                const float4 b = __ldg(reinterpret_cast<const float4 *>(r1 + c0) + k4);
+                                const float4 b = reinterpret_cast<const float4 *>(r1 + c0)[k4];
                                 v[4 * k4] = fmaf(dsig, b.x, v[4 * k4]); v[4 * k4 + 1] = fmaf(dsig, b.y, v[4 * k4 + 1]);
                                 v[4 * k4 + 2] = fmaf(dsig, b.z, v[4 * k4 + 2]); v[4 * k4 + 3] = fmaf(dsig, b.w, v[4 * k4 + 3]);
                             }
                         }
-                        if (ly.act == ACT_RELU) {
+                        if (act == ACT_RELU) {
                             #pragma unroll
                             for (int k = 0; k < 16; ++k) v[k] = fmaxf(v[k], 0.f);
-                        } else if (ly.act == ACT_SIGMOID) {
+                        } else if (act == ACT_SIGMOID) {
                             #pragma unroll
                             for (int k = 0; k < 16; ++k) v[k] = 1.0f / (1.0f + __expf(-v[k]));
                         }
                         if (mask) {
                             float m[16];
-                            if (live) {
-                                unpack8(__ldg(reinterpret_cast<const uint4 *>(mask + c0)), m);
-                                unpack8(__ldg(reinterpret_cast<const uint4 *>(mask + c0) + 1), m + 8);
-                            }
+                            unpack8(mw[2 * u], m);
+                            unpack8(mw[2 * u + 1], m + 8);
                             #pragma unroll
-                            for (int k = 0; k < 16; ++k) v[k] = (live && m[k] > 0.f) ? v[k] : 0.f;
+                            for (int k = 0; k < 16; ++k) v[k] = m[k] > 0.f ? v[k] : 0.f;
                         }
-                        if (ly.flags & F_OUT_RGB) {
+                        if (flags & F_OUT_RGB) {
                             if (live && c0 == 0) { a.rgb[grow * 3] = v[0]; a.rgb[grow * 3 + 1] = v[1]; a.rgb[grow * 3 + 2] = v[2]; }
                         } else {
                             const uint4 w0 = pack8(v), w1 = pack8(v + 8);
+#ifdef ARCB200_PROF
+                            if (!(a.dbg_skip & 2) || w0.x == 0x12345678u)
+#endif
+                            {
                             *tile_word(tile, r, 2 * (cb + u)) = w0;
                             *tile_word(tile, r, 2 * (cb + u) + 1) = w1;
-                            if (save && live) {
-                                reinterpret_cast<uint4 *>(save + c0)[0] = w0;
-                                reinterpret_cast<uint4 *>(save + c0)[1] = w1;
                             }
                         }
                     }
                 }
-                if (!BWD && (ly.flags & F_VIEW)) {
+                if (!BWD && (flags & F_VIEW) && half == 1) {
                     // the position embedding has served its last layer: the view embedding takes its columns
                     float d[3] = {0.f, 0.f, 1.f};
                     if (live) {
@@ -338,23 +500,25 @@ dense_chain_kernel(const __grid_constant__ Program prog, const ChainArgs a) {
                         const float inv = 1.0f / sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
                         d[0] *= inv; d[1] *= inv; d[2] *= inv;
                     }
-                    for (int cg = 0; cg < 4; ++cg) {
-                        float v[8];
-                        #pragma unroll
-                        for (int k = 0; k < 8; ++k) {
-                            const int c = cg * 8 + k;
-                            v[k] = (live && c < prog.embed_v) ? embed_col(d, 3, c) : 0.f;
-                        }
-                        const uint4 w = pack8(v);
-                        *tile_word(tile, r, aux_cg0 + cg) = w;
-                        if (a.save && live) *reinterpret_cast<uint4 *>(a.save + (size_t)prog.ve_col * a.n_cap + grow * 32 + cg * 8) = w;
-                    }
+                    write_embedding(tile, r, aux_cg0, d, 3, prog.n_freq_v, 32, live);
                 }
-                if (l + 1 < L) {
+                if (l + 1 < L || (BWD && a.save)) {
+#ifdef ARCB200_PROF
+                    if (!(a.dbg_skip & 16))
+#endif
                     tc05::fence_proxy_async();
                     tc05::fence_before_sync();
                     mbar_arrive(&ctl->h_ready[t]);
                 }
+#ifdef ARCB200_PROF
+                if (tid == 0) { atomicAdd(&g_chain_prof[4], (unsigned long long)(clock64() - ep_t1)); atomicAdd(&g_chain_layer_prof[l], (unsigned long long)(clock64() - ep_t1)); }
+#endif
+            }
+            if (BWD && a.save) {
+                // the MMA thread stores the last gradient tile and says when the tile may be overwritten by the next pair
+                if (lane == 0) mbar_wait_sleep(&ctl->acc_full[t], accph, 100);
+                __syncwarp();
+                accph ^= 1u;
             }
             tc05::fence_before_sync();      // the next pair's first MMA must not overtake these accumulator reads
         }
@@ -388,7 +552,27 @@ __device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src,
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" :: "r"(tc05::smem_u32(smem_dst)), "l"(gmem_src), "r"(sz) : "memory");
 }
 
-__global__ void __launch_bounds__(kWgThreads, 1) dense_wgrad_kernel(const WgArgs a) {
+// All weight-gradient GEMMs of a backward pass run as ONE launch: job j owns CTAs [first[j], first[j+1]), which split the
+// batch rows between them.  A job with few CTAs flushes few partial sums (the flush is atomics on the same dW entries), and
+// the jobs together fill the machine.
+#ifdef ARCB200_PROF
+__device__ unsigned long long g_wg_prof[8];   // thread 0 of big jobs: [0] wait stage free, [1] issue loads, [2] wait loads, [3] column sums, [4] sync + MMA issue, [5] iterations
+#define WG_PROF(slot, expr) do { const long long t0__ = clock64(); expr; if (tid == 0 && a.N == 256 && a.K == 256) atomicAdd(&g_wg_prof[slot], (unsigned long long)(clock64() - t0__)); } while (0)
+#else
+#define WG_PROF(slot, expr) do { expr; } while (0)
+#endif
+constexpr int kMaxWgJobs = 20;
+struct WgJobs {
+    WgArgs job[kMaxWgJobs];
+    int32_t first[kMaxWgJobs + 1];
+    int32_t n_jobs;
+};
+
+__global__ void __launch_bounds__(kWgThreads, 1) dense_wgrad_kernel(const __grid_constant__ WgJobs jobs) {
+    int ji = 0;
+    while (ji + 1 < jobs.n_jobs && (int)blockIdx.x >= jobs.first[ji + 1]) ++ji;
+    const WgArgs &a = jobs.job[ji];
+    const int cta = (int)blockIdx.x - jobs.first[ji], n_cta = jobs.first[ji + 1] - jobs.first[ji];
     extern __shared__ __align__(128) uint8_t smem[];
     uint64_t *mbar = reinterpret_cast<uint64_t *>(smem);          // [kWgStages] stage consumed by the tensor core
     uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(smem + 64);
@@ -411,25 +595,31 @@ __global__ void __launch_bounds__(kWgThreads, 1) dense_wgrad_kernel(const WgArgs
     const uint32_t tmem = *tmem_slot;
     // rows of this CTA
     const int64_t blocks = (a.n + kWgRows - 1) / kWgRows;
-    const int64_t per = (blocks + gridDim.x - 1) / gridDim.x;
-    const int64_t b0 = (int64_t)blockIdx.x * per, b1 = b0 + per < blocks ? b0 + per : blocks;
+    const int64_t per = (blocks + n_cta - 1) / n_cta;
+    const int64_t b0 = (int64_t)cta * per, b1 = b0 + per < blocks ? b0 + per : blocks;
     const int n_iter = b1 > b0 ? (int)(b1 - b0) : 0;
     const int dz_words = kWgRows * (a.N / 8), act_words = kWgRows * (a.K / 8);
     const int n_half = Mp / 128;
-    float colsum[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};      // this thread always stages the same dZ column group
+    float colsum[8][8];                  // bias gradient: partial column sums of the dZ words this thread stages
+    #pragma unroll
+    for (int q = 0; q < 8; ++q)
+        #pragma unroll
+        for (int k = 0; k < 8; ++k) colsum[q][k] = 0.f;
 
     auto stage_load = [&](int it) {
         uint8_t *st = stage0 + (size_t)(it % kWgStages) * stage_bytes;
         const int64_t row0 = (b0 + it) * kWgRows;
         // a word = 8 columns of one row; word w -> (row = w / groups, group = w % groups): consecutive threads read consecutive
         // 16-byte pieces of a row (coalesced), and write the MN-major tile: group * (64 * 16) + row * 16
+        // sources are in the tiled layout (see tiled_word): word w -> (group = w / 64, row = w % 64), so that consecutive threads
+        // read consecutive 16-byte words of a tile's column group and write consecutive words of the stage
         for (int w = tid; w < dz_words; w += kWgThreads) {
-            const int groups = a.N / 8, rr = w / groups, cg = w - rr * groups;
-            cp_async16(st + (size_t)cg * (kWgRows * 16) + (size_t)rr * 16, a.dz + (row0 + rr) * a.ldz + cg * 8, row0 + rr < a.n);
+            const int cg = w >> 6, rr = w & 63;
+            cp_async16(st + (size_t)cg * (kWgRows * 16) + (size_t)rr * 16, a.dz + tiled_word(row0 + rr, (int)a.ldz, cg), row0 + rr < a.n);
         }
         for (int w = tid; w < act_words; w += kWgThreads) {
-            const int groups = a.K / 8, rr = w / groups, cg = w - rr * groups;
-            cp_async16(st + dz_bytes + (size_t)cg * (kWgRows * 16) + (size_t)rr * 16, a.act + (row0 + rr) * a.lda + cg * 8, row0 + rr < a.n);
+            const int cg = w >> 6, rr = w & 63;
+            cp_async16(st + dz_bytes + (size_t)cg * (kWgRows * 16) + (size_t)rr * 16, a.act + tiled_word(row0 + rr, (int)a.lda, cg), row0 + rr < a.n);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
@@ -450,28 +640,34 @@ __global__ void __launch_bounds__(kWgThreads, 1) dense_wgrad_kernel(const WgArgs
         // the stage that the next load overwrites was consumed by the MMAs of iteration it-1
         if (it + kWgStages - 1 < n_iter) {
             const int sn = (it + kWgStages - 1) % kWgStages;
-            if (it >= 1) { tc05::mbar_wait(&mbar[sn], ph[sn]); ph[sn] ^= 1u; ++waits[sn]; }
-            stage_load(it + kWgStages - 1);
+            if (it >= 1) { WG_PROF(0, tc05::mbar_wait(&mbar[sn], ph[sn])); ph[sn] ^= 1u; ++waits[sn]; }
+            WG_PROF(1, stage_load(it + kWgStages - 1));
         } else {
             asm volatile("cp.async.commit_group;" ::: "memory");
         }
-        asm volatile("cp.async.wait_group %0;" :: "n"(kWgStages - 1) : "memory");
+        WG_PROF(2, asm volatile("cp.async.wait_group %0;" :: "n"(kWgStages - 1) : "memory"));
+#ifdef ARCB200_PROF
+        const long long cs_t0 = clock64();
+#endif
         // bias gradient: column sums of the dZ words this thread staged itself (visible to it after its own wait)
         if (a.db) {
             uint8_t *st = stage0 + (size_t)s * stage_bytes;
-            for (int w = tid; w < dz_words; w += kWgThreads) {
-                const int groups = a.N / 8, rr = w / groups, cg = w - rr * groups;
-                float v[8];
-                unpack8(*reinterpret_cast<const uint4 *>(st + (size_t)cg * (kWgRows * 16) + (size_t)rr * 16), v);
-                if ((kWgThreads % groups) == 0) {          // fixed column group per thread: keep the sums in registers
+            // word tid + 256 q of every stage is column group (tid >> 6) + 4 q: one register accumulator set per q
+            #pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int w = tid + q * kWgThreads;
+                if (w < dz_words) {
+                    float v[8];
+                    unpack8(*reinterpret_cast<const uint4 *>(st + (size_t)(w >> 6) * (kWgRows * 16) + (size_t)(w & 63) * 16), v);
                     #pragma unroll
-                    for (int k = 0; k < 8; ++k) colsum[k] += v[k];
-                } else {
-                    #pragma unroll
-                    for (int k = 0; k < 8; ++k) atomicAdd(&db_s[cg * 8 + k], v[k]);
+                    for (int k = 0; k < 8; ++k) colsum[q][k] += v[k];
                 }
             }
         }
+#ifdef ARCB200_PROF
+        const long long cs_t1 = clock64();
+        if (tid == 0 && a.N == 256 && a.K == 256) { atomicAdd(&g_wg_prof[3], (unsigned long long)(cs_t1 - cs_t0)); atomicAdd(&g_wg_prof[5], 1ull); }
+#endif
         tc05::fence_proxy_async();
         tc05::fence_before_sync();
         __syncthreads();
@@ -488,6 +684,9 @@ __global__ void __launch_bounds__(kWgThreads, 1) dense_wgrad_kernel(const WgArgs
             }
             tc05::mma_commit(&mbar[s]);
         }
+#ifdef ARCB200_PROF
+        if (tid == 0 && a.N == 256 && a.K == 256) atomicAdd(&g_wg_prof[4], (unsigned long long)(clock64() - cs_t1));
+#endif
         ++commits[s];
     }
     // drain: every commit that has not been waited for yet (all threads followed the same schedule, so they agree on the counts)
@@ -512,11 +711,13 @@ __global__ void __launch_bounds__(kWgThreads, 1) dense_wgrad_kernel(const WgArgs
             }
         }
         if (a.db) {
-            const int groups = a.N / 8;
-            if ((kWgThreads % groups) == 0) {
-                const int cg = tid % groups;
-                #pragma unroll
-                for (int k = 0; k < 8; ++k) atomicAdd(&db_s[cg * 8 + k], colsum[k]);
+            #pragma unroll
+            for (int q = 0; q < 8; ++q) {
+                const int w = tid + q * kWgThreads;
+                if (w < dz_words) {
+                    #pragma unroll
+                    for (int k = 0; k < 8; ++k) atomicAdd(&db_s[(w >> 6) * 8 + k], colsum[q][k]);
+                }
             }
             __syncthreads();
             if (tid < a.N && tid < a.n_out_valid) atomicAdd(a.db + tid, db_s[tid] * a.out_scale);
@@ -607,7 +808,7 @@ void make_vec_layout(const NerfArch &A, VecLayout &V) {
 
 static int n_slots_for(const NerfArch &A) {
     const size_t tile = (size_t)kRows * (kHCols + A.aux_cols) * 2;
-    const long long left = 227ll * 1024 - 256 - 2 * (long long)tile;
+    const long long left = 227ll * 1024 - 256 - 2 * 256 * 4 - 2 * (long long)tile;
     int s = (int)(left / kSlotBytes);
     return s > kMaxSlots ? kMaxSlots : s;
 }
@@ -722,7 +923,7 @@ void build_backward(const NerfArch &A, const VecLayout &V, const Program &F, Pro
 }
 
 static size_t chain_smem(const Program &P) {
-    return 256 + 2 * (size_t)kRows * (kHCols + P.aux_cols) * 2 + (size_t)P.n_slots * kSlotBytes;
+    return 256 + 2 * (size_t)kRows * (kHCols + P.aux_cols) * 2 + (size_t)P.n_slots * kSlotBytes + 2 * 256 * sizeof(float);
 }
 
 template <typename K>
@@ -743,18 +944,39 @@ static int build_all(Built &b, int d_x, int n_freq_x, int n_freq_v, int W, int D
     return 0;
 }
 
-static int launch_wgrad(const __half *dz, int64_t ldz, int N, int n_out_valid, const __half *act, int64_t lda, int K, int k_valid,
-                        float *dW, int64_t ldw, float *db, float out_scale, int64_t n, cudaStream_t st) {
-    WgArgs w;
+static void add_wgrad(WgJobs &J, const __half *dz, int64_t ldz, int N, int n_out_valid, const __half *act, int64_t lda, int K, int k_valid,
+                      float *dW, int64_t ldw, float *db, float out_scale, int64_t n) {
+    WgArgs &w = J.job[J.n_jobs++];
     w.dz = dz; w.ldz = ldz; w.N = N; w.act = act; w.lda = lda; w.K = K; w.n_out_valid = n_out_valid; w.k_valid = k_valid;
     w.dW = dW; w.ldw = ldw; w.db = db; w.out_scale = out_scale; w.n = n;
-    const int Mp = (N + 127) / 128 * 128;
-    const size_t smem = 128 + 1024 + (size_t)kWgStages * kWgRows * (Mp + K) * 2;
+}
+
+// CTAs per job in proportion to the cost of one of its 64-row iterations, which the staging of the two operands and the
+// fixed per-iteration work dominate (measured: about 3100 cycles for 256 + 256 columns, of which 1000 are tensor-core time),
+// at least one each, all SMs used
+static int launch_wgrad_jobs(WgJobs &J, cudaStream_t st) {
+    const int sms = arc_sm_count();
+    double work[kMaxWgJobs], total = 0.0;
+    size_t smem = 0;
+    for (int j = 0; j < J.n_jobs; ++j) {
+        const int Mp = (J.job[j].N + 127) / 128 * 128;
+        work[j] = (double)(Mp + J.job[j].K) + 128.0;
+        total += work[j];
+        const size_t need = 128 + 1024 + (size_t)kWgStages * kWgRows * (Mp + J.job[j].K) * 2;
+        smem = need > smem ? need : smem;
+    }
+    const int64_t blocks = (J.job[0].n + kWgRows - 1) / kWgRows;
+    int used = 0;
+    J.first[0] = 0;
+    for (int j = 0; j < J.n_jobs; ++j) {
+        int c = (int)(work[j] / total * (sms - J.n_jobs)) + 1;
+        if (c > blocks) c = (int)blocks;
+        used += c;
+        J.first[j + 1] = used;
+    }
     int rc = set_max_smem(dense_wgrad_kernel, smem);
     if (rc != ARCB200_OK) return rc;
-    const int64_t blocks = (n + kWgRows - 1) / kWgRows;
-    const int64_t cap = arc_sm_count();
-    arc_launch(dense_wgrad_kernel, (unsigned)(blocks < cap ? blocks : cap), kWgThreads, smem, st, w);
+    arc_launch(dense_wgrad_kernel, (unsigned)used, kWgThreads, smem, st, J);
     return ARCB200_OK;
 }
 
@@ -804,12 +1026,13 @@ int arcb200_nerf_mlp_fwd(NERF_ARCH_ARGS, const float *x, const float *dirs, cons
     Built b;
     ARC_REQUIRE(build_all(b, NERF_ARCH_PASS) == 0, "nerf_mlp_fwd: unsupported architecture");
     ARC_REQUIRE(x && dirs && blob_fwd && vec && sigma && rgb, "nerf_mlp_fwd: null pointer");
-    ARC_REQUIRE((((uintptr_t)blob_fwd | (uintptr_t)vec | (uintptr_t)save) & 15u) == 0 && (n_cap % 8) == 0,
-                "nerf_mlp_fwd: blob / vec / save must be 16-byte aligned and n_cap a multiple of 8");
+    ARC_REQUIRE((((uintptr_t)blob_fwd | (uintptr_t)vec | (uintptr_t)save) & 15u) == 0 && (n_cap % 128) == 0,
+                "nerf_mlp_fwd: blob / vec / save must be 16-byte aligned and n_cap a multiple of 128");
     ChainArgs a;
     memset(&a, 0, sizeof(a));
     a.x = x; a.dirs = dirs; a.blob = (const uint8_t *)blob_fwd; a.vec = vec; a.save = (__half *)save; a.sigma = sigma; a.rgb = rgb;
     a.n = n; a.n_cap = n_cap;
+    if (const char *e = getenv("ARCB200_CHAIN_DBG")) a.dbg_skip = atoi(e);
     const size_t smem = chain_smem(b.F);
     int rc = set_max_smem(dense_chain_kernel<false>, smem);
     if (rc != ARCB200_OK) return rc;
@@ -834,7 +1057,7 @@ int arcb200_nerf_mlp_bwd(NERF_ARCH_ARGS, const void *blob_bwd, const float *vec,
     ARC_REQUIRE(build_all(b, NERF_ARCH_PASS) == 0, "nerf_mlp_bwd: unsupported architecture");
     ARC_REQUIRE(blob_bwd && vec && fwd_save && rgb && d_sigma && d_rgb && bwd_save && dsig16 && d_params, "nerf_mlp_bwd: null pointer");
     ARC_REQUIRE((((uintptr_t)blob_bwd | (uintptr_t)vec | (uintptr_t)fwd_save | (uintptr_t)bwd_save | (uintptr_t)dsig16) & 15u) == 0 &&
-                (n_cap % 8) == 0, "nerf_mlp_bwd: buffers must be 16-byte aligned and n_cap a multiple of 8");
+                (n_cap % 128) == 0, "nerf_mlp_bwd: buffers must be 16-byte aligned and n_cap a multiple of 128");
     cudaStream_t st = (cudaStream_t)stream;
     ChainArgs a;
     memset(&a, 0, sizeof(a));
@@ -844,8 +1067,11 @@ int arcb200_nerf_mlp_bwd(NERF_ARCH_ARGS, const void *blob_bwd, const float *vec,
     int rc = set_max_smem(dense_chain_kernel<true>, smem);
     if (rc != ARCB200_OK) return rc;
     const int64_t pairs = (n + 2 * kRows - 1) / (2 * kRows), cap = arc_sm_count();
-    arc_launch(dense_chain_kernel<true>, (unsigned)(pairs < cap ? pairs : cap), kThreads, smem, st, b.B, a);
+    const char *parts_env = getenv("ARCB200_NERF_BWD_PARTS");           // profiling aid: 1 = data-gradient chain only, 2 = weight gradients only
+    const int parts = parts_env ? atoi(parts_env) : 3;
+    if (parts & 1) arc_launch(dense_chain_kernel<true>, (unsigned)(pairs < cap ? pairs : cap), kThreads, smem, st, b.B, a);
     ARC_LAUNCH_CHECK();
+    if (!(parts & 2)) return ARCB200_OK;
 
     // weight and bias gradients, one batch-contraction GEMM per (layer, input source)
     const NerfArch &A = b.A;
@@ -859,7 +1085,9 @@ int arcb200_nerf_mlp_bwd(NERF_ARCH_ARGS, const void *blob_bwd, const float *vec,
     auto dZ = [&](int i) { return bcol(b.B.layer[2 + (D - 1 - i)].save_col); };
     float *g = d_params;
     const int l_r0 = D + 1, l_r1 = D + 2;
-#define WG(...) do { rc = launch_wgrad(__VA_ARGS__, 1.0f / loss_scale, n, st); if (rc != ARCB200_OK) return rc; } while (0)
+    WgJobs J;
+    memset(&J, 0, sizeof(J));
+#define WG(...) add_wgrad(J, __VA_ARGS__, 1.0f / loss_scale, n)
     // colour layer (3 x W_rad)
     WG(dz_rgb, 16, 16, 3, H(D + 1), A.W_rad, A.W_rad, A.W_rad, g + A.w_off[l_r1], A.W_rad, g + A.b_off[l_r1]);
     // radiance hidden layer (W_rad x (embed_v + W)): view columns, then feature columns
@@ -878,8 +1106,29 @@ int arcb200_nerf_mlp_bwd(NERF_ARCH_ARGS, const void *blob_bwd, const float *vec,
         }
     }
 #undef WG
+    rc = launch_wgrad_jobs(J, st);
+    if (rc != ARCB200_OK) return rc;
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }
+
+#ifdef ARCB200_PROF
+int arcb200_debug_wg_prof(unsigned long long *out8) {
+    ARC_CUDA(cudaMemcpyFromSymbol(out8, g_wg_prof, sizeof(unsigned long long) * 8));
+    unsigned long long z[8] = {0};
+    ARC_CUDA(cudaMemcpyToSymbol(g_wg_prof, z, sizeof(z)));
+    return ARCB200_OK;
+}
+int arcb200_debug_chain_prof(unsigned long long *out8) {
+    ARC_CUDA(cudaMemcpyFromSymbol(out8, g_chain_prof, sizeof(unsigned long long) * 8));
+    ARC_CUDA(cudaMemcpyFromSymbol(out8 + 8, g_chain_layer_prof, sizeof(unsigned long long) * 16));
+    ARC_CUDA(cudaMemcpyFromSymbol(out8 + 24, g_chain_load_prof, sizeof(unsigned long long) * 2));
+    unsigned long long z[16] = {0};
+    ARC_CUDA(cudaMemcpyToSymbol(g_chain_prof, z, sizeof(unsigned long long) * 8));
+    ARC_CUDA(cudaMemcpyToSymbol(g_chain_layer_prof, z, sizeof(z)));
+    ARC_CUDA(cudaMemcpyToSymbol(g_chain_load_prof, z, sizeof(unsigned long long) * 2));
+    return ARCB200_OK;
+}
+#endif
 
 }  // extern "C"

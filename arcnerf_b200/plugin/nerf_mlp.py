@@ -19,13 +19,12 @@ from .. import _lib
 
 class _ChainFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, nets, x, dirs, flat):
+    def forward(ctx, nets, x, dirs, flat, need_grad):
         n = x.shape[0]
         sigma = torch.empty((n,), dtype=torch.float32, device=x.device)
         rgb = torch.empty((n, 3), dtype=torch.float32, device=x.device)
-        need_grad = ctx.needs_input_grad[3]          # (grad mode is off inside Function.forward; this is the caller's view)
         nets._pack_if_changed()
-        n_cap = (n + 7) // 8 * 8
+        n_cap = (n + 127) // 128 * 128
         save = torch.empty(nets.fwd_cols * n_cap, dtype=torch.float16, device=x.device) if need_grad else None
         _lib.call('arcb200_nerf_mlp_fwd', *nets.arch, x.data_ptr(), dirs.data_ptr(), nets.blob_fwd.data_ptr(), nets.vec.data_ptr(),
                   _lib.ptr(save), n_cap, sigma.data_ptr(), rgb.data_ptr(), n, _lib.current_stream())
@@ -48,7 +47,7 @@ class _ChainFn(torch.autograd.Function):
         _lib.call('arcb200_nerf_mlp_bwd', *nets.arch, nets.blob_bwd.data_ptr(), nets.vec.data_ptr(), save.data_ptr(), rgb.data_ptr(),
                   g_sigma.data_ptr(), g_rgb.data_ptr(), float(nets.loss_scale), bwd_save.data_ptr(), dsig16.data_ptr(), n_cap, d_params.data_ptr(), n,
                   _lib.current_stream())
-        return None, None, None, d_params
+        return None, None, None, d_params, None
 
 
 class FusedNeRFNets(nn.Module):
@@ -116,8 +115,15 @@ class FusedNeRFNets(nn.Module):
             rad['layers.%d.weight' % i], rad['layers.%d.bias' % i] = views[n_geo + i][0].clone(), views[n_geo + i][1].clone()
         return geo, rad
 
+    @staticmethod
+    def untile(region, n_cap, width):
+        """a saved tensor (flat fp16 region of n_cap * width elements in the operand-tile layout of csrc/dense_chain.cu: 128-row
+        tiles, inside a tile 8-column groups of 128 rows) -> (n_cap, width) row-major"""
+        return region.view(n_cap // 128, width // 8, 128, 8).permute(0, 2, 1, 3).reshape(n_cap, width)
+
     def saved_columns(self):
-        """name -> (first column, width) of the forward save buffer (region c starts at c * n_cap, row stride = width)"""
+        """name -> (first column, width) of the forward save buffer (region c starts at c * n_cap and holds n_cap * width
+        elements in the tiled layout, see untile)"""
         d_x, nfx, nfv, W, D, skip, W_rad = self.arch
         xe_pad = (self.embed_x + 31) // 32 * 32
         cols, c = {'xe': (0, xe_pad), 've': (xe_pad, 32)}, xe_pad + 32
@@ -140,5 +146,7 @@ class FusedNeRFNets(nn.Module):
         if not x.is_cuda or not view_dirs.is_cuda:
             raise RuntimeError('FusedNeRFNets needs CUDA tensors')
         assert x.dim() == 2 and x.shape[1] == self.arch[0] and view_dirs.shape == (x.shape[0], 3), 'x (B,d_x), view_dirs (B,3)'
-        sigma, rgb = _ChainFn.apply(self, x.contiguous().float(), view_dirs.contiguous().float(), self.flat)
+        # activations are kept for a backward only when one can follow (grad mode is not visible inside Function.forward)
+        need_grad = torch.is_grad_enabled() and self.flat.requires_grad
+        sigma, rgb = _ChainFn.apply(self, x.contiguous().float(), view_dirs.contiguous().float(), self.flat, need_grad)
         return sigma.unsqueeze(-1), rgb

@@ -34,6 +34,7 @@ class Registry:
 ENCODER_REGISTRY = Registry('encoder')
 MODULE_REGISTRY = Registry('module')
 BOUND_REGISTRY = Registry('bound')
+MODEL_REGISTRY = Registry('model')          # arcnerf/models/__init__.py:19-41 (NeRF, NeRFPP, Neus ... selected by cfgs.model.type)
 
 
 def cfg_to_dict(cfg):

@@ -462,7 +462,8 @@ int arcb200_field_fwd(const float *unit, const void *table_half, int n_levels, i
  * arcb200_nerf_mlp_pack: parameters -> blobs + vectors (after every update).  _fwd: x (n,d_x), dirs (n,3) -> sigma (n) raw,
  * rgb (n,3); save = NULL for inference or (out[4] x n_cap) fp16.  _bwd: d_sigma (n), d_rgb (n,3) -> d_params ACCUMULATED;
  * bwd_save (out[5] x n_cap) fp16 and dsig16 (n_cap x 16) fp16 are scratch; loss_scale multiplies the gradients inside the fp16
- * tiles and is divided out again (128 in the reference's tcnn path).  n_cap % 8 == 0. */
+ * tiles and is divided out again (128 in the reference's tcnn path).  n_cap % 128 == 0; the save buffers keep the kernels'
+ * operand-tile layout (128-row tiles), they are opaque to the caller. */
 int arcb200_nerf_mlp_sizes(int d_x, int n_freq_x, int n_freq_v, int W, int D, int skip, int W_rad, int64_t *out);
 int arcb200_nerf_mlp_pack(int d_x, int n_freq_x, int n_freq_v, int W, int D, int skip, int W_rad, const float *params,
                           void *blob_fwd, void *blob_bwd, float *vec, void *stream);
