@@ -195,6 +195,7 @@ def main():
     ap.add_argument('--occ-every', type=int, default=16, help='occupancy refresh period in steps (0 = never); the reference config uses 16')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--stages', action='store_true', help='print the per-stage timing table to stderr')
+    ap.add_argument('--config', default='ngp', choices=['ngp', 'nerf'], help="ngp: BASELINE configs[1] (the headline); nerf: the vanilla-NeRF step of configs[0] (bench_nerf.py)")
     args = ap.parse_args()
 
     rank = int(os.environ.get('RANK', 0))
@@ -202,6 +203,11 @@ def main():
     world = int(os.environ.get('WORLD_SIZE', 1))
 
     if args.impl == 'reference':
+        if args.config == 'nerf':
+            if rank == 0:
+                import bench_nerf
+                bench_nerf.run_reference(args)
+            return
         run_reference_arm(args, rank, world)
         return
 
@@ -215,6 +221,14 @@ def main():
         dist = None
         torch.cuda.set_device(0)
     dev = torch.device('cuda', local_rank if world > 1 else 0)
+
+    if args.config == 'nerf':
+        import bench_nerf
+        bench_nerf.run(args, rank, world, dev, dist, read_peaks, ClockSampler)
+        if dist is not None:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
 
     from arcnerf_b200 import synth
     from arcnerf_b200.ngp import NGPPipeline, StageTimer
