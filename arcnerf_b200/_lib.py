@@ -92,6 +92,7 @@ _SIGS = {
     'arcb200_nerf_mlp_pack': [I, I, I, I, I, I, I, P, P, P, P, P],
     'arcb200_nerf_mlp_fwd': [I, I, I, I, I, I, I, P, P, P, P, P, L, P, P, L, P],
     'arcb200_nerf_mlp_bwd': [I, I, I, I, I, I, I, P, P, P, P, P, P, F, P, P, L, P, L, P],
+    'arcb200_gen_rays': [P, I, P, P, I, I, I, I, I, P, P, P, L, P],
     'arcb200_field_fwd': [P, P, I, I, P, P, P, P, P, P, P, I, P, P, P, P, P, P, P, L, P, P],
 }
 _RESTYPE = {

@@ -35,6 +35,7 @@ SOURCES = {
     'freq.cu': ['-fmad=false'],
     'probe.cu': [],
     'dense_chain.cu': [],
+    'raygen.cu': ['-fmad=false'],
 }
 
 

@@ -259,3 +259,52 @@ def upsample_zvals(zvals, weights, n_importance, det=True, eps=1e-5):
     zvals_mid = 0.5 * (zvals[..., 1:] + zvals[..., :-1])
     new = sample_pdf(zvals_mid, weights_coarse, n_importance, det, eps).detach()
     return sort_rows(torch.cat([zvals, new], -1)), new
+
+
+def pack_cameras(intrinsics, c2ws, device):
+    """(n,3,3) intrinsics + (n,4,4) poses -> the (n,17) device table arcb200_gen_rays reads"""
+    k, c = torch.as_tensor(intrinsics, dtype=torch.float32).reshape(-1, 3, 3), torch.as_tensor(c2ws, dtype=torch.float32).reshape(-1, 4, 4)
+    tab = torch.cat([k[:, 0, 0:1], k[:, 1, 1:2], k[:, 0, 2:3], k[:, 1, 2:3], k[:, 0, 1:2], c[:, :3, :].reshape(-1, 12)], 1)
+    return tab.contiguous().to(device)
+
+
+@torch.no_grad()
+def get_rays(W, H, intrinsic, c2w, wh_order=True, index=None, n_rays=-1, to_np=False, ndc=False, ndc_near=1.0, center_pixel=False,
+             normalize_rays_d=True):
+    """arcnerf.render.ray_helper.get_rays (:12-119) on the device: same arguments and returns (rays_o, rays_d, index list,
+    rays_r).  NDC rays are not provided."""
+    assert (index is None) or n_rays <= 0, 'You are not allowed to sampled both by index and N_ray'
+    assert not ndc, 'ndc rays are not provided by this build'
+    dev = intrinsic.device
+    if not intrinsic.is_cuda:
+        raise RuntimeError('get_rays needs CUDA tensors')
+    cams = pack_cameras(intrinsic, c2w, dev)
+    pix = None
+    if index is not None:
+        assert len(index.shape) == 2 and index.shape[-1] == 2, 'invalid shape, should be (N_rays, 2)'
+        idx = torch.as_tensor(index, dtype=torch.long, device=dev)
+        pix = (idx[:, 0] * H + idx[:, 1]).contiguous()
+    if n_rays > 0:
+        pix = torch.randperm(W * H, device=dev)[:n_rays].contiguous()
+    n = W * H if pix is None else pix.shape[0]
+    rays_o = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    rays_d = torch.empty((n, 3), dtype=torch.float32, device=dev)
+    rays_r = torch.empty((n, 1), dtype=torch.float32, device=dev) if pix is None else None
+    _lib.call('arcb200_gen_rays', cams.data_ptr(), 1, None, _lib.ptr(pix), int(W), int(H), int(bool(wh_order)), int(bool(center_pixel)),
+              int(bool(normalize_rays_d)), rays_o.data_ptr(), rays_d.data_ptr(), _lib.ptr(rays_r), n, _lib.current_stream())
+    index_list = pix.tolist() if pix is not None else None
+    if to_np:
+        return rays_o.cpu().numpy(), rays_d.cpu().numpy(), index_list, rays_r
+    return rays_o, rays_d, index_list, rays_r
+
+
+@torch.no_grad()
+def get_train_batch_rays(cams, cam_id, pix, W, H, center_pixel=False, normalize_rays_d=True):
+    """A training batch drawn from many cameras in one launch (what Pipeline.get_train_batch gathers from pre-computed per-image
+    rays, pipeline.py:204-300): cams from pack_cameras, cam_id (N) int32, pix (N) int64 pixel index i * H + j."""
+    n = pix.shape[0]
+    rays_o = torch.empty((n, 3), dtype=torch.float32, device=pix.device)
+    rays_d = torch.empty((n, 3), dtype=torch.float32, device=pix.device)
+    _lib.call('arcb200_gen_rays', cams.data_ptr(), cams.shape[0], cam_id.data_ptr(), pix.data_ptr(), int(W), int(H), 1,
+              int(bool(center_pixel)), int(bool(normalize_rays_d)), rays_o.data_ptr(), rays_d.data_ptr(), None, n, _lib.current_stream())
+    return rays_o, rays_d

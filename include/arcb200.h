@@ -474,6 +474,15 @@ int arcb200_nerf_mlp_bwd(int d_x, int n_freq_x, int n_freq_v, int W, int D, int 
                          const float *vec, const void *fwd_save, const float *rgb, const float *d_sigma, const float *d_rgb,
                          float loss_scale, void *bwd_save, void *dsig16, int64_t n_cap, float *d_params, int64_t n, void *stream);
 
+/* ---- camera rays on the device (csrc/raygen.cu) -----------------------------------------------------------------------
+ * One ray per (camera, pixel): replaces arcnerf/render/ray_helper.py:12-119 get_rays (pixel grid, pixel_to_world, direction,
+ * normalisation, mip-NeRF radius) and the per-batch ray gather of arcnerf/trainer/pipeline.py:204-300.  cams: DEVICE array of
+ * n_cams x 17 floats (fx, fy, cx, cy, skew, rows 0..2 of c2w row-major); cam_id (n) int32 or NULL (camera 0); pix (n) int64
+ * pixel index i * H + j, or NULL for the full W x H image (n = W * H) in wh order (wh_order != 0) or row-major; rays_r (n) or
+ * NULL (full image only). */
+int arcb200_gen_rays(const float *cams, int n_cams, const int32_t *cam_id, const int64_t *pix, int W, int H, int wh_order,
+                     int center_pixel, int normalize, float *rays_o, float *rays_d, float *rays_r, int64_t n, void *stream);
+
 /* ---- measurement aid (csrc/probe.cu) ---------------------------------------------------------------------------------
  * Random-gather bandwidth of a device table: n_threads (rounded up to 256) threads issue trips * 8 independent loads of
  * req_bytes (4, 8 or 16) at uniformly random entries of `table` (n_bytes) and write one checksum each to sink
