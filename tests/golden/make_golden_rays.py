@@ -14,6 +14,7 @@ import torch
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, '/root/reference')
 sys.path.insert(0, os.path.join(ROOT, 'tests'))
+sys.path.insert(1, ROOT)
 p3d = types.ModuleType('pytorch3d'); tr = types.ModuleType('pytorch3d.transforms')
 rc = types.ModuleType('pytorch3d.transforms.rotation_conversions')
 for name in ('axis_angle_to_matrix', 'matrix_to_axis_angle', 'matrix_to_rotation_6d', 'rotation_6d_to_matrix'):
