@@ -93,6 +93,9 @@ _SIGS = {
     'arcb200_nerf_mlp_fwd': [I, I, I, I, I, I, I, P, P, P, P, P, L, P, P, L, P],
     'arcb200_nerf_mlp_bwd': [I, I, I, I, I, I, I, P, P, P, P, P, P, F, P, P, L, P, L, P],
     'arcb200_gen_rays': [P, I, P, P, I, I, I, I, I, P, P, P, L, P],
+    'arcb200_gemm_nt': [P, L, P, L, P, P, L, L, I, I, P],
+    'arcb200_gemm_tn': [P, L, P, L, P, L, L, I, I, P],
+    'arcb200_softplus': [P, F, I, P, L, P],
     'arcb200_field_fwd': [P, P, I, I, P, P, P, P, P, P, P, I, P, P, P, P, P, P, P, L, P, P],
 }
 _RESTYPE = {

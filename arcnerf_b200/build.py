@@ -36,6 +36,7 @@ SOURCES = {
     'probe.cu': [],
     'dense_chain.cu': [],
     'raygen.cu': ['-fmad=false'],
+    'small_gemm.cu': [],
 }
 
 

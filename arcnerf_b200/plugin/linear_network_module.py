@@ -3,16 +3,18 @@
 GeoNet (:17-197) and RadianceNet (:234-335) with the same constructor arguments, layer structure (`layers.{i}.weight /
 bias`, so reference checkpoints load) and forward contracts.
 
-This is the one configuration of the reference that is a chain of plain 256-wide dense layers; the layers stay
-`torch.nn.Linear` (cuBLAS: library GEMMs, not a kernel of this library).  What comes from libarcb200 is the encoding in
-front of them (plugin/freq_encoder.py, or the hash grid / SH encoders selected by the encoder cfg) and everything around
-the networks (sampling, compositing).  Siren layers are not mirrored."""
+Every dense layer here runs on the library's own fp32 kernels (plugin/small_ops.py -> csrc/small_gemm.cu: no torch.nn.Linear,
+no cuBLAS) and is differentiable to second order, which is what the SDF models need (normals by forward_with_grad, eikonal
+loss).  These general mirrors serve the narrow networks (the 64-wide, weight-normed softplus SDF net of the NeuS-NGP
+configuration) and any shape of the classes; the 8 x 256 vanilla-NeRF / NeRF++ pair has its own tensor-core path,
+plugin/nerf_mlp.py FusedNeRFNets (csrc/dense_chain.cu), which loads the same state dicts.  Siren layers are not mirrored."""
 import math
 
 import numpy as np
 import torch
 import torch.nn as nn
 
+from . import small_ops
 from .registry import ENCODER_REGISTRY, MODULE_REGISTRY, cfg_to_dict
 
 
@@ -21,9 +23,9 @@ def get_activation(cfg=None, default='relu'):
     d = cfg_to_dict(cfg)
     t = (d.get('type') or default).lower()
     if t == 'relu':
-        return nn.ReLU(inplace=True)
+        return nn.ReLU()
     if t == 'softplus':
-        return nn.Softplus(beta=d.get('beta', 100))
+        return _Softplus(beta=d.get('beta', 100))
     if t == 'sigmoid':
         return nn.Sigmoid()
     if t == 'leakyrelu':
@@ -41,12 +43,31 @@ def build_encoder(cfg):
     return enc, d.get('input_dim', 3), d.get('n_freqs', 0)
 
 
-class DenseLayer(nn.Linear):
+class _Softplus(nn.Module):
+    """nn.Softplus(beta) on the library's kernel (differentiable twice)"""
+
+    def __init__(self, beta=100):
+        super().__init__()
+        self.beta = float(beta)
+
+    def forward(self, x):
+        return small_ops.softplus(x, self.beta)
+
+
+class Linear(nn.Linear):
+    """nn.Linear's parameters (weight (out,in), bias; so that the reference's state dicts load and nn.utils.weight_norm wraps it)
+    with the product on arcb200_gemm_nt"""
+
+    def forward(self, x):
+        return small_ops.linear(x, self.weight, self.bias)
+
+
+class DenseLayer(Linear):
     """Linear + activation (base_modules/linear.py)"""
 
     def __init__(self, input_dim, out_dim, activation=None, *args, **kwargs):
         super().__init__(input_dim, out_dim, *args, **kwargs)
-        self.activation = nn.ReLU(inplace=True) if activation is None else activation
+        self.activation = nn.ReLU() if activation is None else activation
 
     def forward(self, x):
         return self.activation(super().forward(x))
@@ -79,7 +100,7 @@ class GeoNet(nn.Module):
             else:
                 out_dim = W
             layer = DenseLayer(in_dim, out_dim, activation=get_activation(act_cfg), bias=use_bias) if i != D \
-                else nn.Linear(in_dim, out_dim, bias=use_bias)
+                else Linear(in_dim, out_dim, bias=use_bias)
             if geometric_init:                                    # linear_network_module.py:134-157
                 if i == D:
                     nn.init.normal_(layer.weight, mean=np.sqrt(np.pi) / np.sqrt(in_dim), std=0.0001)

@@ -483,6 +483,18 @@ int arcb200_nerf_mlp_bwd(int d_x, int n_freq_x, int n_freq_v, int W, int D, int 
 int arcb200_gen_rays(const float *cams, int n_cams, const int32_t *cam_id, const int64_t *pix, int W, int H, int wh_order,
                      int center_pixel, int normalize, float *rays_o, float *rays_d, float *rays_r, int64_t n, void *stream);
 
+/* ---- narrow dense layers in fp32 (csrc/small_gemm.cu) -------------------------------------------------------------------
+ * The SDF network of the NeuS-NGP configuration (32 -> 64 softplus(100) -> 17, weight-normed, GeoNet of
+ * geo_rad_model/linear_network_module.py:17-197 with DenseLayer = nn.Linear + activation, base_modules/linear.py) and the
+ * derivative passes autograd builds for forward_with_grad and the eikonal loss (base_network.py:30-44).
+ * arcb200_gemm_nt: C (n x N) = A (n x K) . B^T (+ bias), B (N x K), N, K <= 128.   arcb200_gemm_tn: C (N x K) += A^T . B with
+ * A (n x N), B (n x K), N * K <= 4096 (caller zeroes C).   arcb200_softplus: order-th derivative (0, 1, 2) of softplus_beta. */
+int arcb200_gemm_nt(const float *A, int64_t lda, const float *B, int64_t ldb, const float *bias, float *C, int64_t ldc, int64_t n,
+                    int N, int K, void *stream);
+int arcb200_gemm_tn(const float *A, int64_t lda, const float *B, int64_t ldb, float *C, int64_t ldc, int64_t n, int N, int K,
+                    void *stream);
+int arcb200_softplus(const float *x, float beta, int order, float *y, int64_t n, void *stream);
+
 /* ---- measurement aid (csrc/probe.cu) ---------------------------------------------------------------------------------
  * Random-gather bandwidth of a device table: n_threads (rounded up to 256) threads issue trips * 8 independent loads of
  * req_bytes (4, 8 or 16) at uniformly random entries of `table` (n_bytes) and write one checksum each to sink

@@ -58,6 +58,23 @@ def main():
         out['geo2_sd/%s' % k] = v.numpy()
     sdf, f2, grad = geo2.forward_with_grad(x.clone())
     out.update(sdf=sdf.detach().numpy(), feat2=f2.detach().numpy(), sdf_grad=grad.detach().numpy())
+    # the SDF network of the NeuS-NGP configuration (nerf_lego_neus_ngp.yaml geometry: W 64, D 1, no bias, weight norm, softplus 100,
+    # geometric init) on a 32-dim input standing in for the hash-grid features, with the second-order pass of the eikonal loss
+    torch.manual_seed(3)
+    geo3 = GeoNet(W=64, D=1, skips=[], encoder=dict_to_obj(dict(type='FreqEmbedder', input_dim=32, n_freqs=0)), W_feat=16, use_bias=False,
+                  geometric_init=True, radius_init=0.5, weight_norm=True, skip_reduce_output=True, norm_skip=True,
+                  act_cfg=dict_to_obj(dict(type='Softplus', beta=100)))
+    for k, v in geo3.state_dict().items():
+        out['geo3_sd/%s' % k] = v.numpy()
+    x3 = torch.randn((300, 32)) * 0.3
+    w1, w2, w3 = torch.randn((300, 1)), torch.randn((300, 16)), torch.randn((300, 32))
+    sdf3, feat3, grad3 = geo3.forward_with_grad(x3.clone())
+    loss = ((grad3.norm(dim=-1) - 1.0) ** 2).mean() + (sdf3 * w1).sum() + (feat3 * w2).sum() + (grad3 * w3).sum()
+    loss.backward()
+    out.update(x3=x3.numpy(), w1_3=w1.numpy(), w2_3=w2.numpy(), w3_3=w3.numpy(), sdf3=sdf3.detach().numpy(), feat3=feat3.detach().numpy(),
+               grad3=grad3.detach().numpy(), loss3=np.array(float(loss)))
+    for k, p in geo3.named_parameters():
+        out['geo3_grad/%s' % k] = p.grad.numpy()
     np.savez_compressed(os.path.join(ROOT, 'tests', 'golden', 'nerf_golden.npz'), **out)
     print('wrote nerf_golden.npz with', len(out), 'arrays')
 
