@@ -25,12 +25,43 @@ class _FreqFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         (xc, ) = ctx.saved_tensors
-        freqs_c, n_freqs, include_input, out_dim = ctx.args
+        return _FreqBwdFn.apply(g, xc, ctx.args), None, None, None, None
+
+
+class _FreqBwdFn(torch.autograd.Function):
+    """The input gradient as a function of (g, x) that can be differentiated again: the normals of an SDF network behind a
+    frequency embedding enter the eikonal loss, whose backward needs d(g_x)/d(g) and d(g_x)/d(x)."""
+
+    @staticmethod
+    def forward(ctx, g, xc, args):
+        freqs_c, n_freqs, include_input, out_dim = args
         gc = g.contiguous().float()
         gx = torch.empty_like(xc)
         _lib.call('arcb200_freq_embed_bwd', xc.data_ptr(), xc.shape[1], freqs_c, n_freqs, int(include_input), gc.data_ptr(),
                   out_dim, gx.data_ptr(), xc.shape[0], _lib.current_stream())
-        return gx, None, None, None, None
+        ctx.save_for_backward(gc, xc)
+        ctx.args = args
+        return gx
+
+    @staticmethod
+    def backward(ctx, v):
+        """g_x = g_0 + sum_k f_k (cos(x f_k) g_sin,k - sin(x f_k) g_cos,k): linear in g (Jacobian of the embedding applied to v)
+        and a second derivative in x.  Second-order passes are rare and small: elementwise torch expressions."""
+        gc, xc = ctx.saved_tensors
+        freqs_c, n_freqs, include_input, out_dim = ctx.args
+        d = xc.shape[1]
+        parts, dx = [], torch.zeros_like(xc)
+        col = 0
+        if include_input:
+            parts.append(v)
+            col = d
+        for k in range(n_freqs):
+            f = float(freqs_c[k])
+            s, c = torch.sin(xc * f), torch.cos(xc * f)
+            parts += [v * f * c, -v * f * s]
+            dx = dx + v * (f * f) * (-s * gc[:, col:col + d] - c * gc[:, col + d:col + 2 * d])
+            col += 2 * d
+        return torch.cat(parts, 1), dx, None
 
 
 @ENCODER_REGISTRY.register()
