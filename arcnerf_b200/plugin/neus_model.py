@@ -1,0 +1,218 @@
+# -*- coding: utf-8 -*-
+"""NeuS foreground model on libarcb200 (BASELINE.json configs[2], the NeuS-NGP configuration
+configs/expr/NeRF/lego/nerf_lego_neus_ngp.yaml): the reference's `Neus(SdfModel(FgModel))` -
+arcnerf/models/neus_model.py:19-265, sdf_model.py:42-114, fg_model.py:153-387 - with the same cfg fields, forward
+arguments and output keys (rgb, depth, mask, normal, normal_pts, params, progress_*).
+
+Per forward: occupancy-volume sampling (VolumeBound -> arcb200 ray-AABB + march kernels), `handle_mid_pts`, the SDF network
+with normals (`geo_net.forward_with_grad`: hash grid with dy/dx + the 64-wide weight-normed softplus net on arcb200_gemm_nt),
+the 'pvnf' radiance head (tcgen05 fused MLP, 38 inputs padded to 48 with ones), slope and cosine annealing, `sdf_to_alpha`
+with the learnable scale s = exp(10 inv_s) (csrc/composite.cu), compositing from alpha, normal map.  The training backward
+runs through the library's backward kernels, including the second-order pass the eikonal loss on `normal_pts` needs
+(arcb200_grid_bwd_bwd_input, the twice-differentiable small-GEMM functions).
+
+What stays in eager torch, as in the reference: the boolean-mask bookkeeping between padded (rays, points) matrices and the
+list of valid points (fg_model.py:188-229, sdf_model.py:61-101), and elementwise glue (slope dot product, annealing, normal
+normalisation, weight-norm re-parametrisation of 5 k parameters)."""
+import math
+
+import numpy as np
+import torch
+import torch.nn as nn
+import torch.nn.functional as tnf
+
+from . import ray_helper as rh
+from .linear_network_module import GeoNet
+from .obj_bound import VolumeBound
+from .registry import MODEL_REGISTRY, MODULE_REGISTRY, cfg_to_dict
+from .tcnn_fusedmlp_module import FusedMLPRadianceNet  # noqa: F401  (registers the module)
+
+
+def _get(d, key, default=None):
+    v = d.get(key, default)
+    return default if v is None else v
+
+
+def _build(cfg, default_type):
+    d = cfg_to_dict(cfg)
+    cls = MODULE_REGISTRY.get(d.get('type') or default_type)
+    return cls(**{k: v for k, v in d.items() if k != 'type'})
+
+
+@MODEL_REGISTRY.register()
+class Neus(nn.Module):
+    """cfgs: the `model` section of nerf_lego_neus_ngp.yaml (obj_bound / rays / params / chunk_* / geometry / radiance)"""
+
+    def __init__(self, cfgs, device='cuda:0'):
+        super().__init__()
+        c = cfg_to_dict(cfgs)
+        rays, params, bound = cfg_to_dict(c.get('rays')), cfg_to_dict(c.get('params')), cfg_to_dict(c.get('obj_bound'))
+        self.ray_cfgs = dict(n_sample=_get(rays, 'n_sample', 128), n_importance=_get(rays, 'n_importance', 0), n_iter=_get(rays, 'n_iter', 4),
+                             inverse_linear=_get(rays, 'inverse_linear', False), perturb=_get(rays, 'perturb', False),
+                             add_inf_z=_get(rays, 'add_inf_z', False), noise_std=_get(rays, 'noise_std', 0.0),
+                             white_bkg=_get(rays, 'white_bkg', False), radius_bound=_get(rays, 'radius_bound', 1.5))
+        assert self.ray_cfgs['n_importance'] == 0, 'Neus.upsample_zvals (n_importance > 0) is not provided'
+        assert not self.ray_cfgs['add_inf_z'], 'Do not add_inf_z for sdf modeling'          # neus_model.py: the sdf models assert the same
+        self.render_cfgs = dict(bkg_color=_get(bound, 'bkg_color', [1.0, 1.0, 1.0]), depth_far=_get(bound, 'depth_far', 10.0),
+                                normal=_get(bound, 'normal', [0.0, 1.0, 0.0]))
+        self.chunk_rays, self.chunk_pts = _get(c, 'chunk_rays', 32768), _get(c, 'chunk_pts', 1 << 20)
+        self.geo_net = _build(c.get('geometry'), 'GeoNet')
+        self.radiance_net = _build(c.get('radiance'), 'RadianceNet')
+        self.speed_factor = _get(params, 'speed_factor', 10)
+        self.inv_s = nn.Parameter(torch.tensor([-np.log(_get(params, 'init_var', 0.05)) / self.speed_factor], dtype=torch.float32))
+        self.anneal_end = _get(params, 'anneal_end', 0)
+        self.obj_bound = VolumeBound(bound)
+        self.to(device)
+
+    # ------------------------------------------------------------------------------------------ small accessors
+    def get_ray_cfgs(self, key=None):
+        return self.ray_cfgs if key is None else self.ray_cfgs[key]
+
+    def get_chunk_rays(self):
+        return self.chunk_rays
+
+    def forward_scale(self):
+        """scale = exp(inv_s * speed)   (neus_model.py:52-54)"""
+        return torch.exp(self.inv_s * self.speed_factor)
+
+    def get_cos_anneal(self, cur_epoch):
+        return 1.0 if self.anneal_end == 0 else min(1.0, cur_epoch / self.anneal_end)
+
+    # ------------------------------------------------------------------------------------------ FgModel.forward
+    def forward(self, inputs, inference_only=False, get_progress=False, cur_epoch=0, total_epoch=300000):
+        rays_o, rays_d = inputs['rays_o'].float().contiguous(), inputs['rays_d'].float().contiguous()
+        bkg_color = inputs.get('bkg_color')
+        n_rays = rays_o.shape[0]
+        with torch.no_grad():
+            near, far, mask_rays = self.obj_bound.get_near_far_from_rays({'rays_o': rays_o, 'rays_d': rays_d})
+            zvals, mask_pts = self.obj_bound.get_zvals_from_near_far(near, far, self.ray_cfgs['n_sample'], inference_only,
+                                                                     rays_o=rays_o, rays_d=rays_d)
+            max_num_pts = max(2, int(mask_pts.sum(dim=1).max()))                       # reduce_empty_mask (fg_model.py:251-262)
+            zvals, mask_pts = zvals[:, :max_num_pts].contiguous(), mask_pts[:, :max_num_pts].contiguous()
+            mask_rays = torch.logical_and(mask_rays, torch.any(mask_pts, dim=1))
+        if bool(torch.all(mask_rays)):
+            return self._forward(rays_o, rays_d, zvals, mask_pts, bkg_color, inference_only, get_progress, cur_epoch)
+        empty_batch = int(mask_rays.sum()) == 0
+        if empty_batch:                                   # all rays miss: one synthetic ray gives the output keys (fg_model.py:198-207)
+            mask_rays = mask_rays.clone()
+            mask_rays[0] = True
+            z_valid = torch.zeros((1, zvals.shape[1]), dtype=zvals.dtype, device=zvals.device)
+            z_valid[0, 1:] = 1.0
+            m_valid = torch.zeros((1, mask_pts.shape[1]), dtype=torch.bool, device=zvals.device)
+            m_valid[0, :2] = True
+        else:
+            z_valid, m_valid = zvals[mask_rays], mask_pts[mask_rays]
+        out_valid = self._forward(rays_o[mask_rays], rays_d[mask_rays], z_valid, m_valid,
+                                  bkg_color[mask_rays] if bkg_color is not None else None, inference_only, get_progress, cur_epoch)
+        if empty_batch:
+            mask_rays[0] = False
+        return self.update_values_for_invalid_rays(out_valid, mask_rays, bkg_color, n_rays)
+
+    def update_values_for_invalid_rays(self, out_valid, mask, rand_bkg_color, n_rays):
+        """fg_model.py:320-387: background colour / far depth / zero mask / default normal for the rays that miss the bound"""
+        out = {}
+        n_valid = int(mask.sum())
+        for k, v in out_valid.items():
+            if not torch.is_tensor(v):
+                out[k] = v
+                continue
+            shape = (n_rays, *v.shape[1:])
+            kw = dict(dtype=v.dtype, device=v.device)
+            if k.startswith('rgb'):
+                fill = rand_bkg_color if rand_bkg_color is not None else torch.tensor(self.render_cfgs['bkg_color'], **kw)[None]
+                t = torch.ones(shape, **kw) * fill
+            elif k.startswith('depth'):
+                t = torch.ones(shape, **kw) * self.render_cfgs['depth_far']
+            elif k.startswith('mask'):
+                t = torch.zeros(shape, **kw)
+            elif k.startswith('normal'):
+                nrm = tnf.normalize(torch.tensor(self.render_cfgs['normal'], **kw)[None], dim=-1)
+                t = torch.ones(shape, **kw) * (nrm[None] if k == 'normal_pts' else nrm)
+            elif k.startswith('progress'):
+                t = -torch.ones(shape, **kw) if 'sigma' in k else (torch.ones(shape, **kw) if 'trans_shift' in k else torch.zeros(shape, **kw))
+            else:
+                out[k] = v
+                continue
+            if n_valid:
+                t[mask] = v[:n_valid]
+            out[k] = t
+        return out
+
+    # ------------------------------------------------------------------------------------------ Neus._forward
+    def handle_mid_pts(self, zvals, mask_pts):
+        """neus_model.py:173-202 (the masked branch): interval mid points, one extra interval of the ray's step appended"""
+        sample_dist = (zvals[:, -1] - zvals[:, 0]) / self.ray_cfgs['n_sample'] * 0.5
+        final_zvals = zvals[:, -1] + sample_dist * 2.0
+        _zvals = torch.ones((zvals.shape[0], zvals.shape[1] + 1), dtype=zvals.dtype, device=zvals.device) * final_zvals.unsqueeze(1)
+        _mask = torch.cat([mask_pts, torch.zeros_like(mask_pts[:, :1])], dim=1)
+        _zvals[_mask] = zvals[mask_pts]
+        mid_zvals = 0.5 * (_zvals[..., 1:] + _zvals[..., :-1])
+        mask_mid = torch.cat([torch.ones_like(mask_pts[:, :1]), mask_pts[:, :-1]], dim=1)
+        return mid_zvals, _zvals, mask_mid
+
+    def get_sdf_radiance_normal_by_mask_pts(self, rays_o, rays_d, zvals, mask_pts):
+        """sdf_model.py:42-114: networks on the valid points only, results re-expanded with the ray's last valid value"""
+        n_rays, n_pts = zvals.shape
+        pts = rh.get_ray_points_by_zvals(rays_o, rays_d, zvals)
+        dirs = rays_d[:, None, :].expand(n_rays, n_pts, 3)
+        pts_v, dirs_v = pts[mask_pts].view(-1, 3), dirs[mask_pts].reshape(-1, 3)
+        sdf_v, rad_v, nrm_v = self._forward_pts_dir(pts_v, dirs_v)
+        last = torch.cumsum(mask_pts.sum(dim=1), dim=0) - 1
+        sdf = (torch.ones((n_rays, n_pts), dtype=sdf_v.dtype, device=sdf_v.device) * sdf_v[last].unsqueeze(1)).clone()
+        rad = (torch.ones((n_rays, n_pts, 3), dtype=sdf_v.dtype, device=sdf_v.device) * rad_v[last].unsqueeze(1)).clone()
+        nrm = (torch.ones((n_rays, n_pts, 3), dtype=sdf_v.dtype, device=sdf_v.device) * nrm_v[last].unsqueeze(1)).clone()
+        sdf[mask_pts], rad[mask_pts], nrm[mask_pts] = sdf_v, rad_v, nrm_v
+        return sdf, rad, nrm
+
+    def _forward_pts_dir(self, pts, rays_d):
+        """sdf_model.py:104-114: sdf (N,), radiance (N,3), normal (N,3) = d sdf / d pts kept in the graph"""
+        sdf, feat, normal = self.geo_net.forward_with_grad(pts)
+        radiance = self.radiance_net(pts, rays_d, normal, feat)
+        return sdf[..., 0], radiance, normal
+
+    def _forward(self, rays_o, rays_d, zvals, mask_pts, bkg_color, inference_only, get_progress, cur_epoch):
+        mid_zvals, zvals, mask_mid = self.handle_mid_pts(zvals, mask_pts)
+        sdf, radiance, normal_pts = self.get_sdf_radiance_normal_by_mask_pts(rays_o, rays_d, mid_zvals, mask_mid)
+        cos_anneal = 1.0 if inference_only else self.get_cos_anneal(cur_epoch)
+        slope = torch.sum(rays_d[:, None, :] * normal_pts, dim=-1)
+        iter_slope = -(tnf.relu(-slope * 0.5 + 0.5) * (1 - cos_anneal) + tnf.relu(-slope) * cos_anneal)
+        alpha = rh.sdf_to_alpha(sdf.contiguous(), zvals.contiguous(), iter_slope.contiguous(), self.forward_scale())
+        out = rh.ray_marching(sdf, radiance.contiguous(), mid_zvals.contiguous(), False, 0.0, white_bkg=self.ray_cfgs['white_bkg'],
+                              alpha=alpha, bkg_color=bkg_color)
+        output = {k: out[k] for k in ('rgb', 'depth', 'mask')}
+        output['normal'] = torch.sum(out['weights'].unsqueeze(-1) * tnf.normalize(normal_pts, dim=-1), -2)
+        if not inference_only:
+            output['params'] = {'scale': float(self.forward_scale().detach())}
+            output['normal_pts'] = normal_pts
+        if get_progress:
+            for k in ('sigma', 'zvals', 'alpha', 'trans_shift', 'weights'):
+                if out.get(k) is not None:
+                    output['progress_' + k] = out[k].detach()
+        return output
+
+    # ------------------------------------------------------------------------------------------ occupancy refresh
+    @torch.no_grad()
+    def _geo_with_normal(self, pts):
+        with torch.enable_grad():
+            sdf, _, normal = self.geo_net.forward_with_grad(pts.clone())
+        return sdf.detach(), normal.detach()
+
+    def get_est_opacity(self, dt, pts):
+        """neus_model.py:204-219: opacity of a fake ray pointing at the origin through every sampled voxel point"""
+        n = pts.shape[0]
+        rays_d = -tnf.normalize(pts, dim=-1)
+        sdf, normal = self._geo_with_normal(pts)
+        slope = torch.sum(rays_d * normal, dim=-1, keepdim=True)
+        zvals = torch.zeros((n, 2), dtype=pts.dtype, device=pts.device)
+        zvals[:, 1] += dt * 1.0 / math.sqrt(3)
+        with torch.no_grad():
+            return rh.sdf_to_alpha(sdf.contiguous(), zvals, (-tnf.relu(-slope)).contiguous(), self.forward_scale().detach())[:, 0]
+
+    def optimize(self, cur_epoch=0):
+        """FgModel.optimize (fg_model.py:400-410): refresh the occupancy volume from the current SDF"""
+        self.obj_bound.optimize(cur_epoch, self.ray_cfgs['n_sample'], self.get_est_opacity)
+
+
+def eikonal_loss(normal_pts):
+    """EikonalLoss (arcnerf/loss/geo_loss.py:12-73, key normal_pts): mean (|grad sdf| - 1)^2 over all points"""
+    return ((torch.norm(normal_pts, dim=-1) - 1.0) ** 2).mean()
