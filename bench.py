@@ -195,7 +195,7 @@ def main():
     ap.add_argument('--occ-every', type=int, default=16, help='occupancy refresh period in steps (0 = never); the reference config uses 16')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--stages', action='store_true', help='print the per-stage timing table to stderr')
-    ap.add_argument('--config', default='ngp', choices=['ngp', 'nerf'], help="ngp: BASELINE configs[1] (the headline); nerf: the vanilla-NeRF step of configs[0] (bench_nerf.py)")
+    ap.add_argument('--config', default='ngp', choices=['ngp', 'nerf', 'neus'], help="ngp: BASELINE configs[1] (the headline); nerf: the vanilla-NeRF step of configs[0] (bench_nerf.py); neus: the NeuS-NGP step of configs[2] (bench_neus.py)")
     args = ap.parse_args()
 
     rank = int(os.environ.get('RANK', 0))
@@ -207,6 +207,10 @@ def main():
             if rank == 0:
                 import bench_nerf
                 bench_nerf.run_reference(args)
+            return
+        if args.config == 'neus':
+            if rank == 0:
+                print(json.dumps(dict(impl='reference', unavailable='NeuS-NGP needs tinycudann on a GPU in the reference; no CPU implementation of this configuration exists')))
             return
         run_reference_arm(args, rank, world)
         return
@@ -222,9 +226,9 @@ def main():
         torch.cuda.set_device(0)
     dev = torch.device('cuda', local_rank if world > 1 else 0)
 
-    if args.config == 'nerf':
-        import bench_nerf
-        bench_nerf.run(args, rank, world, dev, dist, read_peaks, ClockSampler)
+    if args.config in ('nerf', 'neus'):
+        mod = __import__('bench_' + args.config)
+        mod.run(args, rank, world, dev, dist, read_peaks, ClockSampler)
         if dist is not None:
             dist.barrier()
             dist.destroy_process_group()
