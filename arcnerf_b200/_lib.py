@@ -93,6 +93,10 @@ _SIGS = {
     'arcb200_nerf_mlp_fwd': [I, I, I, I, I, I, I, P, P, P, P, P, L, P, P, L, P],
     'arcb200_nerf_mlp_bwd': [I, I, I, I, I, I, I, P, P, P, P, P, P, F, P, P, L, P, L, P],
     'arcb200_gen_rays': [P, I, P, P, I, I, I, I, I, P, P, P, L, P],
+    'arcb200_volume_pts': [P, P, I, I, I, P, P],
+    'arcb200_mc_scratch_sizes': [I, I, I, P],
+    'arcb200_mc_count': [P, I, I, I, F, I, P, P, P],
+    'arcb200_mc_emit': [P, I, I, I, F, I, P, P, P, P, P, P, P, L, P, L, P],
     'arcb200_gemm_nt': [P, L, P, L, P, P, L, L, I, I, P],
     'arcb200_gemm_tn': [P, L, P, L, P, L, L, I, I, P],
     'arcb200_softplus': [P, F, I, P, L, P],

@@ -37,6 +37,7 @@ SOURCES = {
     'dense_chain.cu': [],
     'raygen.cu': ['-fmad=false'],
     'small_gemm.cu': [],
+    'mcubes.cu': ['-fmad=false'],
 }
 
 

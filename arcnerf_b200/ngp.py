@@ -290,16 +290,39 @@ class NGPPipeline:
         """Density at the voxel centres of an n_grid^3 lattice over the bounding box (the grid a mesh extraction runs
         marching cubes on: Volume.get_volume_pts -> forward_pts, base_3d_model.py:343-366), for x slabs
         [x_range[0], x_range[1]) -> (nx, n_grid, n_grid) fp32.  Ranks take disjoint slabs (dist.shard_range) and gather."""
+        from .plugin.mesh import volume_pts
         x0, x1 = x_range if x_range is not None else (0, n_grid)
         out = torch.empty((x1 - x0, n_grid, n_grid), dtype=torch.float32, device=self.dev)
-        lo, side = self.aabb[0], self.aabb[1] - self.aabb[0]
-        vs = side / n_grid
-        ax = [lo[a] + (torch.arange(n_grid, device=self.dev, dtype=torch.float32) + 0.5) * vs[a] for a in range(3)]
+        lo, hi = self.aabb[0].tolist(), self.aabb[1].tolist()
+        pts = torch.empty((min(slab, max(1, x1 - x0)) * n_grid * n_grid, 3), dtype=torch.float32, device=self.dev)
         for a in range(x0, x1, slab):
             b = min(x1, a + slab)
-            pts = torch.stack(torch.meshgrid(ax[0][a:b], ax[1], ax[2], indexing='ij'), -1).reshape(-1, 3)
-            out[a - x0:b - x0] = self.forward_pts(pts).view(b - a, n_grid, n_grid)
+            # voxel centres of the slab generated in place (csrc/mcubes.cu), the same values as Volume.get_volume_pts()
+            p = volume_pts(lo, hi, n_grid, a, b, out=pts)
+            out[a - x0:b - x0] = self.forward_pts(p).view(b - a, n_grid, n_grid)
         return out
+
+    def extract_mesh(self, n_grid, level=50.0, grad_dir='descent', slab=16, x_range=None, return_grid=False):
+        """run_infer_volume (arcnerf/eval/infer_func.py:448-500): density on the n_grid^3 lattice, then marching cubes
+        (plugin/mesh.py) -> verts, faces, vertex normals as device tensors in world coordinates.
+        x_range = (x0, x1): the cells of x slabs [x0, x1) only (a rank's shard, dist.shard_range); the slab reads lattice planes
+        x0..x1, so neighbouring shards evaluate one plane twice and need no exchange."""
+        from .plugin.mesh import extract_mesh
+        x0, x1 = x_range if x_range is not None else (0, n_grid)
+        sigma = self.density_grid(n_grid, x_range=(x0, min(n_grid, x1 + 1)), slab=slab)
+        side = (self.aabb[1] - self.aabb[0]).tolist()
+        lo = self.aabb[0].tolist()
+        vs = [s / n_grid for s in side]
+        if sigma.shape[0] < 2:
+            verts = torch.zeros((0, 3), dtype=torch.float32, device=self.dev)
+            faces, normals = torch.zeros((0, 3), dtype=torch.int32, device=self.dev), verts.clone()
+        else:
+            verts, faces, normals = extract_mesh(sigma, level, vs, side, grad_dir)
+            # extract_mesh centres the volume at the origin; the reference adds volume_origin afterwards (infer_func.py:545-552)
+            shift = torch.tensor([lo[0] + side[0] / 2 + x0 * vs[0], lo[1] + side[1] / 2, lo[2] + side[2] / 2],
+                                 dtype=torch.float32, device=self.dev)
+            verts = verts + shift
+        return (verts, faces, normals, sigma) if return_grid else (verts, faces, normals)
 
     @torch.no_grad()
     def get_est_opacity(self, dt, pts):

@@ -31,7 +31,10 @@ class _RenderFn(torch.autograd.Function):
         rgb, depth, mask = pipe.forward(rays_o, rays_d, bkg)
         ctx.model, ctx.R, ctx.bkg, ctx.rays_d = model, R, bkg, rays_d
         ctx.set_key = pipe.forward_serial            # counts every sample() of the pipeline: two alternating sets would alias
-        return rgb.clone(), depth.clone(), mask.clone(), pipe.counts[:R].clone()
+        mask = mask.clone()
+        # a background MODEL behind this foreground (FullModel: bkg is its colour per ray) receives d rgb / d bkg = T_last
+        ctx.trans_last = (1.0 - mask) if bkg.requires_grad else None
+        return rgb.clone(), depth.clone(), mask, pipe.counts[:R].clone()
 
     @staticmethod
     def backward(ctx, g_rgb, g_depth, g_mask, _g_counts):
@@ -47,7 +50,12 @@ class _RenderFn(torch.autograd.Function):
         gd = g_depth.contiguous().float() if g_depth is not None else None
         gm = g_mask.contiguous().float() if g_mask is not None else None
         pipe.backward(ctx.rays_d, R, ctx.bkg, composite=True, g_depth=gd, g_mask=gm)
-        return None, None, None, None, pipe.g_table.clone(), pipe.g_geo.clone(), pipe.g_rad.clone()
+        g_bkg = None
+        if ctx.trans_last is not None and g_rgb is not None:
+            g_bkg = g_rgb * ctx.trans_last[:, None]
+            if ctx.bkg.shape[0] == 1:
+                g_bkg = g_bkg.sum(0, keepdim=True)
+        return None, None, None, g_bkg, pipe.g_table.clone(), pipe.g_geo.clone(), pipe.g_rad.clone()
 
 
 class NGPFgModel(nn.Module):
@@ -103,6 +111,11 @@ class NGPFgModel(nn.Module):
             self._versions = now
 
     # ------------------------------------------------------------------ the reference's model surface
+    blends_bkg_in_compositor = True      # FullModel: a background model's colour goes in as the per-ray bkg_color
+
+    def get_chunk_rays(self):
+        return min(self.chunk_rays, self.pipe.max_rays)
+
     def get_n_coarse_sample(self):
         return self.pipe.cfg['n_sample']
 
@@ -138,7 +151,8 @@ class NGPFgModel(nn.Module):
         bkg = inputs.get('bkg_color', None)
         if bkg is None:
             bkg = torch.tensor([self.bkg_color], dtype=torch.float32, device=self.pipe.dev)
-        bkg = bkg.to(self.pipe.dev, torch.float32).contiguous()
+        bkg = bkg.to(self.pipe.dev, torch.float32)
+        bkg = bkg if bkg.is_contiguous() else bkg.contiguous()
         n, chunk = rays_o.shape[0], self.pipe.max_rays
         grad = torch.is_grad_enabled() and not inference_only
         was_training, self.pipe.training = self.pipe.training, bool(grad)

@@ -206,6 +206,8 @@ class FullModel(nn.Module):
         return out
 
     def process_fg_bkg_model(self, flat_inputs, inference_only, get_progress, cur_epoch, total_epoch):
+        if self.bkg_model is not None and getattr(self.fg_model, 'blends_bkg_in_compositor', False):
+            return self._fg_over_bkg_fused(flat_inputs, inference_only, cur_epoch, total_epoch)
         get_progress_fg = True if self.bkg_model is not None else get_progress
         fg = self.fg_model(flat_inputs, inference_only, get_progress_fg, cur_epoch, total_epoch)
         if self.bkg_model is None:
@@ -214,6 +216,22 @@ class FullModel(nn.Module):
         out = self._blend(fg, bkg)
         if not get_progress:
             out = {k: v for k, v in out.items() if not k.startswith('progress_')}
+        return out
+
+    def _fg_over_bkg_fused(self, flat_inputs, inference_only, cur_epoch, total_epoch):
+        """The packed NGP foreground (plugin/fg_model.py) keeps no per-sample progress tensors; the same blend
+        rgb = rgb_fg + T_last * rgb_bkg (blend_bkg_rgb, full_model.py:310-330) is evaluated by its compositing kernel when the
+        background model's colour is handed in as the per-ray background colour.  T_last = 1 - mask (the weights sum to 1 - T).
+        The background model runs first; its gradient arrives through d rgb / d bkg = T_last."""
+        bkg = self.bkg_model(flat_inputs, inference_only, False, cur_epoch, total_epoch)
+        b_rgb = bkg.get('rgb_fine', bkg.get('rgb_coarse', bkg.get('rgb')))
+        b_depth = bkg.get('depth_fine', bkg.get('depth_coarse', bkg.get('depth')))
+        fg_in = dict(flat_inputs, bkg_color=b_rgb)
+        fg = self.fg_model(fg_in, inference_only, False, cur_epoch, total_epoch)
+        out = dict(fg)
+        for suffix in ('', '_coarse'):
+            if 'depth' + suffix in fg:
+                out['depth' + suffix] = fg['depth' + suffix] + (1.0 - fg['mask' + suffix]) * b_depth
         return out
 
     def forward(self, inputs, inference_only=False, get_progress=False, cur_epoch=0, total_epoch=300000):

@@ -195,7 +195,12 @@ def main():
     ap.add_argument('--occ-every', type=int, default=16, help='occupancy refresh period in steps (0 = never); the reference config uses 16')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--stages', action='store_true', help='print the per-stage timing table to stderr')
-    ap.add_argument('--config', default='ngp', choices=['ngp', 'nerf', 'neus'], help="ngp: BASELINE configs[1] (the headline); nerf: the vanilla-NeRF step of configs[0] (bench_nerf.py); neus: the NeuS-NGP step of configs[2] (bench_neus.py)")
+    ap.add_argument('--config', default='ngp', choices=['ngp', 'nerf', 'neus', 'ngp_nerfpp', 'mesh'],
+                    help="ngp: BASELINE configs[1] (the headline); nerf: the vanilla-NeRF step of configs[0] (bench_nerf.py); neus: the NeuS-NGP step "
+                         "of configs[2] (bench_neus.py); ngp_nerfpp: NGP foreground + NeRF++ background training of configs[3]; mesh: 1920x1080 "
+                         "frame + 512^3 mesh extraction of configs[4] (both bench_scene.py)")
+    ap.add_argument('--mesh-grid', type=int, default=512)
+    ap.add_argument('--mesh-slab', type=int, default=16)
     args = ap.parse_args()
 
     rank = int(os.environ.get('RANK', 0))
@@ -207,6 +212,11 @@ def main():
             if rank == 0:
                 import bench_nerf
                 bench_nerf.run_reference(args)
+            return
+        if args.config in ('ngp_nerfpp', 'mesh'):
+            if rank == 0:
+                print(json.dumps(dict(impl='reference', unavailable='the reference needs tinycudann and skimage (GPU / absent packages) for this configuration; '
+                                                                    'the CPU port of its parts is timed inside the ours line (cpu_baseline)')))
             return
         if args.config == 'neus':
             if rank == 0:
@@ -226,9 +236,13 @@ def main():
         torch.cuda.set_device(0)
     dev = torch.device('cuda', local_rank if world > 1 else 0)
 
-    if args.config in ('nerf', 'neus'):
-        mod = __import__('bench_' + args.config)
-        mod.run(args, rank, world, dev, dist, read_peaks, ClockSampler)
+    if args.config in ('nerf', 'neus', 'ngp_nerfpp', 'mesh'):
+        if args.config in ('ngp_nerfpp', 'mesh'):
+            import bench_scene
+            getattr(bench_scene, 'run_' + args.config)(args, rank, world, dev, dist, read_peaks, ClockSampler)
+        else:
+            mod = __import__('bench_' + args.config)
+            mod.run(args, rank, world, dev, dist, read_peaks, ClockSampler)
         if dist is not None:
             dist.barrier()
             dist.destroy_process_group()

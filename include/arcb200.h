@@ -483,6 +483,29 @@ int arcb200_nerf_mlp_bwd(int d_x, int n_freq_x, int n_freq_v, int W, int D, int 
 int arcb200_gen_rays(const float *cams, int n_cams, const int32_t *cam_id, const int64_t *pix, int W, int H, int wh_order,
                      int center_pixel, int normalize, float *rays_o, float *rays_d, float *rays_r, int64_t n, void *stream);
 
+/* ---- mesh extraction on the device (csrc/mcubes.cu) ---------------------------------------------------------------------
+ * arcb200_volume_pts: voxel-centre points of x slabs [x0, x1) of an n_grid^3 lattice over the box [lo, hi] (HOST float[3] each),
+ * pts ((x1 - x0) * n_grid^2, 3), x outermost - Volume.cal_volume_pts, arcnerf/geometry/volume.py:225-232 (symmetric linspace per
+ * axis), generated slab by slab so that the full lattice never has to be stored.
+ *
+ * Marching cubes over vol (nx, ny, nz) fp32, z fastest - extract_mesh, arcnerf/geometry/mesh.py:12-47 (which runs
+ * skimage.measure.marching_cubes on the host): ascent = 0 for grad_dir 'descent' (inside: value > level), 1 for 'ascent'.
+ *   1. arcb200_mc_scratch_sizes -> out[0..2] = int32 entries of point_blocks, cell_blocks, vbase;
+ *   2. arcb200_mc_count fills point_blocks / cell_blocks with exclusive block offsets; their LAST entries are the vertex and the
+ *      face count (read them back to size the outputs);
+ *   3. arcb200_mc_emit writes verts (V, 3) = index * spacing - offset (HOST float[3] each; extract_mesh's offset is
+ *      (volume_len - voxel_size) / 2), unit vertex normals (V, 3) pointing outside (NULL to skip) and faces (F, 3) int32 whose
+ *      winding has the normal pointing outside (what extract_mesh returns after its faces[:, ::-1]).
+ * Vertices are welded by construction (one per crossing lattice edge, in lattice order); the order of vertices and faces and the
+ * resolution of ambiguous cells follow this library's generated case table, not skimage's. */
+int arcb200_volume_pts(const float *lo, const float *hi, int n_grid, int x0, int x1, float *pts, void *stream);
+int arcb200_mc_scratch_sizes(int nx, int ny, int nz, int64_t *out);
+int arcb200_mc_count(const float *vol, int nx, int ny, int nz, float level, int ascent, int32_t *point_blocks,
+                     int32_t *cell_blocks, void *stream);
+int arcb200_mc_emit(const float *vol, int nx, int ny, int nz, float level, int ascent, const float *spacing, const float *offset,
+                    const int32_t *point_blocks, const int32_t *cell_blocks, int32_t *vbase, float *verts, float *normals,
+                    int64_t v_cap, int32_t *faces, int64_t f_cap, void *stream);
+
 /* ---- narrow dense layers in fp32 (csrc/small_gemm.cu) -------------------------------------------------------------------
  * The SDF network of the NeuS-NGP configuration (32 -> 64 softplus(100) -> 17, weight-normed, GeoNet of
  * geo_rad_model/linear_network_module.py:17-197 with DenseLayer = nn.Linear + activation, base_modules/linear.py) and the

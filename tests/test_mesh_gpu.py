@@ -1,0 +1,111 @@
+"""Mesh extraction: csrc/mcubes.cu against the numpy restatement oracle/marching_cubes.py bit for bit, and
+against closed-form surfaces.  skimage (the reference's marching cubes) is not in this image: see the oracle's header."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import marching_cubes as M
+from mesh_cases import blobs_volume, closed_and_oriented, sphere_volume
+
+pytestmark = pytest.mark.gpu
+GOLD = np.load(os.path.join(os.path.dirname(__file__), 'golden', 'volume_golden.npz'))
+
+
+def _same(a, b):
+    return a.shape == b.shape and np.array_equal(a.view(np.uint32) if a.dtype == np.float32 else a,
+                                                 b.view(np.uint32) if b.dtype == np.float32 else b)
+
+
+@pytest.mark.parametrize('grad_dir', ['descent', 'ascent'])
+@pytest.mark.parametrize('shape', [(40, 40, 40), (33, 21, 50), (2, 2, 2), (5, 2, 3)])
+def test_marching_cubes_equals_restatement(shape, grad_dir):
+    from arcnerf_b200.plugin.mesh import extract_mesh
+    vol, vs, vl, level = blobs_volume(shape, seed=sum(shape))
+    if grad_dir == 'ascent':
+        vol, level = -vol, -level
+    v, f, n = extract_mesh(vol, level, vs, vl, grad_dir)
+    rv, rf, rn = M.extract_mesh(vol, level, vs, vl, grad_dir)
+    assert _same(v, rv) and _same(f, rf)
+    assert n.shape == rn.shape and np.allclose(n, rn, atol=2e-6)            # fp32 sqrt / division sequence: last-bit agreement
+    if min(shape) > 2:
+        assert len(f) > 0
+
+
+def test_all_256_cases_give_a_closed_oriented_surface():
+    """white noise hits every sign configuration; padded with outside values the surface must be closed, every directed edge
+    matched by its reverse exactly once"""
+    from arcnerf_b200.plugin.mesh import extract_mesh
+    rng = np.random.default_rng(3)
+    vol = np.zeros((36, 36, 36), np.float32)
+    vol[2:-2, 2:-2, 2:-2] = rng.random((32, 32, 32), dtype=np.float32)
+    v, f, _ = extract_mesh(vol, 0.5, (1., 1., 1.), (36., 36., 36.))
+    rv, rf, _ = M.extract_mesh(vol, 0.5, (1., 1., 1.), (36., 36., 36.))
+    assert _same(v, rv) and _same(f, rf)
+    closed_and_oriented(v, f, manifold=False)
+
+
+def test_sphere_area_volume_normals():
+    from arcnerf_b200.plugin.mesh import extract_mesh
+    n, r = 96, 0.6
+    vol, vs, vl = sphere_volume(n, r)
+    v, f, nr = extract_mesh(torch.from_numpy(vol).cuda(), 50.0, vs, vl)
+    assert v.is_cuda and f.dtype == torch.int32
+    v, f, nr = v.cpu().numpy(), f.cpu().numpy(), nr.cpu().numpy()
+    closed_and_oriented(v, f)
+    d = np.linalg.norm(v, axis=1)
+    assert abs(d - r).max() < 2e-3
+    a, b, c = v[f[:, 0]], v[f[:, 1]], v[f[:, 2]]
+    cr = np.cross(b - a, c - a)
+    assert abs(0.5 * np.linalg.norm(cr, axis=1).sum() / (4 * np.pi * r * r) - 1) < 2e-3
+    assert abs((a * cr).sum() / 6 / (4 / 3 * np.pi * r ** 3) - 1) < 2e-3    # positive: faces wind outward
+    assert ((nr * (v / d[:, None])).sum(1)).min() > 0.999
+    assert len(v) - 3 * len(f) // 2 + len(f) == 2                           # Euler characteristic of a sphere
+
+
+def test_empty_and_full_volumes_and_bad_arguments():
+    from arcnerf_b200.plugin.mesh import extract_mesh
+    for fill in (0.0, 100.0):
+        v, f, n = extract_mesh(np.full((8, 8, 8), fill, np.float32), 50.0, (1, 1, 1), (8, 8, 8))
+        assert v.shape == (0, 3) and f.shape == (0, 3) and n.shape == (0, 3)
+    with pytest.raises(AssertionError):
+        extract_mesh(np.zeros((4, 4, 4), np.float32), 0.5, (1, 1, 1), (4, 4, 4), 'sideways')
+    with pytest.raises(RuntimeError):
+        extract_mesh(torch.zeros((4, 4, 4)), 0.5, (1, 1, 1), (4, 4, 4))
+    with pytest.raises(RuntimeError):
+        extract_mesh(np.zeros((1, 4, 4), np.float32), 0.5, (1, 1, 1), (1, 4, 4))
+
+
+@pytest.mark.parametrize('tag', ['cube16', 'box9', 'one', 'box67'])
+def test_volume_pts_match_reference_volume(tag):
+    """the reference's Volume.get_volume_pts() (tests/golden/make_golden_volume.py)"""
+    from arcnerf_b200.plugin.mesh import volume_pts
+    lo, hi, n = GOLD['%s_lo' % tag], GOLD['%s_hi' % tag], int(GOLD['%s_n' % tag])
+    ref = GOLD['%s_pts' % tag]
+    got = volume_pts(lo, hi, n).cpu().numpy()
+    assert _same(got, ref)
+    if n >= 4:
+        part = volume_pts(lo, hi, n, 1, 3).cpu().numpy()
+        assert _same(part, got.reshape(n, n * n, 3)[1:3].reshape(-1, 3))
+
+
+def test_ngp_density_grid_and_mesh_extraction():
+    """run_infer_volume on the NGP pipeline (infer_func.py:448-500): the lattice density equals forward_pts of the reference's
+    voxel centres, slab ranges tile the grid, and the extracted mesh is in world coordinates"""
+    from arcnerf_b200.ngp import NGPPipeline
+    from arcnerf_b200.plugin.mesh import volume_pts
+    pipe = NGPPipeline(max_rays=256, capacity=1 << 16, grid_scale=1.0)
+    n = 24
+    lo, hi = pipe.aabb[0].tolist(), pipe.aabb[1].tolist()
+    grid = pipe.density_grid(n, slab=5)
+    ref = pipe.forward_pts(volume_pts(lo, hi, n)).view(n, n, n)
+    assert torch.equal(grid, ref)
+    part = pipe.density_grid(n, x_range=(7, 19), slab=4)
+    assert torch.equal(part, grid[7:19])
+    level = float(grid.median())
+    v, f, nr = pipe.extract_mesh(n, level=level)
+    assert v.shape[1] == 3 and f.shape[1] == 3 and len(f) > 0 and nr.shape == v.shape
+    assert float(v.min()) >= lo[0] - 1e-5 and float(v.max()) <= hi[0] + 1e-5
+    rv, rf, _ = M.extract_mesh(grid.cpu().numpy(), level, [(hi[a] - lo[a]) / n for a in range(3)], [hi[a] - lo[a] for a in range(3)])
+    assert np.array_equal(f.cpu().numpy(), rf) and np.allclose(v.cpu().numpy(), rv + (np.asarray(lo) + np.asarray(hi)) / 2, atol=1e-6)

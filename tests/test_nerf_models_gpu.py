@@ -86,3 +86,44 @@ def test_nerf_trains_through_the_library_backward():
         opt.step()
         losses.append(float(loss.detach()))
     assert all(np.isfinite(losses)) and losses[-1] < 0.7 * losses[0], losses
+
+
+def test_ngp_foreground_over_nerfpp_background_blend_and_gradients():
+    """config 3 (NGP fg + NeRF++ bkg): the blend rgb_fg + T_last * rgb_bkg of full_model.py:310-330 evaluated inside the NGP
+    compositing kernel equals the explicit blend of separately rendered foreground (black background) and background, and the
+    background networks receive d loss / d rgb * T_last"""
+    from arcnerf_b200.plugin.fg_model import NGPFgModel
+    from arcnerf_b200.plugin.nerf_model import FullModel, NeRFPP
+    torch.manual_seed(0)
+    fg = NGPFgModel(dict(chunk_rays=512), max_rays=512, capacity=1 << 16)
+    bkg = NeRFPP(mc.NERFPP_BKG_CFG)
+    model = FullModel(fg, bkg)
+    o, d = mc.rays(300, seed=9)
+    feed = {'rays_o': torch.from_numpy(o).cuda()[None], 'rays_d': torch.from_numpy(d).cuda()[None]}
+    flat = {k: v[0] for k, v in feed.items()}
+    with torch.no_grad():
+        out = model(feed, inference_only=True)
+        black = fg(dict(flat, bkg_color=torch.zeros((1, 3), device='cuda')), inference_only=True)
+        b = bkg(flat, inference_only=True)
+    T = 1.0 - black['mask']
+    assert float(black['mask'].max()) > 0.05                                # the foreground does absorb something
+    # the kernel blends with the running product T_last, the explicit form with 1 - sum(weights): equal up to fp32 rounding
+    assert torch.allclose(out['rgb'][0], black['rgb'] + T[:, None] * b['rgb'], atol=3e-5)
+    assert torch.allclose(out['mask'][0], black['mask'], atol=1e-7)
+    assert torch.allclose(out['depth'][0], black['depth'] + T * b['depth'], atol=1e-4)
+    # training pass: gradients of the background nets through the fused blend == through the explicit blend
+    w = torch.rand((300, 3), generator=torch.Generator().manual_seed(2)).cuda()
+    model.zero_grad()
+    trn = model(feed)
+    (trn['rgb_coarse'][0] * w).sum().backward()
+    got = {k: p.grad.clone() for k, p in bkg.named_parameters() if p.grad is not None}
+    g_fg = fg.table.grad.clone()
+    assert got and float(g_fg.abs().max()) > 0
+    model.zero_grad()
+    bt = bkg(flat)
+    b_rgb = bt.get('rgb_fine', bt.get('rgb_coarse'))
+    (T[:, None].detach() * b_rgb * w).sum().backward()
+    for k, p in bkg.named_parameters():
+        if p.grad is not None:
+            ref = p.grad
+            assert torch.allclose(got[k], ref, rtol=1e-3, atol=1e-4 * float(ref.abs().max()) + 1e-9), k
