@@ -86,6 +86,7 @@ _SIGS = {
     'arcb200_peer_barrier': [P, I, I, P, P, I, P],
     'arcb200_grad_to_half': [P, P, L, L, L, F, P],
     'arcb200_adam_step_peer16': [P, P, P, I, I, L, L, P, P, P, F, I, F, F, F, F, F, F, P, P],
+    'arcb200_adam_step_mc16': [P, P, L, L, P, P, P, F, I, F, F, F, F, F, F, P, P],
     'arcb200_adam_step_peer': [P, P, I, L, L, P, P, P, I, F, F, F, F, F, F, P, P],
     'arcb200_probe_gather': [P, L, I, I, I, C.c_uint32, P, P],
     'arcb200_nerf_mlp_sizes': [I, I, I, I, I, I, I, P],

@@ -230,6 +230,70 @@ void launch_adam_peer16(unsigned blocks, cudaStream_t st, size_t lo, size_t hi, 
     arc_launch(adam_peer16_kernel<W>, blocks, 256, 0, st, lo, hi, p, m, v, g_own, pl, world, rank, inv_scale, h, step_dev);
 }
 
+// ---- the exchange done by the switch (NVLS): the arena is also mapped through a multicast object (torch symmetric memory sets
+// it up, arcnerf_b200/peer.py SymmArena); one multimem.ld_reduce returns the sum over ALL ranks' fp16 gradient copies of 8
+// entries (added in fp32 inside the fabric, returned as f16x2), one multimem.st writes the updated fp16 entries into every
+// rank's working table.  Per element a GPU issues one load and one store instead of world-1 loads and world stores, and each
+// NVLink carries the reduced / broadcast data once.
+__device__ __forceinline__ uint4 mc_ld_reduce_h8(const void *mc) {
+    uint4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(mc) : "memory");
+    return r;
+}
+__device__ __forceinline__ void mc_st_h8(void *mc, const uint4 &v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f16x2 [%0], {%1, %2, %3, %4};"
+                 :: "l"(mc), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// Adam over [lo, hi) (multiples of 8) on  sum over all ranks of grad16 / scale;  mc_grad16 / mc_half_out are MULTICAST addresses of
+// the fp16 gradient copy and of the fp16 working table.
+__global__ void adam_mc16_kernel(size_t lo, size_t hi, float *__restrict__ p, float *__restrict__ m, float *__restrict__ v,
+                                 const __half *mc_grad16, __half *mc_half_out, float inv_scale, AdamHyper h,
+                                 const int32_t *__restrict__ step_dev) {
+    arc_pdl_sync();
+    if (step_dev) bias_from_step(h, max(*step_dev, 1));
+    const size_t stride = (size_t)gridDim.x * blockDim.x;
+    constexpr int U = 1;                                  // reductions in flight per thread (more did not help: N = 2 measured 85 vs 76 us at U = 4)
+    for (size_t k0 = lo / 8 + (size_t)blockIdx.x * blockDim.x + threadIdx.x; k0 < hi / 8; k0 += stride * U) {
+        uint4 gsu[U];
+        #pragma unroll
+        for (int u = 0; u < U; ++u)
+            if (k0 + u * stride < hi / 8) gsu[u] = mc_ld_reduce_h8(reinterpret_cast<const uint4 *>(mc_grad16) + k0 + u * stride);
+        #pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const size_t k = k0 + u * stride;
+            if (k >= hi / 8) break;
+            const uint4 gs = gsu[u];
+            float pv[8], mv[8], vv[8], g[8];
+            #pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                const float4 a = reinterpret_cast<const float4 *>(p)[2 * k + q], b = reinterpret_cast<const float4 *>(m)[2 * k + q],
+                             c = reinterpret_cast<const float4 *>(v)[2 * k + q];
+                pv[4 * q] = a.x; pv[4 * q + 1] = a.y; pv[4 * q + 2] = a.z; pv[4 * q + 3] = a.w;
+                mv[4 * q] = b.x; mv[4 * q + 1] = b.y; mv[4 * q + 2] = b.z; mv[4 * q + 3] = b.w;
+                vv[4 * q] = c.x; vv[4 * q + 1] = c.y; vv[4 * q + 2] = c.z; vv[4 * q + 3] = c.w;
+            }
+            const uint32_t wd[4] = {gs.x, gs.y, gs.z, gs.w};
+            #pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&wd[q]));
+                g[2 * q] = f.x * inv_scale; g[2 * q + 1] = f.y * inv_scale;
+            }
+            #pragma unroll
+            for (int q = 0; q < 8; ++q) adam_one(pv[q], mv[q], vv[q], g[q], h);
+            #pragma unroll
+            for (int q = 0; q < 2; ++q) {
+                reinterpret_cast<float4 *>(p)[2 * k + q] = make_float4(pv[4 * q], pv[4 * q + 1], pv[4 * q + 2], pv[4 * q + 3]);
+                reinterpret_cast<float4 *>(m)[2 * k + q] = make_float4(mv[4 * q], mv[4 * q + 1], mv[4 * q + 2], mv[4 * q + 3]);
+                reinterpret_cast<float4 *>(v)[2 * k + q] = make_float4(vv[4 * q], vv[4 * q + 1], vv[4 * q + 2], vv[4 * q + 3]);
+            }
+            mc_st_h8(reinterpret_cast<uint4 *>(mc_half_out) + k,
+                     make_uint4(pack_h2(pv[0], pv[1]), pack_h2(pv[2], pv[3]), pack_h2(pv[4], pv[5]), pack_h2(pv[6], pv[7])));
+        }
+    }
+}
+
 __device__ __forceinline__ void st_release_sys(unsigned long long *p, unsigned long long v) {
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
@@ -454,6 +518,30 @@ int arcb200_adam_step_peer16(float *g_own, const void *const *grads16, void *con
         case 8: launch_adam_peer16<8>((unsigned)blocks, st, lo, hi, p, m, v, g_own, pl, world, rank, inv, h, step_dev); break;
         default: launch_adam_peer16<0>((unsigned)blocks, st, lo, hi, p, m, v, g_own, pl, world, rank, inv, h, step_dev); break;
     }
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// The same step with the reduce and the broadcast done in the NVSwitch: mc_grad16 / mc_half_out are multicast addresses (one
+// mapping that reaches the same offset of every rank's arena) of the fp16 gradient copies (arcb200_grad_to_half over the WHOLE
+// vector: keep_lo = keep_hi = 0, so the own gradient takes the same fp16 rounding as the peers') and of the fp16 working table.
+// lo and hi are multiples of 8.  Same ordering contract as arcb200_adam_step_peer: a barrier before and after.
+int arcb200_adam_step_mc16(const void *mc_grad16, void *mc_half_out, int64_t lo, int64_t hi, float *p, float *m, float *v,
+                           float scale, int step, float lr, float beta1, float beta2, float eps, float weight_decay,
+                           float grad_scale, const int32_t *step_dev, void *stream) {
+    ARC_REQUIRE(lo >= 0 && hi >= lo && (lo & 7) == 0 && (hi & 7) == 0, "adam_step_mc16: bad range [%lld, %lld)", (long long)lo, (long long)hi);
+    if (hi == lo) return ARCB200_OK;
+    ARC_REQUIRE(mc_grad16 && mc_half_out && p && m && v && scale > 0.f && (step >= 1 || step_dev), "adam_step_mc16: null pointer, scale or step");
+    if (step < 1) step = 1;
+    ARC_REQUIRE((((uintptr_t)p | (uintptr_t)m | (uintptr_t)v | (uintptr_t)mc_grad16 | (uintptr_t)mc_half_out) & 15u) == 0,
+                "adam_step_mc16: misaligned buffer");
+    const AdamHyper h = make_adam_hyper(lr, beta1, beta2, eps, weight_decay, grad_scale, step);
+    long long blocks = ((hi - lo) / 8 + 255) / 256;
+    const long long cap = (long long)arc_sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    arc_launch(adam_mc16_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, (size_t)lo, (size_t)hi, p, m, v,
+               (const __half *)mc_grad16, (__half *)mc_half_out, 1.0f / scale, h, step_dev);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }

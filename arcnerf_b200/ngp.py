@@ -138,37 +138,61 @@ class NGPPipeline:
             exchange = os.environ.get('ARCB200_EXCHANGE', 'peer16')
         self.exchange = exchange if self.world_size > 1 else 'none'
         self.arena = None
-        if self.exchange in ('peer', 'peer16'):
+        if self.exchange in ('peer', 'peer16', 'mc16'):
             import torch.distributed as dist
-            from .peer import PeerArena, slice_bounds
+            from .peer import PeerArena, SymmArena, slice_bounds
 
             def share(handle):
                 out = [None] * self.world_size
                 dist.all_gather_object(out, handle)
                 return out
-            self.rank = dist.get_rank()
-            regions = {'grad': (nt + ng + nr) * 4, 'table_h': nt * 2}
-            if self.exchange == 'peer16':
-                regions['grad16'] = nt * 2
-            # peer mapping needs every rank to see every GPU of the node (a launcher that hides devices per process, or GPUs
-            # without P2P, makes cudaIpcOpenMemHandle fail): all ranks then agree to use the NCCL all-reduce instead
-            err = None
-            try:
-                self.arena = PeerArena(regions, dev, self.rank, self.world_size, share)
-            except RuntimeError as e:
-                err = e
-            ok = torch.tensor([0 if err is not None else 1], dtype=torch.int32, device=dev if dist.get_backend() != 'gloo' else 'cpu')
-            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-            if int(ok.item()) == 0:
+
+            def all_ok(flag):
+                ok = torch.tensor([1 if flag else 0], dtype=torch.int32, device=dev if dist.get_backend() != 'gloo' else 'cpu')
+                dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+                return int(ok.item()) == 1
+
+            def note(msg):
                 if self.rank == 0:
                     import sys
-                    sys.stderr.write('arcnerf_b200: peer-memory exchange unavailable (%s); using the NCCL all-reduce\n'
-                                     % (err if err is not None else 'another rank could not map the arenas'))
-                if self.arena is not None:       # mapped here, but another rank could not: give the mappings and the arena back
-                    self.arena.close(sync_ranks=dist.barrier)
-                else:
-                    dist.barrier()
-                self.arena, self.exchange = None, 'nccl'
+                    sys.stderr.write('arcnerf_b200: %s\n' % msg)
+            self.rank = dist.get_rank()
+            regions = {'grad': (nt + ng + nr) * 4, 'table_h': nt * 2}
+            if self.exchange in ('peer16', 'mc16'):
+                regions['grad16'] = nt * 2
+            if self.exchange == 'mc16':
+                # in-switch reduce / broadcast: needs torch's symmetric memory with a multicast mapping on every rank (NVSwitch)
+                err = None
+                try:
+                    assert nt % 8 == 0, 'table size not a multiple of 8'
+                    self.arena = SymmArena(regions, dev, self.rank, self.world_size)
+                    if not self.arena.mc_base:
+                        err = 'no multicast support on this fabric'
+                except Exception as e:                          # noqa: BLE001  (any failure -> agree on the fallback)
+                    err = e
+                if not all_ok(err is None):
+                    note('multicast exchange unavailable (%s); using the peer-memory exchange' % (err if err is not None else 'another rank failed'))
+                    if self.arena is not None:
+                        self.arena.close(sync_ranks=dist.barrier)
+                    else:
+                        dist.barrier()
+                    self.arena, self.exchange = None, 'peer16'
+            if self.arena is None:
+                # peer mapping needs every rank to see every GPU of the node (a launcher that hides devices per process, or GPUs
+                # without P2P, makes cudaIpcOpenMemHandle fail): all ranks then agree to use the NCCL all-reduce instead
+                err = None
+                try:
+                    self.arena = PeerArena(regions, dev, self.rank, self.world_size, share)
+                except RuntimeError as e:
+                    err = e
+                if not all_ok(err is None):
+                    note('peer-memory exchange unavailable (%s); using the NCCL all-reduce'
+                         % (err if err is not None else 'another rank could not map the arenas'))
+                    if self.arena is not None:   # mapped here, but another rank could not: give the mappings and the arena back
+                        self.arena.close(sync_ranks=dist.barrier)
+                    else:
+                        dist.barrier()
+                    self.arena, self.exchange = None, 'nccl'
         if self.arena is not None:
             self.table_h = self.arena.local('table_h', torch.float16)
             F.cast_f16(self.table, self.table_h)
@@ -536,7 +560,7 @@ class NGPPipeline:
         and broadcasts the fp16 working copy (hash table: this rank's slice only; the two small heads: redundantly on
         every rank, same summation order, so the replicas stay identical), barrier, clear the own gradients.
         'nccl': ONE all-reduce of the flat gradient buffer (48.8 MB), then the single-GPU Adam kernels."""
-        if self.exchange not in ('peer', 'peer16'):
+        if self.exchange not in ('peer', 'peer16', 'mc16'):
             import torch.distributed as dist
             self._run('all_reduce', lambda: dist.all_reduce(self.g_all))
             self.optimizer_step(counted)
@@ -554,15 +578,22 @@ class NGPPipeline:
                                ar.pointers('table_h'))
         g_t, g_g, g_r, th = self._peer_ptrs
         lo, hi = self.slice
-        half = self.exchange == 'peer16'
+        half = self.exchange in ('peer16', 'mc16')
+        mc = self.exchange == 'mc16'
         if half:
-            from .peer import adam_step_peer16, grad_to_half
+            from .peer import adam_step_mc16, adam_step_peer16, grad_to_half
             if not hasattr(self, '_g16'):
                 self._g16 = self.arena.local('grad16', torch.float16)
                 self._g16_ptrs = ar.pointers('grad16')
-            self._run('grad_to_half', lambda: grad_to_half(self.g_table, self._g16, lo, hi, cfg.get('exchange_scale', 128.0)))
+            # 'mc16': the whole vector goes to fp16 (the switch sums every rank's copy, the own one included)
+            keep = (0, 0) if mc else (lo, hi)
+            self._run('grad_to_half', lambda: grad_to_half(self.g_table, self._g16, keep[0], keep[1], cfg.get('exchange_scale', 128.0)))
         self._run('peer_barrier', ar.barrier)
-        if half:
+        if mc:
+            self._run('adam_table_peer', lambda: adam_step_mc16(ar.mc_pointer('grad16'), ar.mc_pointer('table_h'), lo, hi,
+                                                                self.table, self.m_table, self.v_table, self.step_count,
+                                                                cfg['lr'], scale=cfg.get('exchange_scale', 128.0), **kw))
+        elif half:
             self._run('adam_table_peer', lambda: adam_step_peer16(self.g_table, self._g16_ptrs, th, W, self.rank, lo, hi,
                                                                   self.table, self.m_table, self.v_table, self.step_count,
                                                                   cfg['lr'], scale=cfg.get('exchange_scale', 128.0), **kw))
@@ -587,10 +618,21 @@ class NGPPipeline:
                 self.g_all.zero_()
         self._run('peer_barrier+clear', close)
 
+    def close(self):
+        """Orderly teardown of a multi-rank pipeline: captured graphs first (they reference arena memory), then the peer arena
+        (every rank unmaps its peers, a barrier, every rank frees its own allocation).  Collective: call it on every rank, before
+        torch.distributed.destroy_process_group()."""
+        self.graphs = [None, None]
+        torch.cuda.synchronize(self.dev)
+        if self.arena is not None:
+            import torch.distributed as dist
+            arena, self.arena = self.arena, None
+            arena.close(sync_ranks=dist.barrier)
+
     def gather_master_table(self):
         """'peer' exchange keeps the fp32 master of the hash table sharded (each rank owns self.slice); this collects
         the full fp32 table on every rank (checkpointing; not on the step path)."""
-        if self.exchange not in ('peer', 'peer16'):
+        if self.exchange not in ('peer', 'peer16', 'mc16'):
             return self.table
         import torch.distributed as dist
         from .peer import slice_bounds

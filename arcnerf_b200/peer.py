@@ -109,6 +109,56 @@ class PeerArena:
                 self.base = None
 
 
+class SymmArena(PeerArena):
+    """The same arena on torch's symmetric memory (torch.distributed._symmetric_memory: cuMemCreate + fabric handles exchanged
+    through the process group's store): every rank's pointer to every arena as before, plus - when the fabric supports it - ONE
+    multicast address per region that reaches all arenas at once (multimem.ld_reduce / multimem.st, csrc/peer.cu
+    adam_mc16_kernel).  Torch is plumbing here: allocation and handle exchange; the kernels are the library's."""
+
+    def __init__(self, regions, device, rank, world, group=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        self.rank, self.world, self.device = rank, world, torch.device(device)
+        self.offsets, off = {}, FLAG_BYTES
+        for name, nbytes in regions.items():
+            self.offsets[name] = (off, nbytes)
+            off = _round_up(off + nbytes, ALIGN)
+        self.nbytes = off
+        with torch.cuda.device(self.device):
+            self._bytes = symm.empty(self.nbytes, dtype=torch.uint8, device=self.device)
+            self._hdl = symm.rendezvous(self._bytes, group if group is not None else dist.group.WORLD)
+            self._bytes.zero_()
+            torch.cuda.synchronize(self.device)
+        self.bases = [int(b) for b in self._hdl.buffer_ptrs]
+        self.base = self.bases[rank]
+        assert self.base == self._bytes.data_ptr()
+        self.mc_base = int(self._hdl.multicast_ptr or 0)
+        self.epoch = torch.zeros(1, dtype=torch.int64, device=self.device)
+        self.status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._flag_ptrs = (C.c_void_p * world)(*self.bases)
+
+    def mc_pointer(self, name, byte_offset=0):
+        """multicast address of the region (0 when the fabric has no multicast)"""
+        return self.mc_base + self.offsets[name][0] + byte_offset if self.mc_base else 0
+
+    def close(self, sync_ranks=None):
+        """torch owns the allocation and the mappings: synchronise, let every rank finish, drop the references"""
+        if getattr(self, 'bases', None) is None:
+            return
+        torch.cuda.synchronize(self.device)
+        if sync_ranks is not None:
+            sync_ranks()
+        self.bases, self._hdl, self._bytes = None, None, None
+
+
+def adam_step_mc16(mc_grad16, mc_half_out, lo, hi, p, m, v, step, lr, scale=128.0, beta1=0.9, beta2=0.999, eps=1e-8,
+                   weight_decay=0.0, grad_scale=1.0, step_dev=None):
+    """mc_grad16 / mc_half_out: multicast addresses from SymmArena.mc_pointer"""
+    _lib.call('arcb200_adam_step_mc16', mc_grad16, mc_half_out, int(lo), int(hi), p.data_ptr(), m.data_ptr(), v.data_ptr(),
+              float(scale), int(step), float(lr), float(beta1), float(beta2), float(eps), float(weight_decay), float(grad_scale),
+              _lib.ptr(step_dev), _lib.current_stream())
+
+
 def adam_step_peer(grads, half_out, world, lo, hi, p, m, v, step, lr, beta1=0.9, beta2=0.999, eps=1e-8,
                    weight_decay=0.0, grad_scale=1.0, step_dev=None):
     """grads / half_out: ctypes pointer arrays from PeerArena.pointers (half_out may be None)"""

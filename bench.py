@@ -112,6 +112,7 @@ EXCHANGE_NOTE = {
     'none': 'single GPU',
     'peer': 'fused into the Adam kernel: peer loads of the gradient slices + peer stores of the fp16 table over NVLink (csrc/peer.cu)',
     'peer16': 'fused into the Adam kernel over NVLink peer memory (csrc/peer.cu): the hash-table gradient travels as a loss-scaled fp16 copy (the precision tcnn hands to DDP in the reference), summed in fp32 with the owner\'s own fp32 slice; fp16 table slices stored back to every rank',
+    'mc16': 'done by the NVSwitch, fused into the Adam kernel (csrc/peer.cu adam_mc16_kernel): one multimem.ld_reduce per 8 entries sums every rank\'s loss-scaled fp16 gradient copy in the fabric (fp32 accumulation), one multimem.st broadcasts the updated fp16 table entries to every rank',
     'nccl': 'one NCCL all-reduce of the flat fp32 gradient buffer per step, then Adam on every rank',
 }
 
@@ -404,6 +405,9 @@ def main():
         sl = slice(rank * per, min(n_all, (rank + 1) * per))
         o_d, d_d = torch.from_numpy(o[sl]).to(dev), torch.from_numpy(d[sl]).to(dev)
         white = torch.ones((1, 3), device=dev)
+        # the frame is assembled on every rank by ONE all-gather into a preallocated buffer (equal tiles of `per` rays)
+        tile = torch.zeros((per, 3), device=dev)
+        frame = torch.empty((world * per, 3), device=dev) if dist is not None else None
         for _ in range(2):
             rp.render(o_d, d_d, white)
         times = []
@@ -412,9 +416,8 @@ def main():
             e0.record()
             rgb, _, _ = rp.render(o_d, d_d, white)
             if dist is not None:
-                pad = torch.zeros((per, 3), device=dev); pad[:rgb.shape[0]] = rgb
-                outs = [torch.empty_like(pad) for _ in range(world)] if rank == 0 else None
-                dist.gather(pad, outs, dst=0)
+                tile[:rgb.shape[0]].copy_(rgb)
+                dist.all_gather_into_tensor(frame, tile)
             e1.record()
             barrier()
             times.append(max_over_ranks(e0.elapsed_time(e1)))
@@ -459,21 +462,20 @@ def main():
                         occupancy_refresh=('every %d steps inside the timed region: 524288 + 524288 voxels of 128^3 re-evaluated (steady-state VolumeBound.optimize), result not applied to the synthetic scene' % occ_every) if occ_every > 0 else 'off',
                         parallelism='dp%d' % world, gradient_exchange=EXCHANGE_NOTE[pipe.exchange]),
             e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=4, ms_per_step=ms_e2e / K, path=e2e_mode),
-            gpu_launches=(NGPPipeline.LAUNCHES_TRAIN + {'peer': 2, 'peer16': 3}.get(pipe.exchange, 0)) * K
+            gpu_launches=(NGPPipeline.LAUNCHES_TRAIN + {'peer': 2, 'peer16': 3, 'mc16': 3}.get(pipe.exchange, 0)) * K
             + (NGPPipeline.LAUNCHES_REFRESH * (K // occ_every) if occ_every > 0 else 0),
             clocks=clock_info, roofline=roofline, cpu_baseline=cpu_baseline,
             render_ms_800x800=render_ms,
         )
         print(json.dumps(line))
     if dist is not None:
-        # captured graphs hold NCCL work: release them before the communicator, and never let teardown hang the job
+        # orderly teardown: captured graphs and the peer arena are released (collectively) before the communicator
         sys.stdout.flush()
-        threading.Timer(20.0, lambda: os._exit(0)).start()
-        pipe.graphs = None
-        torch.cuda.synchronize()
+        if not args.no_render:
+            rp.close()
+        pipe.close()
         dist.barrier()
         dist.destroy_process_group()
-        os._exit(0)
 
 
 if __name__ == '__main__':

@@ -209,17 +209,17 @@ def run_mesh(args, rank, world, dev, dist, read_peaks, ClockSampler):
     cam_id = torch.zeros(p1 - p0, dtype=torch.int32, device=dev)
     x0, x1 = adist.shard_range(n_grid, rank, world)
     frame_host = torch.empty((Wd * Ht, 3), dtype=torch.float32).pin_memory() if rank == 0 else None
+    tile = torch.zeros((per, 3), device=dev)
+    frame_dev = torch.empty((world * per, 3), device=dev) if dist is not None else None
 
     def frame():
         o, d = ray_helper.get_train_batch_rays(cams, cam_id, pix, Wd, Ht)
         rgb, _, _ = rp.render(o, d, white)
         if dist is None:
             return rgb
-        pad = torch.zeros((per, 3), device=dev)
-        pad[:rgb.shape[0]] = rgb
-        out = torch.empty((world * per, 3), device=dev) if rank == 0 else None
-        dist.gather(pad, list(out.view(world, per, 3).unbind(0)) if rank == 0 else None, dst=0)
-        return out[:Wd * Ht] if rank == 0 else None
+        tile[:rgb.shape[0]].copy_(rgb)
+        dist.all_gather_into_tensor(frame_dev, tile)                     # one collective into the preallocated frame
+        return frame_dev[:Wd * Ht]
 
     stats = {}
 

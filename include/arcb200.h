@@ -433,6 +433,14 @@ int arcb200_adam_step_peer16(float *g_own, const void *const *grads16, void *con
                              int64_t lo, int64_t hi, float *p, float *m, float *v, float scale, int step, float lr,
                              float beta1, float beta2, float eps, float weight_decay, float grad_scale,
                              const int32_t *step_dev, void *stream);
+/* The same exchange carried out by the NVSwitch (NVLS): mc_grad16 and mc_half_out are MULTICAST addresses (one mapping bound to
+ * the same offset of every rank's arena; arcnerf_b200/peer.py SymmArena obtains it from torch's symmetric memory) of the fp16
+ * gradient copies - made by arcb200_grad_to_half over the whole vector (keep_lo = keep_hi = 0) - and of the fp16 working table.
+ * One multimem.ld_reduce (fp32 accumulation in the fabric) replaces the world-1 peer loads, one multimem.st the world peer
+ * stores.  lo, hi multiples of 8.  Replaces the same DDP all-reduce + Adam (common/trainer/basic_trainer.py:192-202). */
+int arcb200_adam_step_mc16(const void *mc_grad16, void *mc_half_out, int64_t lo, int64_t hi, float *p, float *m, float *v,
+                           float scale, int step, float lr, float beta1, float beta2, float eps, float weight_decay,
+                           float grad_scale, const int32_t *step_dev, void *stream);
 
 /* ---- fused field forward (csrc/field_fused.cuh) -----------------------------------------------------------------------
  * The NGP foreground model's per-sample network in one launch: hash-grid encode (16 levels x 2 features) -> geometry head

@@ -123,7 +123,9 @@ def _two_rank_worker(rank, world, port, out_dir, one_device):
     params = init_params(dict(NGP_DEFAULTS), seed=3, grid_scale=0.5)
     n = 1024
     res = {}
-    for mode in ('nccl', 'peer', 'peer16'):
+    # 'mc16' (in-switch reduce) needs two real GPUs behind an NVSwitch; two ranks on one device cannot form a multicast group
+    peer_modes = ('peer', 'peer16') if one_device else ('peer', 'peer16', 'mc16')
+    for mode in ('nccl', ) + peer_modes:
         pipe = NGPPipeline(max_rays=n, capacity=1 << 17, device='cuda:%d' % dev, world_size=world, exchange=mode,
                            params={k: v.clone() for k, v in params.items()}, lr=1e-2)
         pipe.set_occupancy(synth.occupancy_volume('lego'))
@@ -137,11 +139,14 @@ def _two_rank_worker(rank, world, port, out_dir, one_device):
         if mode != 'nccl':
             assert pipe.arena is not None and pipe.exchange == mode, 'peer arena was not mapped: fell back to %s' % pipe.exchange
             pipe.arena.check()
-        res[mode] = dict(table=pipe.gather_master_table().clone(), table_h=pipe.table_h.clone(), geo=pipe.geo_p.clone(),
-                         rad=pipe.rad_p.clone(), loss=losses)
+            pipe_table = pipe.gather_master_table().clone()
+        else:
+            pipe_table = pipe.table.clone()
+        res[mode] = dict(table=pipe_table, table_h=pipe.table_h.clone(), geo=pipe.geo_p.clone(), rad=pipe.rad_p.clone(), loss=losses)
+        pipe.close()                                   # collective teardown of the arena before the next mode allocates one
     ok = True
     msg = []
-    for mode_b in ('peer', 'peer16'):
+    for mode_b in peer_modes:
         for k in ('table', 'table_h', 'geo', 'rad'):
             # the hash-grid backward accumulates with float atomics (run-to-run order differs), and Adam turns a sign flip
             # of a near-zero gradient into a +-lr step: compare by the fraction of entries that moved apart
@@ -154,7 +159,8 @@ def _two_rank_worker(rank, world, port, out_dir, one_device):
             ok = False
             msg.append('%s losses differ %s %s' % (mode_b, res['nccl']['loss'], res[mode_b]['loss']))
         # replicas agree across ranks
-        th = res[mode_b]['table_h'].float().cpu()
+        th = res[mode_b]['table_h'].float()
+        th = th.cpu() if one_device else th                 # gloo gathers host tensors, NCCL device tensors
         other = [torch.empty_like(th) for _ in range(world)]
         dist.all_gather(other, th)
         if not all(torch.equal(o, th) for o in other):
