@@ -98,6 +98,7 @@ _SIGS = {
     'arcb200_mc_scratch_sizes': [I, I, I, P],
     'arcb200_mc_count': [P, I, I, I, F, I, P, P, P],
     'arcb200_mc_emit': [P, I, I, I, F, I, P, P, P, P, P, P, P, L, P, L, P],
+    'arcb200_mesh_components': [P, P, L, L, P, P, P, P],
     'arcb200_gemm_nt': [P, L, P, L, P, P, L, L, I, I, P],
     'arcb200_gemm_tn': [P, L, P, L, P, L, L, I, I, P],
     'arcb200_softplus': [P, F, I, P, L, P],

@@ -254,6 +254,45 @@ __global__ void mc_scan_kernel(int32_t* __restrict__ sums, int64_t n) {
     if (threadIdx.x == 0) sums[n] = carry_s;
 }
 
+// ------------------------------------------------------------------------------------------------ mesh components
+// get_normals / get_face_centers (arcnerf/geometry/mesh.py:88-125; trimesh face normals + mean_vertex_normals): unit face normal by
+// the right-hand rule, face centre, and per vertex the sum of the unit normals of its faces (normalised by the second kernel)
+__global__ void mesh_face_kernel(const float* __restrict__ verts, const int32_t* __restrict__ faces, int64_t n_f,
+                                 float* __restrict__ face_normals, float* __restrict__ face_centers, float* __restrict__ vert_acc) {
+    int64_t f = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (f >= n_f) return;
+    int ia = faces[3 * f], ib = faces[3 * f + 1], ic = faces[3 * f + 2];
+    float a[3], b[3], c[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { a[k] = verts[3 * (int64_t)ia + k]; b[k] = verts[3 * (int64_t)ib + k]; c[k] = verts[3 * (int64_t)ic + k]; }
+    float u[3] = {b[0] - a[0], b[1] - a[1], b[2] - a[2]}, w[3] = {c[0] - a[0], c[1] - a[1], c[2] - a[2]};
+    float n[3] = {u[1] * w[2] - u[2] * w[1], u[2] * w[0] - u[0] * w[2], u[0] * w[1] - u[1] * w[0]};
+    float len = sqrtf(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+    float inv = len > 0.f ? 1.f / len : 0.f;               // degenerate faces contribute nothing (trimesh drops them too)
+#pragma unroll
+    for (int k = 0; k < 3; ++k) {
+        n[k] *= inv;
+        if (face_normals) face_normals[3 * f + k] = n[k];
+        if (face_centers) face_centers[3 * f + k] = (a[k] + b[k] + c[k]) / 3.0f;
+    }
+    if (vert_acc) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+            atomicAdd(vert_acc + 3 * (int64_t)ia + k, n[k]);
+            atomicAdd(vert_acc + 3 * (int64_t)ib + k, n[k]);
+            atomicAdd(vert_acc + 3 * (int64_t)ic + k, n[k]);
+        }
+    }
+}
+
+__global__ void mesh_vert_normalize_kernel(float* __restrict__ vn, int64_t n_v) {
+    int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (v >= n_v) return;
+    float x = vn[3 * v], y = vn[3 * v + 1], z = vn[3 * v + 2];
+    float len = sqrtf(x * x + y * y + z * z) + 1e-8f;      // transformation.py:11-25 normalize
+    vn[3 * v] = x / len; vn[3 * v + 1] = y / len; vn[3 * v + 2] = z / len;
+}
+
 inline int64_t blocks_of(int64_t n) { return (n + kBlock - 1) / kBlock; }
 
 inline int check_vol(const float* vol, int nx, int ny, int nz) {
@@ -319,6 +358,16 @@ int arcb200_mc_emit(const float* vol, int nx, int ny, int nz, float level, int a
         V, n_pts, point_blocks, make_float3(spacing[0], spacing[1], spacing[2]), make_float3(offset[0], offset[1], offset[2]), vbase,
         verts, normals, v_cap);
     mc_cell_emit_kernel<<<(unsigned)blocks_of(n_cells), kBlock, 0, st>>>(V, n_cells, cell_blocks, vbase, faces, f_cap);
+    return cudaGetLastError() == cudaSuccess ? ARCB200_OK : ARCB200_ERR_CUDA;
+}
+
+int arcb200_mesh_components(const float* verts, const int32_t* faces, int64_t n_v, int64_t n_f, float* face_normals,
+                            float* face_centers, float* vert_normals, void* stream) {
+    if (n_v < 0 || n_f < 0 || (n_f > 0 && (!verts || !faces))) return ARCB200_ERR_ARG;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (vert_normals && n_v > 0 && cudaMemsetAsync(vert_normals, 0, sizeof(float) * 3 * n_v, st) != cudaSuccess) return ARCB200_ERR_CUDA;
+    if (n_f > 0) mesh_face_kernel<<<(unsigned)blocks_of(n_f), kBlock, 0, st>>>(verts, faces, n_f, face_normals, face_centers, vert_normals);
+    if (vert_normals && n_v > 0) mesh_vert_normalize_kernel<<<(unsigned)blocks_of(n_v), kBlock, 0, st>>>(vert_normals, n_v);
     return cudaGetLastError() == cudaSuccess ? ARCB200_OK : ARCB200_ERR_CUDA;
 }
 

@@ -194,6 +194,8 @@ class NGPPipeline:
                         dist.barrier()
                     self.arena, self.exchange = None, 'nccl'
         if self.arena is not None:
+            if os.environ.get('ARCB200_PEER_HOST_BARRIER', '0') == '1':
+                self.arena.host_barrier = dist.barrier          # ranks sharing one device (tests): no spinning kernels
             self.table_h = self.arena.local('table_h', torch.float16)
             F.cast_f16(self.table, self.table_h)
             self.slice = slice_bounds(nt, self.rank, self.world_size)
@@ -308,6 +310,35 @@ class NGPPipeline:
             F.grid_forward(unit[:b - a], self.table_h, self.geom, out=enc[:b - a])
             F.mlp_forward(enc[:b - a], self.geo_blob, self.geo_spec, out=feat[:b - a], exp0_out=out[a:b])
         return out
+
+    @torch.no_grad()
+    def forward_pts_dir(self, pts, dirs, chunk=1 << 19):
+        """density and colour at world points seen along `dirs` (N,3 each) -> sigma (N,), rgb (N,3): one fused launch per chunk
+        (Base3dModel.forward_pts_dir, base_3d_model.py:233-254; used for mesh colours, infer_func.py:582-632)"""
+        pts = pts.to(self.dev, torch.float32).contiguous()
+        dirs = dirs.to(self.dev, torch.float32).contiguous()
+        n = pts.shape[0]
+        sigma = torch.empty((n, ), dtype=torch.float32, device=self.dev)
+        rgb = torch.empty((n, 3), dtype=torch.float32, device=self.dev)
+        unit = torch.empty((min(n, chunk), 3), dtype=torch.float32, device=self.dev)
+        nl, nf, off, sc, rs = self.geom._args()
+        for a in range(0, n, chunk):
+            b = min(n, a + chunk)
+            _lib.call('arcb200_world_to_unit', pts[a:b].data_ptr(), self.aabb.data_ptr(), unit.data_ptr(), b - a, _lib.current_stream())
+            _lib.call('arcb200_field_fwd', unit.data_ptr(), self.table_h.data_ptr(), nl, nf, off, sc, rs, self.geo_blob.data_ptr(),
+                      self.rad_blob.data_ptr(), dirs[a:b].data_ptr(), None, 1, None, None, None, None, sigma[a:].data_ptr(),
+                      rgb[a:].data_ptr(), None, b - a, None, _lib.current_stream())
+        return sigma, rgb
+
+    @torch.no_grad()
+    def mesh_components(self, verts, faces):
+        """get_mesh_components (infer_func.py:582-632): normals, face centres and the colours the model gives to vertices and
+        face centres when looked at against their normals"""
+        from .plugin.mesh import get_mesh_components
+        vn, fn, fc = get_mesh_components(verts, faces)
+        _, vc = self.forward_pts_dir(verts, -vn)
+        _, fcol = self.forward_pts_dir(fc, -fn)
+        return dict(verts=verts, faces=faces, vert_normals=vn, face_normals=fn, face_centers=fc, vert_colors=vc, face_colors=fcol)
 
     @torch.no_grad()
     def density_grid(self, n_grid, x_range=None, slab=16):

@@ -82,6 +82,12 @@ class PeerArena:
     def barrier(self, timeout_ms=0):
         """flag barrier between the ranks, on the current stream (nothing blocks on the host).  A rank that waits longer than
         the timeout (default ARCB200_PEER_TIMEOUT_MS or 10 minutes) ends the job: the kernel traps, see arcb200_peer_barrier"""
+        if getattr(self, 'host_barrier', None) is not None:
+            # ranks that share ONE device (a test on a 1-GPU box): kernels of different processes are time-sliced, so a kernel
+            # spinning on another rank's flag may never see it run - synchronise through the host instead
+            torch.cuda.current_stream(self.device).synchronize()
+            self.host_barrier()
+            return
         _lib.call('arcb200_peer_barrier', self._flag_ptrs, self.world, self.rank, self.epoch.data_ptr(),
                   self.status.data_ptr(), int(timeout_ms), _lib.current_stream())
 

@@ -54,3 +54,19 @@ def extract_mesh(sigma, level, voxel_size, volume_len, grad_dir='descent', with_
     if as_numpy:
         return verts.cpu().numpy(), faces.cpu().numpy(), normals.cpu().numpy() if with_normals else None
     return verts, faces, normals
+
+
+def get_mesh_components(verts, faces):
+    """get_normals + get_face_centers (arcnerf/geometry/mesh.py:88-125) on the device: verts (V, 3) fp32, faces (F, 3) int32
+    CUDA tensors -> vert_normals (V, 3), face_normals (F, 3), face_centers (F, 3)"""
+    if not (verts.is_cuda and faces.is_cuda):
+        raise RuntimeError('verts and faces must be CUDA tensors')
+    verts, faces = verts.contiguous().float(), faces.contiguous().to(torch.int32)
+    n_v, n_f = verts.shape[0], faces.shape[0]
+    vn = torch.empty((n_v, 3), dtype=torch.float32, device=verts.device)
+    fn = torch.empty((n_f, 3), dtype=torch.float32, device=verts.device)
+    fc = torch.empty((n_f, 3), dtype=torch.float32, device=verts.device)
+    with torch.cuda.device(verts.device):
+        _lib.call('arcb200_mesh_components', verts.data_ptr(), faces.data_ptr(), n_v, n_f, fn.data_ptr(), fc.data_ptr(), vn.data_ptr(),
+                  _lib.current_stream())
+    return vn, fn, fc

@@ -382,10 +382,10 @@ def main():
     peak = peaks['hbm_gbs'] if bound == 'hbm' else peaks['bf16_tflops']
     traffic, traffic_src = None, None
     try:                                        # DRAM bytes per launch of that kernel from the committed ncu --set full capture
-        with open(os.path.join(ROOT, 'profiles', 'r01b_traffic.json')) as f:
+        with open(os.path.join(ROOT, 'profiles', 'r02_traffic.json')) as f:
             tj = json.load(f)
         if top[0] in tj:
-            traffic, traffic_src = tj[top[0]]['traffic_bytes'], 'profiles/r01b_traffic.json (ncu --set full, dram read + write per launch)'
+            traffic, traffic_src = tj[top[0]]['traffic_bytes'], 'profiles/r02_traffic.json (ncu --set full, dram read + write per launch)'
     except (OSError, ValueError):
         pass
     roofline = dict(kernel=top[0], bound=bound, achieved=ach, peak=peak, unit='GB/s' if bound == 'hbm' else 'TFLOP/s',

@@ -513,6 +513,11 @@ int arcb200_mc_count(const float *vol, int nx, int ny, int nz, float level, int 
 int arcb200_mc_emit(const float *vol, int nx, int ny, int nz, float level, int ascent, const float *spacing, const float *offset,
                     const int32_t *point_blocks, const int32_t *cell_blocks, int32_t *vbase, float *verts, float *normals,
                     int64_t v_cap, int32_t *faces, int64_t f_cap, void *stream);
+/* Mesh components of get_normals / get_face_centers (arcnerf/geometry/mesh.py:88-125, trimesh on the host in the reference): unit
+ * face normals (F, 3) by the right-hand rule, face centres (F, 3), unit vertex normals (V, 3) = normalised sum of the unit
+ * normals of the vertex's faces.  Any output may be NULL. */
+int arcb200_mesh_components(const float *verts, const int32_t *faces, int64_t n_v, int64_t n_f, float *face_normals,
+                            float *face_centers, float *vert_normals, void *stream);
 
 /* ---- narrow dense layers in fp32 (csrc/small_gemm.cu) -------------------------------------------------------------------
  * The SDF network of the NeuS-NGP configuration (32 -> 64 softplus(100) -> 17, weight-normed, GeoNet of

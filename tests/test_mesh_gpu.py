@@ -109,3 +109,39 @@ def test_ngp_density_grid_and_mesh_extraction():
     assert float(v.min()) >= lo[0] - 1e-5 and float(v.max()) <= hi[0] + 1e-5
     rv, rf, _ = M.extract_mesh(grid.cpu().numpy(), level, [(hi[a] - lo[a]) / n for a in range(3)], [hi[a] - lo[a] for a in range(3)])
     assert np.array_equal(f.cpu().numpy(), rf) and np.allclose(v.cpu().numpy(), rv + (np.asarray(lo) + np.asarray(hi)) / 2, atol=1e-6)
+
+
+def test_mesh_components_and_colours():
+    """get_mesh_components (infer_func.py:582-632): face normals / centres / mean vertex normals against numpy, and the colour
+    lookup forward_pts_dir against the oracle's field (fp16 tensor-core path: the tolerance of the field tests)"""
+    from arcnerf_b200.ngp import NGP_DEFAULTS, NGPPipeline, init_params
+    from arcnerf_b200.plugin.mesh import extract_mesh, get_mesh_components
+    from oracle.ngp import NGP_CONFIG, NGPOracle
+    vol, vs, vl = sphere_volume(32, 0.6)
+    v, f, _ = extract_mesh(torch.from_numpy(vol).cuda(), 50.0, vs, vl)
+    vn, fn, fc = get_mesh_components(v, f)
+    vh, fh = v.cpu().numpy().astype(np.float64), f.cpu().numpy()
+    a, b, c = vh[fh[:, 0]], vh[fh[:, 1]], vh[fh[:, 2]]
+    n = np.cross(b - a, c - a)
+    n /= np.linalg.norm(n, axis=1, keepdims=True)
+    assert np.allclose(fn.cpu().numpy(), n, atol=2e-4) and np.allclose(fc.cpu().numpy(), (a + b + c) / 3, atol=1e-6)
+    acc = np.zeros_like(vh)
+    for k in range(3):
+        np.add.at(acc, fh[:, k], n)
+    acc /= np.linalg.norm(acc, axis=1, keepdims=True)
+    assert np.allclose(vn.cpu().numpy(), acc, atol=2e-4)
+    assert (vn.cpu().numpy() * (vh / np.linalg.norm(vh, axis=1, keepdims=True))).sum(1).min() > 0.99      # outward on a sphere
+    # colours
+    params = init_params(dict(NGP_DEFAULTS), seed=5, grid_scale=0.5)
+    pipe = NGPPipeline(max_rays=256, capacity=1 << 16, params={k: t.clone() for k, t in params.items()})
+    comp = pipe.mesh_components(v, f)
+    assert comp['vert_colors'].shape == (v.shape[0], 3) and comp['face_colors'].shape == (f.shape[0], 3)
+    sig, rgb = pipe.forward_pts_dir(v, -vn)
+    # vertex normals are summed with float atomics: two evaluations differ in the last bits, and so do the view directions
+    assert torch.allclose(rgb, comp['vert_colors'], atol=2e-3)
+    assert torch.allclose(sig, pipe.forward_pts(v), rtol=2e-3, atol=1e-4)
+    orc = NGPOracle({k: t.numpy() for k, t in params.items()}, NGP_CONFIG)
+    unit = ((v.cpu().numpy() - orc.aabb[0]) / (orc.aabb[1] - orc.aabb[0])).astype(np.float32)
+    s_ref, c_ref, _ = orc.field(unit, (-vn).cpu().numpy())
+    assert np.allclose(rgb.cpu().numpy(), c_ref.numpy(), atol=4e-3)
+    assert np.allclose(sig.cpu().numpy(), s_ref.numpy(), rtol=2e-2, atol=1e-3)

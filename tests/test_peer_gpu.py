@@ -105,14 +105,19 @@ def test_peer_barrier_single_rank_and_timeout():
 
 
 def _two_rank_worker(rank, world, port, out_dir, one_device):
-    """one_device: both ranks on GPU 0 (a 1-GPU lease).  Two processes can IPC-map each other's arenas on one device and the
-    GPU time-slices their kernels, so the arena mapping, the flag barriers and both peer exchange modes run exactly as on
-    two GPUs; only NCCL refuses two ranks on one device, so the process group (handle exchange, the all-reduce of the
-    checked alternative) is gloo there."""
+    """one_device: both ranks on GPU 0 (a 1-GPU lease).  Two processes can IPC-map each other's arenas on one device, so the
+    arena mapping and both peer exchange kernels (loads from / stores to the other process's arena) run as on two GPUs.  Two
+    things differ there: NCCL refuses two ranks on one device, so the process group (handle exchange, the all-reduce of the
+    checked alternative) is gloo; and the GPU time-slices the two processes, so a kernel spinning on the other rank's flag is
+    not guaranteed to make progress - the flag barrier is replaced by stream-synchronise + host barrier
+    (ARCB200_PEER_HOST_BARRIER).  The flag-barrier kernel itself is covered by test_peer_barrier_single_rank_and_timeout and,
+    on a box with two GPUs, by this test."""
     import torch.distributed as dist
     os.environ['MASTER_ADDR'], os.environ['MASTER_PORT'] = '127.0.0.1', str(port)
     os.environ.setdefault('ARCB200_PEER_TIMEOUT_MS', '30000')       # a stuck barrier fails the test instead of hanging it
     dev = 0 if one_device else rank
+    if one_device:
+        os.environ['ARCB200_PEER_HOST_BARRIER'] = '1'
     torch.cuda.set_device(dev)
     if one_device:
         dist.init_process_group('gloo', rank=rank, world_size=world)
