@@ -67,6 +67,7 @@ _SIGS = {
     'arcb200_adam_step': [P, P, P, P, P, L, I, F, F, F, F, F, F, I, P, P],
     'arcb200_counter_add': [P, I, P],
     'arcb200_fill_f32': [P, F, L, P],
+    'arcb200_scale_f32': [P, F, L, P],
     'arcb200_huber_loss': [P, P, F, F, P, P, L, P],
     'arcb200_mlp_adam_pack': [I, P, P, P, P, P, I, P, I, F, F, F, F, F, F, I, P, P],
     'arcb200_freq_embed_fwd': [P, I, P, I, I, P, L, L, P],

@@ -53,6 +53,11 @@ __global__ void fill_f32_kernel(float *dst, float value, size_t n) {
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = value;
 }
 
+__global__ void scale_f32_kernel(float *x, float a, size_t n) {
+    arc_pdl_sync();
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) x[i] *= a;
+}
+
 // loss_sum[0] += weight/(3R) * sum huber(rgb - target);  g_rgb = d loss / d rgb
 __global__ void huber_kernel(uint32_t n_elem, const float *__restrict__ rgb, const float *__restrict__ target,
                              float delta, float scale, float *__restrict__ g_rgb, float *__restrict__ loss_sum) {
@@ -125,6 +130,18 @@ int arcb200_fill_f32(float *dst, float value, int64_t n, void *stream) {
     const long long cap = (long long)arc_sm_count() * 8;
     if (blocks > cap) blocks = cap;
     arc_launch(fill_f32_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, dst, value, (size_t)n);
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// x[0..n) *= a on the stream (density -> opacity = density * dt of the occupancy refresh, base_3d_model.py:368-389)
+int arcb200_scale_f32(float *x, float a, int64_t n, void *stream) {
+    ARC_REQUIRE(n >= 0 && (x || n == 0), "scale_f32: bad argument");
+    if (n == 0) return ARCB200_OK;
+    long long blocks = (n + 255) / 256;
+    const long long cap = (long long)arc_sm_count() * 8;
+    if (blocks > cap) blocks = cap;
+    arc_launch(scale_f32_kernel, (unsigned)blocks, 256, 0, (cudaStream_t)stream, x, a, (size_t)n);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }

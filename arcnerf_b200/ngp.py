@@ -382,7 +382,9 @@ class NGPPipeline:
     @torch.no_grad()
     def get_est_opacity(self, dt, pts):
         """base_3d_model.py:368-389: opacity = density * dt (the instant-ngp convention)"""
-        return self.forward_pts(pts) * dt
+        out = self.forward_pts(pts)
+        _lib.call('arcb200_scale_f32', out.data_ptr(), float(dt), out.numel(), _lib.current_stream())
+        return out
 
     def attach_bound(self, bound):
         """Use an object bound (plugin/obj_bound.py VolumeBound) as the owner of the occupancy state; its bool volume is
@@ -644,7 +646,8 @@ class NGPPipeline:
         def close():
             ar.barrier()
             if half:
-                self.g_all[nt:].zero_()          # the heads' gradients (40 KB); the table part was cleared on the way
+                heads = self.g_all[nt:]          # the heads' gradients (40 KB); the table part was cleared on the way
+                _lib.call('arcb200_fill_f32', heads.data_ptr(), 0.0, heads.numel(), _lib.current_stream())
             else:
                 self.g_all.zero_()
         self._run('peer_barrier+clear', close)

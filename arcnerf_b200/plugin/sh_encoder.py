@@ -31,4 +31,6 @@ class SHEmbedder(nn.Module):
         with torch.no_grad():
             sh = F.sh_forward(xyz.detach().contiguous().float(), self.n_freqs, remap=True,
                               out_dtype=torch.float16).to(self.dtype)
+        # include_input is False in every NGP / NeuS-NGP configuration (configs/models/nerf_ngp.yaml:56); the concatenation of the
+        # raw direction is the one torch op of this module and stays off the hot path
         return torch.cat([xyz, sh], dim=-1) if self.include_input else sh

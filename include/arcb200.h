@@ -343,6 +343,8 @@ int arcb200_adam_step(float *p, float *m, float *v, float *g, void *p_half, int6
 int arcb200_counter_add(int32_t *counter, int value, void *stream);
 /* dst[0..n) = value on the stream (clears accumulators such as the loss; no counterpart in the reference, where torch does it). */
 int arcb200_fill_f32(float *dst, float value, int64_t n, void *stream);
+/* x[0..n) *= a  (opacity = density * dt in the occupancy refresh, arcnerf/models/base_3d_model.py:368-389) */
+int arcb200_scale_f32(float *x, float a, int64_t n, void *stream);
 /* Adam + fp16 operand re-packing of n_mlps (<= 4) small networks in ONE launch (per network: arcb200_adam_step followed
  * by arcb200_mlp_pack_weights).  Reference: torch.optim.Adam on tcnn's `params` (common/trainer/optimizer.py) and tcnn's
  * fp32->fp16 parameter cast at the next forward (tinycudann/modules.py:156).  shapes: host int[n_mlps*4] = in_dim,
