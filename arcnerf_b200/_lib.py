@@ -55,6 +55,7 @@ _SIGS = {
     'arcb200_mlp_bwd_ex': [P, I, L, P, I, I, I, I, I, I, P, L, F, P, I, L, P, P, P, I, L, P, P, I, L, F, L, P, P],
     'arcb200_mlp_bwd': [P, I, L, P, I, I, I, I, I, I, P, L, F, P, I, L, P, L, P, P],
     'arcb200_composite_fwd': [P, I, L, P, P, I, P, P, P, I, I, P, I, P, P, P, P, P, P, L, P],
+    'arcb200_composite_fwd_ex': [P, I, L, P, P, I, P, P, P, I, I, P, I, P, P, P, P, P, P, P, L, P],
     'arcb200_composite_bwd': [P, I, L, P, P, I, P, P, P, I, I, P, I, P, P, P, P, P, P, I, L, P],
     'arcb200_composite_huber_train': [P, I, L, P, P, P, P, P, I, I, P, I, P, F, F, P, P, P, P, P, P, I, L, P],
     'arcb200_sdf_to_alpha': [P, P, P, P, F, I, P, L, I, P],

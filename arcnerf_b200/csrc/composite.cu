@@ -98,7 +98,8 @@ composite_fwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
                      const float *__restrict__ rad, const float *__restrict__ t, const float *__restrict__ noise,
                      int add_inf_z, int white_bkg, const float *__restrict__ bkg, int bkg_per_ray,
                      float *__restrict__ rgb, float *__restrict__ depth, float *__restrict__ acc_out,
-                     float *__restrict__ w_out, float *__restrict__ trans_out, float *__restrict__ alpha_out) {
+                     float *__restrict__ w_out, float *__restrict__ trans_out, float *__restrict__ alpha_out,
+                     float *__restrict__ t_last_out) {
     arc_pdl_sync();
     const uint32_t ray = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31u;
@@ -160,6 +161,7 @@ composite_fwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
         }
         if (depth) depth[ray] = ad;
         if (acc_out) acc_out[ray] = aw;
+        if (t_last_out) t_last_out[ray] = t_bkg;
     }
 }
 
@@ -277,6 +279,7 @@ composite_bwd_kernel(uint32_t n_rays, const int32_t *__restrict__ offsets, int32
         if (d_rad) { d_rad[3 * s] = 0.f; d_rad[3 * s + 1] = 0.f; d_rad[3 * s + 2] = 0.f; }
     }
 }
+
 
 // ------------------------------------------------------------------------------------------------ fused training pass
 // Forward compositing, the Huber image loss of the ray and the backward in ONE kernel (density input, radiance given):
@@ -520,11 +523,13 @@ extern "C" {
 //   rad (N,3) or NULL; noise (N) or NULL; bkg (n_rays,3) if bkg_per_ray else (1,3), or NULL
 //   outputs: rgb (n_rays,3) (NULL allowed when rad is NULL), depth, acc (n_rays); per-sample w/trans/alpha or NULL
 // Replaces ray_marching + alpha_to_weights (arcnerf/render/ray_helper.py:476-620).
-int arcb200_composite_fwd(const int32_t *offsets, int dense_p, int64_t capacity, const int32_t *pmax_dev,
-                          const float *geo, int is_alpha, const float *rad, const float *t, const float *noise,
-                          int add_inf_z, int white_bkg, const float *bkg, int bkg_per_ray, float *rgb, float *depth,
-                          float *acc, float *w_out, float *trans_out, float *alpha_out, int64_t n_rays,
-                          void *stream) {
+//   arcb200_composite_fwd_ex: + t_last_out (n_rays) or NULL = the transmittance the background is weighted with, the
+//   reference's trans_shift[:, -1] (what FullModel.blend_bkg_rgb multiplies the background model's colour and depth by)
+int arcb200_composite_fwd_ex(const int32_t *offsets, int dense_p, int64_t capacity, const int32_t *pmax_dev,
+                             const float *geo, int is_alpha, const float *rad, const float *t, const float *noise,
+                             int add_inf_z, int white_bkg, const float *bkg, int bkg_per_ray, float *rgb, float *depth,
+                             float *acc, float *w_out, float *trans_out, float *alpha_out, float *t_last_out, int64_t n_rays,
+                             void *stream) {
     ARC_REQUIRE(n_rays >= 0 && n_rays < (1ll << 27), "composite_fwd: n_rays out of range");
     if (n_rays == 0) return ARCB200_OK;
     ARC_REQUIRE(geo && t, "composite_fwd: null input");
@@ -535,13 +540,22 @@ int arcb200_composite_fwd(const int32_t *offsets, int dense_p, int64_t capacity,
     if (is_alpha)
         arc_launch(composite_fwd_kernel<true>, blocks, 256, 0, st, (uint32_t)n_rays, offsets, dense_p, capacity, pmax_dev, geo, rad,
                                                            t, noise, add_inf_z, white_bkg, bkg, bkg_per_ray, rgb, depth,
-                                                           acc, w_out, trans_out, alpha_out);
+                                                           acc, w_out, trans_out, alpha_out, t_last_out);
     else
         arc_launch(composite_fwd_kernel<false>, blocks, 256, 0, st, (uint32_t)n_rays, offsets, dense_p, capacity, pmax_dev, geo, rad,
                                                             t, noise, add_inf_z, white_bkg, bkg, bkg_per_ray, rgb, depth,
-                                                            acc, w_out, trans_out, alpha_out);
+                                                            acc, w_out, trans_out, alpha_out, t_last_out);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
+}
+
+int arcb200_composite_fwd(const int32_t *offsets, int dense_p, int64_t capacity, const int32_t *pmax_dev,
+                          const float *geo, int is_alpha, const float *rad, const float *t, const float *noise,
+                          int add_inf_z, int white_bkg, const float *bkg, int bkg_per_ray, float *rgb, float *depth,
+                          float *acc, float *w_out, float *trans_out, float *alpha_out, int64_t n_rays,
+                          void *stream) {
+    return arcb200_composite_fwd_ex(offsets, dense_p, capacity, pmax_dev, geo, is_alpha, rad, t, noise, add_inf_z, white_bkg, bkg,
+                                    bkg_per_ray, rgb, depth, acc, w_out, trans_out, alpha_out, nullptr, n_rays, stream);
 }
 
 // Backward: d_geo (N) and d_rad (N,3 or NULL) from g_rgb (n_rays,3), g_depth, g_acc (n_rays) and g_w (N), each

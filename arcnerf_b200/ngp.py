@@ -251,6 +251,7 @@ class NGPPipeline:
         self.rad_in = torch.zeros((C, self.rad_in_dim), dtype=f16, device=dev)
         self.sigma, self.rgb_s = e((C,), f32), e((C, 3), f32)
         self.rgb, self.depth, self.acc = e((R, 3), f32), e((R,), f32), e((R,), f32)
+        self.t_last = e((R,), f32)          # transmittance the background is weighted with (trans_shift[:, -1])
         self.g_rgb = e((R, 3), f32)
         self.d_sigma, self.d_rgb_s = torch.zeros((C,), dtype=f32, device=dev), torch.zeros((C, 3), dtype=f32, device=dev)
         self.d_rad_in = e((C, self.rad_in_dim), f32)
@@ -514,10 +515,10 @@ class NGPPipeline:
     def composite(self, R, bkg):
         bkg_per_ray = int(bkg is not None and bkg.shape[0] == R and R > 1)
         self._run('composite_fwd', lambda: _lib.call(
-            'arcb200_composite_fwd', self.offsets.data_ptr(), 0, self.capacity, self.pmax.data_ptr(),
+            'arcb200_composite_fwd_ex', self.offsets.data_ptr(), 0, self.capacity, self.pmax.data_ptr(),
             self.sigma.data_ptr(), 0, self.rgb_s.data_ptr(), self.t.data_ptr(), None, 0, 0, _lib.ptr(bkg),
-            bkg_per_ray, self.rgb.data_ptr(), self.depth.data_ptr(), self.acc.data_ptr(), None, None, None, R,
-            _lib.current_stream()))
+            bkg_per_ray, self.rgb.data_ptr(), self.depth.data_ptr(), self.acc.data_ptr(), None, None, None,
+            self.t_last.data_ptr(), R, _lib.current_stream()))
 
     def forward(self, rays_o, rays_d, bkg=None, next_rays=None):
         """-> rgb (R,3), depth (R,), mask (R,) views of the pipeline's output buffers.
@@ -559,15 +560,16 @@ class NGPPipeline:
             _lib.call('arcb200_counter_add', self.step_dev.data_ptr(), 1, _lib.current_stream())
         kw = dict(beta1=cfg['beta1'], beta2=cfg['beta2'], eps=cfg['eps'], weight_decay=cfg['weight_decay'], grad_scale=gs,
                   step_dev=self.step_dev)
-        self._run('adam_table', lambda: F.adam_step(self.table, self.m_table, self.v_table, self.g_table, self.step_count,
-                                                    cfg['lr'], p_half=self.table_h, **kw))
-
         if getattr(self, '_mlp_opt', None) is None:
             self._mlp_opt = F.MlpAdamPack((self.geo_spec, self.rad_spec), (self.geo_p, self.rad_p), (self.m_geo, self.m_rad),
                                           (self.v_geo, self.v_rad), (self.g_geo, self.g_rad), (self.geo_blob, self.rad_blob))
 
         def mlp_update():
             self._mlp_opt.step(self.step_count, cfg['lr'], **kw)
+
+        def table_update():
+            F.adam_step(self.table, self.m_table, self.v_table, self.g_table, self.step_count, cfg['lr'], p_half=self.table_h, **kw)
+        self._run('adam_table', table_update)
         self._run('adam_mlp+pack', mlp_update)
 
     def train_step(self, rays_o, rays_d, target, bkg=None, optimize=True, next_rays=None):

@@ -31,13 +31,14 @@ class _RenderFn(torch.autograd.Function):
         rgb, depth, mask = pipe.forward(rays_o, rays_d, bkg)
         ctx.model, ctx.R, ctx.bkg, ctx.rays_d = model, R, bkg, rays_d
         ctx.set_key = pipe.forward_serial            # counts every sample() of the pipeline: two alternating sets would alias
-        mask = mask.clone()
+        t_last = pipe.t_last[:R].clone()
         # a background MODEL behind this foreground (FullModel: bkg is its colour per ray) receives d rgb / d bkg = T_last
-        ctx.trans_last = (1.0 - mask) if bkg.requires_grad else None
-        return rgb.clone(), depth.clone(), mask, pipe.counts[:R].clone()
+        ctx.trans_last = t_last if bkg.requires_grad else None
+        ctx.mark_non_differentiable(t_last)
+        return rgb.clone(), depth.clone(), mask.clone(), pipe.counts[:R].clone(), t_last
 
     @staticmethod
-    def backward(ctx, g_rgb, g_depth, g_mask, _g_counts):
+    def backward(ctx, g_rgb, g_depth, g_mask, _g_counts, _g_t_last):
         pipe, R = ctx.model.pipe, ctx.R
         if ctx.set_key != pipe.forward_serial:
             raise RuntimeError('backward through a chunk whose samples were overwritten by a later forward: '
@@ -169,10 +170,11 @@ class NGPFgModel(nn.Module):
                     with torch.no_grad():
                         self._sync_if_changed()
                         r, d, m = self.pipe.forward(rays_o[s:e], rays_d[s:e], b)
-                        outs.append((r.clone(), d.clone(), m.clone(), self.pipe.counts[:e - s].clone()))
+                        outs.append((r.clone(), d.clone(), m.clone(), self.pipe.counts[:e - s].clone(), self.pipe.t_last[:e - s].clone()))
         finally:
             self.pipe.training = was_training
-        rgb, depth, mask, counts = (torch.cat([o[k] for o in outs], 0) if len(outs) > 1 else outs[0][k] for k in range(4))
+        rgb, depth, mask, counts, t_last = (torch.cat([o[k] for o in outs], 0) if len(outs) > 1 else outs[0][k] for k in range(5))
+        self.last_trans = t_last             # trans_shift[:, -1] of the reference: what FullModel blends a background model with
         # rays without samples: composite already returned T=1 * bkg for the colour; depth takes the far default
         depth = torch.where(counts > 0, depth, torch.full_like(depth, self.depth_far))
         suffix = '' if inference_only else '_coarse'

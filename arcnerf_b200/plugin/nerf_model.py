@@ -221,8 +221,10 @@ class FullModel(nn.Module):
     def _fg_over_bkg_fused(self, flat_inputs, inference_only, cur_epoch, total_epoch):
         """The packed NGP foreground (plugin/fg_model.py) keeps no per-sample progress tensors; the same blend
         rgb = rgb_fg + T_last * rgb_bkg (blend_bkg_rgb, full_model.py:310-330) is evaluated by its compositing kernel when the
-        background model's colour is handed in as the per-ray background colour.  T_last = 1 - mask (the weights sum to 1 - T).
-        The background model runs first; its gradient arrives through d rgb / d bkg = T_last."""
+        background model's colour is handed in as the per-ray background colour; T_last (the reference's trans_shift[:, -1], which
+        leaves the last weighted interval out) comes back from the kernel for the depth blend.  The background model runs first;
+        its gradient arrives through d rgb / d bkg = T_last.  The depth blend carries no gradient to the foreground through T_last
+        (depth is not part of any loss of the reference's configurations)."""
         bkg = self.bkg_model(flat_inputs, inference_only, False, cur_epoch, total_epoch)
         b_rgb = bkg.get('rgb_fine', bkg.get('rgb_coarse', bkg.get('rgb')))
         b_depth = bkg.get('depth_fine', bkg.get('depth_coarse', bkg.get('depth')))
@@ -231,7 +233,7 @@ class FullModel(nn.Module):
         out = dict(fg)
         for suffix in ('', '_coarse'):
             if 'depth' + suffix in fg:
-                out['depth' + suffix] = fg['depth' + suffix] + (1.0 - fg['mask' + suffix]) * b_depth
+                out['depth' + suffix] = fg['depth' + suffix] + self.fg_model.last_trans * b_depth
         return out
 
     def forward(self, inputs, inference_only=False, get_progress=False, cur_epoch=0, total_epoch=300000):

@@ -285,6 +285,13 @@ int arcb200_composite_fwd(const int32_t *offsets, int dense_p, int64_t capacity,
                           int add_inf_z, int white_bkg, const float *bkg, int bkg_per_ray, float *rgb, float *depth,
                           float *acc, float *w_out, float *trans_out, float *alpha_out, int64_t n_rays,
                           void *stream);
+/* The same with one more output: t_last_out (n_rays) or NULL, the transmittance that weights the background - the reference's
+ * trans_shift[:, -1], which FullModel.blend_bkg_rgb multiplies the background model's colour and depth with
+ * (arcnerf/models/full_model.py:296-330). */
+int arcb200_composite_fwd_ex(const int32_t *offsets, int dense_p, int64_t capacity, const int32_t *pmax_dev, const float *geo,
+                             int is_alpha, const float *rad, const float *t, const float *noise, int add_inf_z, int white_bkg,
+                             const float *bkg, int bkg_per_ray, float *rgb, float *depth, float *acc, float *w_out,
+                             float *trans_out, float *alpha_out, float *t_last_out, int64_t n_rays, void *stream);
 /* Gradient of the above (the reference uses autograd through ~15 eager ops): d_geo (N), d_rad (N,3) or NULL from
  * g_rgb (n_rays,3), g_depth, g_acc (n_rays), g_w (N), each optional.  max_samples_per_ray <= 4096. */
 int arcb200_composite_bwd(const int32_t *offsets, int dense_p, int64_t capacity, const int32_t *pmax_dev,

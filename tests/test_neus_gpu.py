@@ -26,7 +26,9 @@ CFG = dict(
 
 
 def build(seed=0, table_scale=0.05):
+    from arcnerf_b200.plugin import volume_func
     from arcnerf_b200.plugin.neus_model import Neus
+    volume_func.reset_rng()                   # the module-level sampler generator (common.h:21-23) as after a fresh import
     torch.manual_seed(seed)
     model = Neus(CFG)
     with torch.no_grad():                     # a non-trivial hash table so that the SDF varies in space
