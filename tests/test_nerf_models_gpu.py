@@ -101,8 +101,16 @@ def test_ngp_foreground_over_nerfpp_background_blend_and_gradients():
     o, d = mc.rays(300, seed=9)
     feed = {'rays_o': torch.from_numpy(o).cuda()[None], 'rays_d': torch.from_numpy(d).cuda()[None]}
     flat = {k: v[0] for k, v in feed.items()}
+    from arcnerf_b200 import _lib
+
+    def same_jitter():                       # the march jitters its start at inference too: same generator state for every render
+        fg.pipe.rng = _lib.Rng()
+        for ss in fg.pipe.sets:
+            ss.key = None
     with torch.no_grad():
+        same_jitter()
         out = model(feed, inference_only=True)
+        same_jitter()
         black = fg(dict(flat, bkg_color=torch.zeros((1, 3), device='cuda')), inference_only=True)
         b = bkg(flat, inference_only=True)
     T = fg.last_trans.clone()                # the reference's trans_shift[:, -1] (leaves the last weighted interval out)
@@ -114,6 +122,7 @@ def test_ngp_foreground_over_nerfpp_background_blend_and_gradients():
     # training pass: gradients of the background nets through the fused blend == through the explicit blend
     w = torch.rand((300, 3), generator=torch.Generator().manual_seed(2)).cuda()
     model.zero_grad()
+    same_jitter()
     trn = model(feed)
     (trn['rgb_coarse'][0] * w).sum().backward()
     got = {k: p.grad.clone() for k, p in bkg.named_parameters() if p.grad is not None}
