@@ -145,3 +145,25 @@ def test_mesh_components_and_colours():
     s_ref, c_ref, _ = orc.field(unit, (-vn).cpu().numpy())
     assert np.allclose(rgb.cpu().numpy(), c_ref.numpy(), atol=4e-3)
     assert np.allclose(sig.cpu().numpy(), s_ref.numpy(), rtol=2e-2, atol=1e-3)
+
+
+def test_slab_sharded_extraction_tiles_the_whole_mesh():
+    """mesh extraction sharded by x slabs (bench config 'mesh', dist.shard_range): the cells of the slabs tile the lattice, so the
+    slab meshes together have the faces of the whole-lattice mesh, and every slab vertex is a vertex of the whole mesh"""
+    from arcnerf_b200 import dist as adist
+    from arcnerf_b200.ngp import NGP_DEFAULTS, NGPPipeline, init_params
+    pipe = NGPPipeline(max_rays=256, capacity=1 << 16, params=init_params(dict(NGP_DEFAULTS), seed=7, grid_scale=1.0))
+    n = 40
+    level = float(pipe.density_grid(n).median())
+    v, f, _ = pipe.extract_mesh(n, level=level)
+    whole = {tuple(np.round(p, 5)) for p in v.cpu().numpy()}
+    n_faces, world = 0, 3
+    for rank in range(world):
+        x0, x1 = adist.shard_range(n, rank, world)
+        vs_, fs_, _ = pipe.extract_mesh(n, level=level, x_range=(x0, x1))
+        n_faces += fs_.shape[0]
+        part = {tuple(np.round(p, 5)) for p in vs_.cpu().numpy()}
+        assert part <= whole
+        if fs_.shape[0]:
+            assert int(fs_.max()) < vs_.shape[0]
+    assert n_faces == f.shape[0] and f.shape[0] > 0
