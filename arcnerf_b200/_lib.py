@@ -101,6 +101,12 @@ _SIGS = {
     'arcb200_mc_count': [P, I, I, I, F, I, P, P, P],
     'arcb200_mc_emit': [P, I, I, I, F, I, P, P, P, P, P, P, P, L, P, L, P],
     'arcb200_mesh_components': [P, P, L, L, P, P, P, P],
+    'arcb200_trace_update': [P, P, P, P, P, I, P, P, F, L, P],
+    'arcb200_surface_finish': [P, P, P, P, I, P, L, P],
+    'arcb200_secant_steps': [P, P, P, P, I, I, P, P, L, P],
+    'arcb200_secant_init': [P, P, I, F, I, P, P, P, P, P, P, P, P, P, I, L, P],
+    'arcb200_secant_update': [P, F, I, P, P, P, P, P, P, P, F, P, I, I, L, P],
+    'arcb200_secant_select': [P, P, P, P, I, P, L, P],
     'arcb200_gemm_nt': [P, L, P, L, P, P, L, L, I, I, P],
     'arcb200_gemm_tn': [P, L, P, L, P, L, L, I, I, P],
     'arcb200_softplus': [P, F, I, P, L, P],

@@ -38,6 +38,7 @@ SOURCES = {
     'raygen.cu': ['-fmad=false'],
     'small_gemm.cu': [],
     'mcubes.cu': ['-fmad=false'],
+    'surface.cu': ['-fmad=false'],
 }
 
 

@@ -170,6 +170,34 @@ class Neus(nn.Module):
         radiance = self.radiance_net(pts, rays_d, normal, feat)
         return sdf[..., 0], radiance, normal
 
+    def surface_render(self, inputs, method='sphere_tracing', n_step=128, n_iter=20, threshold=0.01, level=0.0, grad_dir='ascent'):
+        """SdfModel.surface_render (sdf_model.py:116-171): the first surface point of every ray by sphere tracing or the secant
+        method on the SDF network (plugin/surface.py: no host synchronisation inside the search), then colour and normal from the
+        networks at that point.  Returns rgb (B,3) (white where nothing is hit), depth (B,1), mask (B,), normal (B,3)."""
+        from .surface import surface_ray_intersection
+        assert level == 0.0, 'Invalid level for sdf model...'
+        assert grad_dir == 'ascent', 'Invalid grad_dir for sdf model...'
+        rays_o, rays_d = inputs['rays_o'].float().contiguous(), inputs['rays_d'].float().contiguous()
+        n_rays, dev = rays_o.shape[0], rays_o.device
+        with torch.no_grad():
+            near, far, valid_rays = self.obj_bound.get_near_far_from_rays({'rays_o': rays_o, 'rays_d': rays_d})
+        geo_value = self.geo_net.forward_geo_value
+        if valid_rays is None or bool(torch.all(valid_rays)):
+            zvals, pts, mask = surface_ray_intersection(rays_o, rays_d, geo_value, method, near, far, n_step, n_iter, threshold, level, grad_dir)
+        else:
+            zv, pv, mv = surface_ray_intersection(rays_o[valid_rays], rays_d[valid_rays], geo_value, method, near[valid_rays],
+                                                  far[valid_rays], n_step, n_iter, threshold, level, grad_dir)
+            zvals = torch.ones((n_rays, 1), dtype=torch.float32, device=dev) * (zv.max() if zv.numel() else 0.0)
+            pts = torch.ones((n_rays, 3), dtype=torch.float32, device=dev)
+            mask = torch.zeros((n_rays, ), dtype=torch.bool, device=dev)
+            zvals[valid_rays], pts[valid_rays], mask[valid_rays] = zv, pv, mv
+        rgb = torch.ones((n_rays, 3), dtype=torch.float32, device=dev)                  # white bkg
+        normal = torch.zeros((n_rays, 3), dtype=torch.float32, device=dev)
+        if bool(torch.any(mask)):
+            _, rgb_m, normal_m = self._forward_pts_dir(pts[mask], rays_d[mask])
+            rgb[mask], normal[mask] = rgb_m.detach().float(), normal_m.detach().float()
+        return {'rgb': rgb, 'depth': zvals, 'mask': mask.float(), 'normal': normal}
+
     def _forward(self, rays_o, rays_d, zvals, mask_pts, bkg_color, inference_only, get_progress, cur_epoch):
         mid_zvals, zvals, mask_mid = self.handle_mid_pts(zvals, mask_pts)
         sdf, radiance, normal_pts = self.get_sdf_radiance_normal_by_mask_pts(rays_o, rays_d, mid_zvals, mask_mid)

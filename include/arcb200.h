@@ -528,6 +528,31 @@ int arcb200_mc_emit(const float *vol, int nx, int ny, int nz, float level, int a
 int arcb200_mesh_components(const float *verts, const int32_t *faces, int64_t n_v, int64_t n_f, float *face_normals,
                             float *face_centers, float *vert_normals, void *stream);
 
+/* ---- surface-ray intersection (csrc/surface.cu) -------------------------------------------------------------------------
+ * The per-ray state machines of arcnerf/geometry/ray.py:403-601 around the caller's field evaluation; no host synchronisation
+ * inside the loops (the reference's `torch.all(...)` early exits become device-side counters).  near / far: (n_rays) when
+ * near_far_per_ray, else one value.  mask / obj / not_occ: uint8 per ray.
+ * sphere_tracing (:403-467): zvals = near, mask = 1, obj = 0, sdf = 0; repeat n_iter times { pts = arcb200_ray_points(zvals);
+ *   sdf_new = field(pts); arcb200_trace_update }; arcb200_surface_finish (zvals <= near -> 0, pts).
+ * secant_root_finding (:470-601): arcb200_secant_steps (uniform scan + its points) -> geo = field(pts) -> arcb200_secant_init
+ *   (bracket of the first + -> - sign change, first estimate; clears flags, n_iter + 1 int32) -> repeat for it = 0..n_iter-1
+ *   { pts = arcb200_ray_points(z_mid); arcb200_secant_update } -> arcb200_secant_select -> arcb200_surface_finish.
+ *   As in the reference, only the low end of the bracket ever moves (`~ind_low.sum() > 0` never holds, ray.py:571). */
+int arcb200_trace_update(const float *sdf_new, float *zvals, float *sdf, const float *near, const float *far, int near_far_per_ray,
+                         uint8_t *mask, uint8_t *obj, float threshold, int64_t n_rays, void *stream);
+int arcb200_surface_finish(const float *rays_o, const float *rays_d, float *zvals, const float *near, int near_per_ray, float *pts,
+                           int64_t n_rays, void *stream);
+int arcb200_secant_steps(const float *rays_o, const float *rays_d, const float *near, const float *far, int near_far_per_ray,
+                         int n_step, float *step, float *pts, int64_t n_rays, void *stream);
+int arcb200_secant_init(const float *geo, const float *step, int n_step, float level, int descent, uint8_t *not_occ, uint8_t *mask,
+                        float *z_high, float *z_low, float *g_high, float *g_low, float *z_mid, float *z_mid_init, int32_t *flags,
+                        int n_iter, int64_t n_rays, void *stream);
+int arcb200_secant_update(const float *geo_mid, float level, int descent, const uint8_t *mask, float *z_low, float *g_low,
+                          const float *z_high, const float *g_high, float *z_mid, const float *z_mid_init, float threshold,
+                          int32_t *flags, int it, int n_iter, int64_t n_rays, void *stream);
+int arcb200_secant_select(const uint8_t *mask, const uint8_t *not_occ, const float *z_mid, const float *far, int far_per_ray,
+                          float *zvals, int64_t n_rays, void *stream);
+
 /* ---- narrow dense layers in fp32 (csrc/small_gemm.cu) -------------------------------------------------------------------
  * The SDF network of the NeuS-NGP configuration (32 -> 64 softplus(100) -> 17, weight-normed, GeoNet of
  * geo_rad_model/linear_network_module.py:17-197 with DenseLayer = nn.Linear + activation, base_modules/linear.py) and the

@@ -156,14 +156,15 @@ def test_slab_sharded_extraction_tiles_the_whole_mesh():
     n = 40
     level = float(pipe.density_grid(n).median())
     v, f, _ = pipe.extract_mesh(n, level=level)
-    whole = {tuple(np.round(p, 5)) for p in v.cpu().numpy()}
+    from scipy.spatial import cKDTree
+    whole = cKDTree(v.cpu().numpy())
     n_faces, world = 0, 3
     for rank in range(world):
         x0, x1 = adist.shard_range(n, rank, world)
         vs_, fs_, _ = pipe.extract_mesh(n, level=level, x_range=(x0, x1))
         n_faces += fs_.shape[0]
-        part = {tuple(np.round(p, 5)) for p in vs_.cpu().numpy()}
-        assert part <= whole
+        if vs_.shape[0]:                     # the slab's x positions are offset after the kernel: equal to fp32 rounding
+            assert whole.query(vs_.cpu().numpy())[0].max() < 1e-5
         if fs_.shape[0]:
             assert int(fs_.max()) < vs_.shape[0]
     assert n_faces == f.shape[0] and f.shape[0] > 0
