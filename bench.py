@@ -401,13 +401,14 @@ def main():
         rp.set_occupancy(synth.occupancy_volume('lego'))
         o, d = synth.camera_rays(800, 800, synth.sphere_poses(1, seed=5)[0])
         n_all = o.shape[0]
-        per = (n_all + world - 1) // world
-        sl = slice(rank * per, min(n_all, (rank + 1) * per))
-        o_d, d_d = torch.from_numpy(o[sl]).to(dev), torch.from_numpy(d[sl]).to(dev)
+        # ray tiles of 256 are dealt round-robin to the ranks: a contiguous split gives the ranks that see the object many more
+        # samples than the ranks that see the border, and the frame time is the slowest rank's
+        from arcnerf_b200.dist import deal_tiles, gather_dealt
+        idx, per = deal_tiles(n_all, rank, world)
+        o_d, d_d = torch.from_numpy(o[idx.numpy()]).to(dev), torch.from_numpy(d[idx.numpy()]).to(dev)
         white = torch.ones((1, 3), device=dev)
-        # the frame is assembled on every rank by ONE all-gather into a preallocated buffer (equal tiles of `per` rays)
-        tile = torch.zeros((per, 3), device=dev)
-        frame = torch.empty((world * per, 3), device=dev) if dist is not None else None
+        # the frame is assembled on every rank by ONE all-gather + one strided copy that un-deals the tiles (dist.gather_dealt)
+        frame = torch.empty((per * world, 3), device=dev) if dist is not None else None
         for _ in range(2):
             rp.render(o_d, d_d, white)
         times = []
@@ -416,8 +417,7 @@ def main():
             e0.record()
             rgb, _, _ = rp.render(o_d, d_d, white)
             if dist is not None:
-                tile[:rgb.shape[0]].copy_(rgb)
-                dist.all_gather_into_tensor(frame, tile)
+                gather_dealt(rgb, n_all, world, out=frame)
             e1.record()
             barrier()
             times.append(max_over_ranks(e0.elapsed_time(e1)))

@@ -205,23 +205,21 @@ def run_mesh(args, rank, world, dev, dist, read_peaks, ClockSampler):
     focal = 0.5 * Wd / np.tan(0.5 * 0.6911112070083618)
     intrinsic = np.array([[focal, 0, Wd / 2], [0, focal, Ht / 2], [0, 0, 1]], np.float32)
     cams = ray_helper.pack_cameras(torch.from_numpy(intrinsic)[None], torch.from_numpy(c2w.astype(np.float32))[None], dev)
-    p0, p1 = adist.shard_range(Wd * Ht, rank, world)
-    per = (Wd * Ht + world - 1) // world
-    pix = torch.arange(p0, p1, device=dev, dtype=torch.int64)             # pixel index i * H + j of this rank's shard
-    cam_id = torch.zeros(p1 - p0, dtype=torch.int32, device=dev)
+    # pixel tiles of 256 dealt round-robin to the ranks (a contiguous split leaves the ranks that see the object with most of the
+    # samples); pixel index i * H + j
+    pix, per = adist.deal_tiles(Wd * Ht, rank, world)
+    pix = pix.to(dev).contiguous()
+    cam_id = torch.zeros(pix.shape[0], dtype=torch.int32, device=dev)
     x0, x1 = adist.shard_range(n_grid, rank, world)
     frame_host = torch.empty((Wd * Ht, 3), dtype=torch.float32).pin_memory() if rank == 0 else None
-    tile = torch.zeros((per, 3), device=dev)
-    frame_dev = torch.empty((world * per, 3), device=dev) if dist is not None else None
+    frame_dev = torch.empty((per * world, 3), device=dev) if dist is not None else None
 
     def frame():
         o, d = ray_helper.get_train_batch_rays(cams, cam_id, pix, Wd, Ht)
         rgb, _, _ = rp.render(o, d, white)
         if dist is None:
             return rgb
-        tile[:rgb.shape[0]].copy_(rgb)
-        dist.all_gather_into_tensor(frame_dev, tile)                     # one collective into the preallocated frame
-        return frame_dev[:Wd * Ht]
+        return adist.gather_dealt(rgb, Wd * Ht, world, out=frame_dev)     # one all-gather + one strided copy that un-deals the tiles
 
     stats = {}
 

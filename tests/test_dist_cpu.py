@@ -6,7 +6,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from arcnerf_b200.dist import all_reduce_sum_, gather_rows, shard_range
+from arcnerf_b200.dist import all_reduce_sum_, deal_tiles, gather_dealt, gather_rows, shard_range
 
 
 def _free_port():
@@ -34,6 +34,10 @@ def _worker(rank, world, port, n_total, q):
             ok = ok and torch.equal(out, full)
         else:
             ok = ok and out is None
+        # round-robin tiles (frame rendering with balanced load), reassembled on every rank
+        idx, per = deal_tiles(n_total, rank, world, tile=16)
+        back = gather_dealt(full[idx].clone(), n_total, world, tile=16)
+        ok = ok and torch.equal(back, full) and per % 16 == 0
         q.put((rank, bool(ok), (s, e)))
     finally:
         dist.destroy_process_group()
@@ -46,6 +50,19 @@ def test_shard_range_partitions():
             assert spans[0][0] == 0 and spans[-1][1] == n
             assert all(a[1] == b[0] for a, b in zip(spans, spans[1:]))
             assert all(0 <= e - s <= (n + world - 1) // world for s, e in spans)
+
+
+def test_deal_tiles_partitions():
+    for n in (1, 255, 256, 1000, 640000, 2073600):
+        for world in (1, 2, 3, 8):
+            parts = [deal_tiles(n, r, world)[0] for r in range(world)]
+            allidx = torch.cat(parts)
+            assert allidx.numel() == n and torch.equal(torch.sort(allidx)[0], torch.arange(n))
+            pers = {deal_tiles(n, r, world)[1] for r in range(world)}
+            assert len(pers) == 1 and max(p.numel() for p in parts) <= next(iter(pers))
+            # balance: no rank has more than one tile more than another
+            sizes = [p.numel() for p in parts]
+            assert max(sizes) - min(sizes) <= 256
 
 
 def test_two_rank_exchange_and_gather():
