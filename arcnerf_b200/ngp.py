@@ -247,6 +247,9 @@ class NGPPipeline:
         self.cur = 0
         self.forward_serial = 0     # number of sample sets made current so far (stale-activation guard of the autograd wrapper)
         self.side_stream = torch.cuda.Stream(device=dev)
+        self.opt_stream = torch.cuda.Stream(device=dev)
+        self._opt_fork, self._opt_join = torch.cuda.Event(), torch.cuda.Event()
+        self.overlap_heads = os.environ.get('ARCB200_OVERLAP_HEADS', '1') == '1'
         self.enc = e((C, self.enc_dim), f16)
         self.rad_in = torch.zeros((C, self.rad_in_dim), dtype=f16, device=dev)
         self.sigma, self.rgb_s = e((C,), f32), e((C, 3), f32)
@@ -624,17 +627,15 @@ class NGPPipeline:
             keep = (0, 0) if mc else (lo, hi)
             self._run('grad_to_half', lambda: grad_to_half(self.g_table, self._g16, keep[0], keep[1], cfg.get('exchange_scale', 128.0)))
         self._run('peer_barrier', ar.barrier)
-        if mc:
-            self._run('adam_table_peer', lambda: adam_step_mc16(ar.mc_pointer('grad16'), ar.mc_pointer('table_h'), lo, hi,
-                                                                self.table, self.m_table, self.v_table, self.step_count,
-                                                                cfg['lr'], scale=cfg.get('exchange_scale', 128.0), **kw))
-        elif half:
-            self._run('adam_table_peer', lambda: adam_step_peer16(self.g_table, self._g16_ptrs, th, W, self.rank, lo, hi,
-                                                                  self.table, self.m_table, self.v_table, self.step_count,
-                                                                  cfg['lr'], scale=cfg.get('exchange_scale', 128.0), **kw))
-        else:
-            self._run('adam_table_peer', lambda: adam_step_peer(g_t, th, W, lo, hi, self.table, self.m_table, self.v_table,
-                                                                self.step_count, cfg['lr'], **kw))
+        def table_update():
+            if mc:
+                adam_step_mc16(ar.mc_pointer('grad16'), ar.mc_pointer('table_h'), lo, hi, self.table, self.m_table, self.v_table,
+                               self.step_count, cfg['lr'], scale=cfg.get('exchange_scale', 128.0), **kw)
+            elif half:
+                adam_step_peer16(self.g_table, self._g16_ptrs, th, W, self.rank, lo, hi, self.table, self.m_table, self.v_table,
+                                 self.step_count, cfg['lr'], scale=cfg.get('exchange_scale', 128.0), **kw)
+            else:
+                adam_step_peer(g_t, th, W, lo, hi, self.table, self.m_table, self.v_table, self.step_count, cfg['lr'], **kw)
 
         if getattr(self, '_mlp_opt_peer', None) is None:
             self._mlp_opt_peer = F.MlpAdamPack((self.geo_spec, self.rad_spec), (self.geo_p, self.rad_p),
@@ -643,7 +644,20 @@ class NGPPipeline:
 
         def mlp_update():
             self._mlp_opt_peer.step(self.step_count, cfg['lr'], zero_grad=False, **kw)
-        self._run('adam_mlp+pack', mlp_update)
+        if self.timer is not None or not self.overlap_heads:
+            self._run('adam_table_peer', table_update)
+            self._run('adam_mlp+pack', mlp_update)
+        else:
+            # the table kernel waits on NVLink, not on SMs: the heads' update (every rank's 40 KB of gradients, one small launch)
+            # runs beside it on a second stream and is joined before the closing barrier
+            main = torch.cuda.current_stream()
+            self._opt_fork.record(main)
+            self.opt_stream.wait_event(self._opt_fork)
+            with torch.cuda.stream(self.opt_stream):
+                mlp_update()
+                self._opt_join.record(self.opt_stream)
+            table_update()
+            main.wait_event(self._opt_join)
 
         def close():
             ar.barrier()

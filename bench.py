@@ -319,15 +319,27 @@ def main():
             pipe.train_step_graphed(host[i], next_batch=host[i + 1])
         barrier()
         e0.record()
+        # the caller reads every step's loss, one step behind: the D2H copy of step i is queued behind step i, and the host waits
+        # for it only after step i + 1 has been queued (a training loop that logs its loss does not need to stall the device for it)
+        loss_slots = [loss_host, torch.empty(1, dtype=torch.float32).pin_memory()]
+        loss_ready = [torch.cuda.Event(), torch.cuda.Event()]
+        losses_read = 0
         for i in range(K):
             nb = host[W + i + 1] if i + 1 < K else None
             loss = pipe.train_step_graphed(host[W + i], next_batch=nb)     # H2D of rays/targets inside
-            loss_host.copy_(loss, non_blocking=True)
+            loss_slots[i % 2].copy_(loss, non_blocking=True)
+            loss_ready[i % 2].record()
             maybe_refresh(i)
-            torch.cuda.current_stream().synchronize()      # the caller reads the loss every step
+            if i > 0:
+                loss_ready[(i - 1) % 2].synchronize()
+                losses_read += int(np.isfinite(float(loss_slots[(i - 1) % 2][0])))
+        loss_ready[(K - 1) % 2].synchronize()
+        losses_read += int(np.isfinite(float(loss_slots[(K - 1) % 2][0])))
+        assert losses_read == K, 'a step produced a non-finite loss'
         e1.record()
         barrier()
-        e2e_mode = 'host pinned buffers -> static device slots (H2D per step) -> sampler on side stream + CUDA graph replay -> loss D2H + sync per step'
+        e2e_mode = ('host pinned buffers -> static device slots (H2D per step) -> sampler on side stream + CUDA graph replay -> loss D2H '
+                    'every step, read by the host one step behind')
     else:
         dbufs = [[torch.empty_like(x, device=dev) for x in host[0]] for _ in range(2)]   # current / next batch
         barrier()

@@ -16,8 +16,9 @@ run() {   # name, env, args...
 }
 for c in $CFGS; do
     case $c in
-        ngp)  run ngp_peer16 ARCB200_EXCHANGE=peer16 --config ngp --steps 200 --warmup 20 --no-cpu-baseline
-              run ngp_mc16 ARCB200_EXCHANGE=mc16 --config ngp --steps 200 --warmup 20 --no-cpu-baseline
+        ngp)  run ngp_peer16 ARCB200_EXCHANGE=peer16 --config ngp --steps 200 --warmup 20 --no-cpu-baseline ;;
+        ngp_variants)
+              run ngp_mc16 ARCB200_EXCHANGE=mc16 --config ngp --steps 200 --warmup 20 --no-cpu-baseline --no-render
               run ngp_nccl ARCB200_EXCHANGE=nccl --config ngp --steps 200 --warmup 20 --no-cpu-baseline --no-render ;;
         nerf) run nerf X=1 --config nerf --steps 20 --warmup 3 --no-cpu-baseline ;;
         neus) run neus X=1 --config neus --steps 20 --warmup 3 ;;
