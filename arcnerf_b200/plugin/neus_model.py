@@ -87,31 +87,36 @@ class Neus(nn.Module):
             near, far, mask_rays = self.obj_bound.get_near_far_from_rays({'rays_o': rays_o, 'rays_d': rays_d})
             zvals, mask_pts = self.obj_bound.get_zvals_from_near_far(near, far, self.ray_cfgs['n_sample'], inference_only,
                                                                      rays_o=rays_o, rays_d=rays_d)
-            max_num_pts = max(2, int(mask_pts.sum(dim=1).max()))                       # reduce_empty_mask (fg_model.py:251-262)
+            # the three data-dependent decisions of FgModel.forward (longest ray, any / all rays valid) in ONE host read
+            per_ray = mask_pts.sum(dim=1)
+            valid0 = torch.logical_and(mask_rays, per_ray > 0)
+            stats = torch.stack([per_ray.max(), valid0.sum()]).tolist()
+            max_num_pts = max(2, int(stats[0]))                                        # reduce_empty_mask (fg_model.py:251-262)
             zvals, mask_pts = zvals[:, :max_num_pts].contiguous(), mask_pts[:, :max_num_pts].contiguous()
-            mask_rays = torch.logical_and(mask_rays, torch.any(mask_pts, dim=1))
-        if bool(torch.all(mask_rays)):
+            mask_rays, n_valid = valid0, int(stats[1])
+        if n_valid == n_rays:
             return self._forward(rays_o, rays_d, zvals, mask_pts, bkg_color, inference_only, get_progress, cur_epoch)
-        empty_batch = int(mask_rays.sum()) == 0
+        empty_batch = n_valid == 0
         if empty_batch:                                   # all rays miss: one synthetic ray gives the output keys (fg_model.py:198-207)
-            mask_rays = mask_rays.clone()
-            mask_rays[0] = True
+            ray_idx = torch.zeros(1, dtype=torch.long, device=zvals.device)
             z_valid = torch.zeros((1, zvals.shape[1]), dtype=zvals.dtype, device=zvals.device)
             z_valid[0, 1:] = 1.0
             m_valid = torch.zeros((1, mask_pts.shape[1]), dtype=torch.bool, device=zvals.device)
             m_valid[0, :2] = True
         else:
-            z_valid, m_valid = zvals[mask_rays], mask_pts[mask_rays]
-        out_valid = self._forward(rays_o[mask_rays], rays_d[mask_rays], z_valid, m_valid,
-                                  bkg_color[mask_rays] if bkg_color is not None else None, inference_only, get_progress, cur_epoch)
-        if empty_batch:
-            mask_rays[0] = False
-        return self.update_values_for_invalid_rays(out_valid, mask_rays, bkg_color, n_rays)
+            # row indices of the valid rays, once; every per-ray tensor is gathered / scattered with them (a boolean mask would
+            # run its own compaction - and a host synchronisation - at every use)
+            ray_idx = torch.nonzero(mask_rays).squeeze(1)
+            z_valid, m_valid = zvals.index_select(0, ray_idx), mask_pts.index_select(0, ray_idx)
+        out_valid = self._forward(rays_o.index_select(0, ray_idx), rays_d.index_select(0, ray_idx), z_valid, m_valid,
+                                  bkg_color.index_select(0, ray_idx) if bkg_color is not None else None, inference_only, get_progress,
+                                  cur_epoch)
+        return self.update_values_for_invalid_rays(out_valid, None if empty_batch else ray_idx, bkg_color, n_rays)
 
-    def update_values_for_invalid_rays(self, out_valid, mask, rand_bkg_color, n_rays):
-        """fg_model.py:320-387: background colour / far depth / zero mask / default normal for the rays that miss the bound"""
+    def update_values_for_invalid_rays(self, out_valid, ray_idx, rand_bkg_color, n_rays):
+        """fg_model.py:320-387: background colour / far depth / zero mask / default normal for the rays that miss the bound.
+        ray_idx: rows of the valid rays (None: no ray was valid, out_valid only supplies keys and shapes)"""
         out = {}
-        n_valid = int(mask.sum())
         for k, v in out_valid.items():
             if not torch.is_tensor(v):
                 out[k] = v
@@ -133,35 +138,40 @@ class Neus(nn.Module):
             else:
                 out[k] = v
                 continue
-            if n_valid:
-                t[mask] = v[:n_valid]
+            if ray_idx is not None:
+                t = t.index_copy(0, ray_idx, v)
             out[k] = t
         return out
 
     # ------------------------------------------------------------------------------------------ Neus._forward
     def handle_mid_pts(self, zvals, mask_pts):
         """neus_model.py:173-202 (the masked branch): interval mid points, one extra interval of the ray's step appended"""
+        n_rays, n_pts = zvals.shape
         sample_dist = (zvals[:, -1] - zvals[:, 0]) / self.ray_cfgs['n_sample'] * 0.5
         final_zvals = zvals[:, -1] + sample_dist * 2.0
-        _zvals = torch.ones((zvals.shape[0], zvals.shape[1] + 1), dtype=zvals.dtype, device=zvals.device) * final_zvals.unsqueeze(1)
-        _mask = torch.cat([mask_pts, torch.zeros_like(mask_pts[:, :1])], dim=1)
-        _zvals[_mask] = zvals[mask_pts]
+        _zvals = (torch.ones((n_rays, n_pts + 1), dtype=zvals.dtype, device=zvals.device) * final_zvals.unsqueeze(1)).contiguous()
+        # _zvals[_mask] = zvals[mask_pts] with _mask = [mask_pts | False]: the same entries, one column wider
+        idx = torch.nonzero(mask_pts.reshape(-1)).squeeze(1)
+        ray = torch.div(idx, n_pts, rounding_mode='floor')
+        _zvals.view(-1).index_copy_(0, idx + ray, zvals.reshape(-1).index_select(0, idx))
         mid_zvals = 0.5 * (_zvals[..., 1:] + _zvals[..., :-1])
         mask_mid = torch.cat([torch.ones_like(mask_pts[:, :1]), mask_pts[:, :-1]], dim=1)
         return mid_zvals, _zvals, mask_mid
 
     def get_sdf_radiance_normal_by_mask_pts(self, rays_o, rays_d, zvals, mask_pts):
-        """sdf_model.py:42-114: networks on the valid points only, results re-expanded with the ray's last valid value"""
+        """sdf_model.py:42-114: networks on the valid points only, results re-expanded with the ray's last valid value.
+        The valid entries are addressed by ONE index tensor (flat position, ray) instead of a boolean mask per tensor."""
         n_rays, n_pts = zvals.shape
         pts = rh.get_ray_points_by_zvals(rays_o, rays_d, zvals)
-        dirs = rays_d[:, None, :].expand(n_rays, n_pts, 3)
-        pts_v, dirs_v = pts[mask_pts].view(-1, 3), dirs[mask_pts].reshape(-1, 3)
+        idx = torch.nonzero(mask_pts.reshape(-1)).squeeze(1)
+        ray = torch.div(idx, n_pts, rounding_mode='floor')
+        pts_v, dirs_v = pts.view(-1, 3).index_select(0, idx), rays_d.index_select(0, ray)
         sdf_v, rad_v, nrm_v = self._forward_pts_dir(pts_v, dirs_v)
         last = torch.cumsum(mask_pts.sum(dim=1), dim=0) - 1
-        sdf = (torch.ones((n_rays, n_pts), dtype=sdf_v.dtype, device=sdf_v.device) * sdf_v[last].unsqueeze(1)).clone()
-        rad = (torch.ones((n_rays, n_pts, 3), dtype=sdf_v.dtype, device=sdf_v.device) * rad_v[last].unsqueeze(1)).clone()
-        nrm = (torch.ones((n_rays, n_pts, 3), dtype=sdf_v.dtype, device=sdf_v.device) * nrm_v[last].unsqueeze(1)).clone()
-        sdf[mask_pts], rad[mask_pts], nrm[mask_pts] = sdf_v, rad_v, nrm_v
+        fill = lambda v, c: (v.index_select(0, last).unsqueeze(1).expand(n_rays, n_pts, *v.shape[1:]).reshape(n_rays * n_pts, *v.shape[1:]))
+        sdf = fill(sdf_v, 1).index_copy(0, idx, sdf_v).view(n_rays, n_pts)
+        rad = fill(rad_v, 3).index_copy(0, idx, rad_v).view(n_rays, n_pts, 3)
+        nrm = fill(nrm_v, 3).index_copy(0, idx, nrm_v).view(n_rays, n_pts, 3)
         return sdf, rad, nrm
 
     def _forward_pts_dir(self, pts, rays_d):
