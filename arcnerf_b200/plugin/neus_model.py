@@ -23,7 +23,7 @@ import torch.nn.functional as tnf
 
 from . import ray_helper as rh
 from .linear_network_module import GeoNet
-from .obj_bound import VolumeBound
+from .obj_bound import VolumeBound, build_obj_bound
 from .registry import MODEL_REGISTRY, MODULE_REGISTRY, cfg_to_dict
 from .tcnn_fusedmlp_module import FusedMLPRadianceNet  # noqa: F401  (registers the module)
 
@@ -51,7 +51,6 @@ class Neus(nn.Module):
                              inverse_linear=_get(rays, 'inverse_linear', False), perturb=_get(rays, 'perturb', False),
                              add_inf_z=_get(rays, 'add_inf_z', False), noise_std=_get(rays, 'noise_std', 0.0),
                              white_bkg=_get(rays, 'white_bkg', False), radius_bound=_get(rays, 'radius_bound', 1.5))
-        assert self.ray_cfgs['n_importance'] == 0, 'Neus.upsample_zvals (n_importance > 0) is not provided'
         assert not self.ray_cfgs['add_inf_z'], 'Do not add_inf_z for sdf modeling'          # neus_model.py: the sdf models assert the same
         self.render_cfgs = dict(bkg_color=_get(bound, 'bkg_color', [1.0, 1.0, 1.0]), depth_far=_get(bound, 'depth_far', 10.0),
                                 normal=_get(bound, 'normal', [0.0, 1.0, 0.0]))
@@ -61,7 +60,7 @@ class Neus(nn.Module):
         self.speed_factor = _get(params, 'speed_factor', 10)
         self.inv_s = nn.Parameter(torch.tensor([-np.log(_get(params, 'init_var', 0.05)) / self.speed_factor], dtype=torch.float32))
         self.anneal_end = _get(params, 'anneal_end', 0)
-        self.obj_bound = VolumeBound(bound)
+        self.obj_bound, _ = build_obj_bound(c) if c.get('obj_bound') is not None else (VolumeBound(bound), 'volume')
         self.to(device)
 
     # ------------------------------------------------------------------------------------------ small accessors
@@ -86,7 +85,12 @@ class Neus(nn.Module):
         with torch.no_grad():
             near, far, mask_rays = self.obj_bound.get_near_far_from_rays({'rays_o': rays_o, 'rays_d': rays_d})
             zvals, mask_pts = self.obj_bound.get_zvals_from_near_far(near, far, self.ray_cfgs['n_sample'], inference_only,
+                                                                     self.ray_cfgs['inverse_linear'], self.ray_cfgs['perturb'],
                                                                      rays_o=rays_o, rays_d=rays_d)
+            if mask_pts is None:                          # bounds without an occupancy structure (sphere / near-far): every sample counts
+                mask_pts = torch.ones(zvals.shape, dtype=torch.bool, device=zvals.device)
+            if mask_rays is None:
+                mask_rays = torch.ones(n_rays, dtype=torch.bool, device=zvals.device)
             # the three data-dependent decisions of FgModel.forward (longest ray, any / all rays valid) in ONE host read
             per_ray = mask_pts.sum(dim=1)
             valid0 = torch.logical_and(mask_rays, per_ray > 0)
@@ -208,7 +212,44 @@ class Neus(nn.Module):
             rgb[mask], normal[mask] = rgb_m.detach().float(), normal_m.detach().float()
         return {'rgb': rgb, 'depth': zvals, 'mask': mask.float(), 'normal': normal}
 
+    @torch.no_grad()
+    def forward_pts(self, pts):
+        """sdf at world points (N, 3) -> (N,) in chunks of chunk_pts (SdfModel.forward_pts, sdf_model.py:19-40)"""
+        out = [self.geo_net.forward_geo_value(pts[a:a + self.chunk_pts]) for a in range(0, pts.shape[0], self.chunk_pts)]
+        return out[0] if len(out) == 1 else torch.cat(out, 0)
+
+    @torch.no_grad()
+    def upsample_zvals(self, rays_o, rays_d, zvals, mask_pts=None, inference_only=False, s=32):
+        """neus_model.py:106-171: n_iter rounds of inverse-CDF re-sampling where the SDF drops fastest along the ray (eq. 13 of the
+        NeuS paper); the SDF network, sdf_to_alpha, the inverse-CDF gather and the row sort run on the library's kernels"""
+        c = self.ray_cfgs
+        if c['n_importance'] <= 0:
+            return zvals, mask_pts
+        n_per_iter = c['n_importance'] // c['n_iter']
+        det = (not c['perturb']) if not inference_only else True
+        for i in range(c['n_iter']):
+            n_rays, n_pts = zvals.shape
+            pts = rh.get_ray_points_by_zvals(rays_o, rays_d, zvals)                    # (B, N, 3)
+            sdf = self.forward_pts(pts.view(-1, 3)).view(n_rays, n_pts)
+            prev_sdf, next_sdf = sdf[:, :-1], sdf[:, 1:]
+            mid_sdf = (prev_sdf + next_sdf) * 0.5
+            slope = (next_sdf - prev_sdf) / (zvals[:, 1:] - zvals[:, :-1] + 1e-5)
+            prev_slope = torch.cat([torch.zeros((n_rays, 1), dtype=zvals.dtype, device=zvals.device), slope[:, :-1]], dim=-1)
+            slope = torch.minimum(prev_slope, slope).clamp(-10.0, 0.0)
+            radius = torch.norm(pts, dim=-1)
+            inside = (radius[:, :-1] < c['radius_bound']) | (radius[:, 1:] < c['radius_bound'])
+            slope = slope * inside
+            alpha = rh.sdf_to_alpha(mid_sdf.contiguous(), zvals.contiguous(), slope.contiguous(), float(s * (2 ** (i + 1))), clip=False)
+            _, weights = rh.alpha_to_weights(alpha)
+            new = rh.sample_pdf(zvals, weights, n_per_iter, det).detach()
+            zvals = rh.sort_rows(torch.cat([zvals, new], dim=-1))
+            if mask_pts is not None:                      # merge_full_mask (fg_model.py:390-406): the new samples are all valid
+                count = mask_pts.sum(dim=1, keepdim=True) + new.shape[1]
+                mask_pts = torch.arange(zvals.shape[1], device=zvals.device)[None, :] < count
+        return zvals, mask_pts
+
     def _forward(self, rays_o, rays_d, zvals, mask_pts, bkg_color, inference_only, get_progress, cur_epoch):
+        zvals, mask_pts = self.upsample_zvals(rays_o, rays_d, zvals, mask_pts, inference_only)
         mid_zvals, zvals, mask_mid = self.handle_mid_pts(zvals, mask_pts)
         sdf, radiance, normal_pts = self.get_sdf_radiance_normal_by_mask_pts(rays_o, rays_d, mid_zvals, mask_mid)
         cos_anneal = 1.0 if inference_only else self.get_cos_anneal(cur_epoch)

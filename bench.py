@@ -195,6 +195,7 @@ def main():
     ap.add_argument('--no-render', action='store_true')
     ap.add_argument('--occ-every', type=int, default=16, help='occupancy refresh period in steps (0 = never); the reference config uses 16')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-prefetch', action='store_true', help='march every batch on the main stream (measures what the side-stream sampler prefetch hides)')
     ap.add_argument('--stages', action='store_true', help='print the per-stage timing table to stderr')
     ap.add_argument('--config', default='ngp', choices=['ngp', 'nerf', 'neus', 'ngp_nerfpp', 'mesh'],
                     help="ngp: BASELINE configs[1] (the headline); nerf: the vanilla-NeRF step of configs[0] (bench_nerf.py); neus: the NeuS-NGP step "
@@ -300,7 +301,7 @@ def main():
     e0.record()
     for i in range(K):
         o, d, t, b = resident[W + i]
-        nxt = resident[W + i + 1][:2] if i + 1 < K else None      # the trainer knows its next batch: sample it meanwhile
+        nxt = resident[W + i + 1][:2] if (i + 1 < K and not args.no_prefetch) else None      # the trainer knows its next batch: sample it meanwhile
         pipe.train_step(o, d, t, b, next_rays=nxt)
         maybe_refresh(i)
     e1.record()

@@ -104,3 +104,33 @@ def test_training_with_eikonal_term_and_occupancy_refresh():
     model.optimize(cur_epoch=16)
     occ = float(model.obj_bound.volume.bitfield.float().mean())
     assert 0.0 <= occ <= 1.0
+
+
+def test_vanilla_neus_upsampling_and_render_match_reference_model():
+    """The frequency-embedded, sphere-bounded NeuS of configs/models/neus.yaml (narrower networks, tests/neus_cases.py) with the
+    reference model's own weights: the hierarchical up-sampling (upsample_zvals, neus_model.py:106-171) and the rendered outputs
+    against the reference model run on CPU (tests/golden/make_golden_neus.py)."""
+    import os
+    import neus_cases as nc
+    from arcnerf_b200.plugin.neus_model import Neus
+    G = np.load(os.path.join(os.path.dirname(__file__), 'golden', 'neus_golden.npz'))
+    model = Neus(nc.CFG)
+    sd = {k[3:]: torch.from_numpy(G[k]) for k in G.files if k.startswith('sd/')}
+    missing, unexpected = model.load_state_dict(sd, strict=False)
+    assert not unexpected and all('embed' in k or 'freq' in k for k in missing), (missing, unexpected)
+    o, d = nc.rays()
+    ro, rd = torch.from_numpy(o).cuda(), torch.from_numpy(d).cuda()
+    with torch.no_grad():
+        near, far, mask_rays = model.obj_bound.get_near_far_from_rays({'rays_o': ro, 'rays_d': rd})
+        zvals, mask_pts = model.obj_bound.get_zvals_from_near_far(near, far, 32, True, False, False, rays_o=ro, rays_d=rd)
+        assert mask_pts is None and np.array_equal(mask_rays.cpu().numpy(), G['mask_rays'])
+        assert np.allclose(zvals.cpu().numpy(), G['zvals'], atol=1e-5)
+        z_up, m_up = model.upsample_zvals(ro, rd, zvals, None, inference_only=True)
+        out = model({'rays_o': ro, 'rays_d': rd}, inference_only=True)
+    assert z_up.shape == (nc.N_RAYS, 64) and m_up is None
+    hit = G['mask_rays']
+    # the SDF network runs in fp32 on both sides; an inverse-CDF sample moves with the CDF, which is steep near the surface
+    dz = np.abs(z_up.cpu().numpy() - G['z_up'])[hit]
+    assert np.median(dz) < 1e-5 and dz.max() < 5e-3
+    for k, tol in (('rgb', 5e-3), ('mask', 5e-3), ('depth', 2e-2), ('normal', 3e-2)):
+        assert np.abs(out[k].cpu().numpy() - G['out/' + k])[hit].max() < tol, k
