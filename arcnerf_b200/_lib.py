@@ -101,6 +101,8 @@ _SIGS = {
     'arcb200_mc_count': [P, I, I, I, F, I, P, P, P],
     'arcb200_mc_emit': [P, I, I, I, F, I, P, P, P, P, P, P, P, L, P, L, P],
     'arcb200_mesh_components': [P, P, L, L, P, P, P, P],
+    'arcb200_raster_scratch_bytes': [I, I, I, P],
+    'arcb200_raster_mesh': [P, P, P, P, P, P, I, I, I, F, F, P, P, P, P, L, L, P],
     'arcb200_trace_update': [P, P, P, P, P, I, P, P, F, L, P],
     'arcb200_surface_finish': [P, P, P, P, I, P, L, P],
     'arcb200_secant_steps': [P, P, P, P, I, I, P, P, L, P],

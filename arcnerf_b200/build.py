@@ -39,6 +39,7 @@ SOURCES = {
     'small_gemm.cu': [],
     'mcubes.cu': ['-fmad=false'],
     'surface.cu': ['-fmad=false'],
+    'raster.cu': ['-fmad=false'],
 }
 
 

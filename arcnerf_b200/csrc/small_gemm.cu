@@ -15,17 +15,22 @@ namespace {
 constexpr int kRowsPerBlock = 128;
 constexpr int kMaxDim = 128;
 
-// one thread per row: its K inputs in registers, the small matrix in shared memory (read as a broadcast)
+// one thread per row: its K inputs in registers; the small matrix sits in shared memory with rows padded to a multiple of four
+// and is read as broadcast float4s, four output columns at a time (16 FMAs per four 16-byte shared loads)
 template <int KMAX>
 __global__ void __launch_bounds__(kRowsPerBlock) gemm_nt_kernel(int64_t n, int N, int K, const float *__restrict__ A, int64_t lda,
                                                                  const float *__restrict__ B, int64_t ldb, const float *__restrict__ bias,
                                                                  float *__restrict__ C, int64_t ldc) {
     arc_pdl_sync();
-    extern __shared__ float sm[];
-    float *Bs = sm;                                   // N x K
-    float *tile = sm + N * K;                         // 128 x (max(K, N) + 1): the input rows, then the output rows
+    extern __shared__ __align__(16) float sm[];
+    const int Kp = (K + 3) & ~3, Np = (N + 3) & ~3;
+    float *Bs = sm;                                   // Np x Kp, zero padded
+    float *tile = sm + Np * Kp;                       // 128 x (max(K, N) + 1): the input rows, then the output rows
     const int pitch = (K > N ? K : N) + 1;
-    for (int e = threadIdx.x; e < N * K; e += blockDim.x) Bs[e] = B[(size_t)(e / K) * ldb + (e % K)];
+    for (int e = threadIdx.x; e < Np * Kp; e += blockDim.x) {
+        const int j = e / Kp, k = e - j * Kp;
+        Bs[e] = (j < N && k < K) ? B[(size_t)j * ldb + k] : 0.f;
+    }
     for (int64_t row0 = (int64_t)blockIdx.x * kRowsPerBlock; row0 < n; row0 += (int64_t)gridDim.x * kRowsPerBlock) {
         __syncthreads();
         const int rows = (int)((n - row0) < kRowsPerBlock ? (n - row0) : kRowsPerBlock);
@@ -39,12 +44,24 @@ __global__ void __launch_bounds__(kRowsPerBlock) gemm_nt_kernel(int64_t n, int N
         #pragma unroll
         for (int k = 0; k < KMAX; ++k) a[k] = (k < K && r < rows) ? tile[r * pitch + k] : 0.f;
         __syncthreads();
-        for (int j = 0; j < N; ++j) {
-            float acc = bias ? bias[j] : 0.f;
+        for (int j = 0; j < Np; j += 4) {
+            float acc[4];
             #pragma unroll
-            for (int k = 0; k < KMAX; ++k)
-                if (k < K) acc = fmaf(a[k], Bs[j * K + k], acc);
-            tile[r * pitch + j] = acc;
+            for (int q = 0; q < 4; ++q) acc[q] = (bias && j + q < N) ? bias[j + q] : 0.f;
+            #pragma unroll
+            for (int k = 0; k < KMAX; k += 4) {
+                if (k < Kp) {
+                    #pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        const float4 w = *reinterpret_cast<const float4 *>(Bs + (j + q) * Kp + k);
+                        acc[q] = fmaf(a[k], w.x, acc[q]); acc[q] = fmaf(a[k + 1], w.y, acc[q]);
+                        acc[q] = fmaf(a[k + 2], w.z, acc[q]); acc[q] = fmaf(a[k + 3], w.w, acc[q]);
+                    }
+                }
+            }
+            #pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (j + q < N) tile[r * pitch + j + q] = acc[q];
         }
         __syncthreads();
         for (int e = threadIdx.x; e < rows * N; e += blockDim.x) {
@@ -54,46 +71,58 @@ __global__ void __launch_bounds__(kRowsPerBlock) gemm_nt_kernel(int64_t n, int N
     }
 }
 
-// every thread owns up to 16 entries of the small result and walks the rows of the block's slab through shared memory
+// the small result is cut into 4 x 4 register tiles; the 256 threads form G groups of (tiles) threads, group g takes the rows
+// r = g (mod G) of the block's 64-row slab (two 16-byte shared loads per 16 FMAs); one atomic flush per thread at the end
 __global__ void __launch_bounds__(256) gemm_tn_kernel(int64_t n, int N, int K, const float *__restrict__ A, int64_t lda,
                                                        const float *__restrict__ B, int64_t ldb, float *__restrict__ C, int64_t ldc) {
     arc_pdl_sync();
-    extern __shared__ float sm[];
+    extern __shared__ __align__(16) float sm[];
     constexpr int kSlab = 64;
-    float *As = sm;                      // 64 x N
-    float *Bs = sm + kSlab * N;          // 64 x K
-    float acc[16];
+    const int Np = (N + 3) & ~3, Kp = (K + 3) & ~3;
+    float *As = sm;                      // 64 x Np, zero padded
+    float *Bs = sm + kSlab * Np;         // 64 x Kp
+    const int tiles_k = Kp / 4, tiles = (Np / 4) * tiles_k;          // <= 256 (N * K <= 4096)
+    const int G = 256 / tiles > 0 ? 256 / tiles : 1;
+    const int tile_id = threadIdx.x % tiles, g = threadIdx.x / tiles;
+    const bool active = g < G;
+    const int i0 = (tile_id / tiles_k) * 4, j0 = (tile_id % tiles_k) * 4;
+    float acc[4][4];
     #pragma unroll
-    for (int q = 0; q < 16; ++q) acc[q] = 0.f;
+    for (int p = 0; p < 4; ++p)
+        #pragma unroll
+        for (int q = 0; q < 4; ++q) acc[p][q] = 0.f;
     const int64_t slabs = (n + kSlab - 1) / kSlab;
     for (int64_t s = blockIdx.x; s < slabs; s += gridDim.x) {
         const int64_t row0 = s * kSlab;
         const int rows = (int)((n - row0) < kSlab ? (n - row0) : kSlab);
         __syncthreads();
-        for (int e = threadIdx.x; e < kSlab * N; e += blockDim.x) {
-            const int r = e / N, c = e - r * N;
-            As[e] = r < rows ? A[(row0 + r) * lda + c] : 0.f;
+        for (int e = threadIdx.x; e < kSlab * Np; e += blockDim.x) {
+            const int r = e / Np, c = e - r * Np;
+            As[e] = (r < rows && c < N) ? A[(row0 + r) * lda + c] : 0.f;
         }
-        for (int e = threadIdx.x; e < kSlab * K; e += blockDim.x) {
-            const int r = e / K, c = e - r * K;
-            Bs[e] = r < rows ? B[(row0 + r) * ldb + c] : 0.f;
+        for (int e = threadIdx.x; e < kSlab * Kp; e += blockDim.x) {
+            const int r = e / Kp, c = e - r * Kp;
+            Bs[e] = (r < rows && c < K) ? B[(row0 + r) * ldb + c] : 0.f;
         }
         __syncthreads();
-        #pragma unroll
-        for (int q = 0; q < 16; ++q) {
-            const int e = threadIdx.x + q * 256;
-            if (e < N * K) {
-                const int i = e / K, j = e - i * K;
-                float v = acc[q];
-                for (int r = 0; r < kSlab; ++r) v = fmaf(As[r * N + i], Bs[r * K + j], v);
-                acc[q] = v;
+        if (active) {
+            for (int r = g; r < kSlab; r += G) {
+                const float4 av = *reinterpret_cast<const float4 *>(As + r * Np + i0);
+                const float4 bv = *reinterpret_cast<const float4 *>(Bs + r * Kp + j0);
+                const float aa[4] = {av.x, av.y, av.z, av.w}, bb[4] = {bv.x, bv.y, bv.z, bv.w};
+                #pragma unroll
+                for (int p = 0; p < 4; ++p)
+                    #pragma unroll
+                    for (int q = 0; q < 4; ++q) acc[p][q] = fmaf(aa[p], bb[q], acc[p][q]);
             }
         }
     }
-    #pragma unroll
-    for (int q = 0; q < 16; ++q) {
-        const int e = threadIdx.x + q * 256;
-        if (e < N * K && acc[q] != 0.f) atomicAdd(C + (size_t)(e / K) * ldc + (e % K), acc[q]);
+    if (active) {
+        #pragma unroll
+        for (int p = 0; p < 4; ++p)
+            #pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (i0 + p < N && j0 + q < K && acc[p][q] != 0.f) atomicAdd(C + (size_t)(i0 + p) * ldc + (j0 + q), acc[p][q]);
     }
 }
 
@@ -124,7 +153,7 @@ int arcb200_gemm_nt(const float *A, int64_t lda, const float *B, int64_t ldb, co
     ARC_REQUIRE(n >= 0 && N >= 1 && K >= 1 && N <= kMaxDim && K <= kMaxDim, "gemm_nt: the small dimensions must lie in [1, %d]", kMaxDim);
     if (n == 0) return ARCB200_OK;
     ARC_REQUIRE(A && B && C && lda >= K && ldb >= K && ldc >= N, "gemm_nt: null pointer or leading dimension too small");
-    const size_t smem = ((size_t)N * K + (size_t)kRowsPerBlock * ((K > N ? K : N) + 1)) * sizeof(float);
+    const size_t smem = ((size_t)((N + 3) & ~3) * ((K + 3) & ~3) + (size_t)kRowsPerBlock * ((K > N ? K : N) + 1)) * sizeof(float);
     long long blocks = (n + kRowsPerBlock - 1) / kRowsPerBlock;
     const long long cap = (long long)arc_sm_count() * 4;
     const unsigned grid = (unsigned)(blocks < cap ? blocks : cap);
@@ -138,19 +167,26 @@ int arcb200_gemm_nt(const float *A, int64_t lda, const float *B, int64_t ldb, co
     return ARCB200_OK;
 }
 
-// C (N x K, ldc) += A^T . B with A (n x N, lda), B (n x K, ldb); the caller zeroes C.  N * K <= 4096.
+// C (N x K, ldc) += A^T . B with A (n x N, lda), B (n x K, ldb); the caller zeroes C.  N, K <= 128; a result of more than 256
+// register tiles (4 x 4) is produced in several launches over row ranges of C.
 // Replaces the weight-gradient GEMM autograd runs for nn.Linear.
 int arcb200_gemm_tn(const float *A, int64_t lda, const float *B, int64_t ldb, float *C, int64_t ldc, int64_t n, int N, int K,
                     void *stream) {
-    ARC_REQUIRE(n >= 0 && N >= 1 && K >= 1 && N <= kMaxDim && K <= kMaxDim && N * K <= 4096, "gemm_tn: small dimensions out of range (N * K <= 4096)");
+    ARC_REQUIRE(n >= 0 && N >= 1 && K >= 1 && N <= kMaxDim && K <= kMaxDim, "gemm_tn: the small dimensions must lie in [1, %d]", kMaxDim);
     if (n == 0) return ARCB200_OK;
     ARC_REQUIRE(A && B && C && lda >= N && ldb >= K && ldc >= K, "gemm_tn: null pointer or leading dimension too small");
-    const size_t smem = (size_t)64 * (N + K) * sizeof(float);
+    const int tiles_k = (K + 3) / 4;
+    const int rows_per_launch = (256 / tiles_k) * 4;                 // rows of C whose tiles fit one CTA
     long long slabs = (n + 63) / 64;
     const long long cap = (long long)arc_sm_count() * 4;
-    if (smem > 48 * 1024) ARC_CUDA(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    arc_launch(gemm_tn_kernel, (unsigned)(slabs < cap ? slabs : cap), 256, smem, (cudaStream_t)stream, n, N, K, A, lda, B, ldb, C, ldc);
-    ARC_LAUNCH_CHECK();
+    for (int c0 = 0; c0 < N; c0 += rows_per_launch) {
+        const int Nc = N - c0 < rows_per_launch ? N - c0 : rows_per_launch;
+        const size_t smem = (size_t)64 * (((Nc + 3) & ~3) + ((K + 3) & ~3)) * sizeof(float);
+        if (smem > 48 * 1024) ARC_CUDA(cudaFuncSetAttribute(gemm_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        arc_launch(gemm_tn_kernel, (unsigned)(slabs < cap ? slabs : cap), 256, smem, (cudaStream_t)stream, n, Nc, K, A + c0, lda, B, ldb,
+                   C + (size_t)c0 * ldc, ldc);
+        ARC_LAUNCH_CHECK();
+    }
     return ARCB200_OK;
 }
 

@@ -70,3 +70,33 @@ def get_mesh_components(verts, faces):
         _lib.call('arcb200_mesh_components', verts.data_ptr(), faces.data_ptr(), n_v, n_f, fn.data_ptr(), fc.data_ptr(), vn.data_ptr(),
                   _lib.current_stream())
     return vn, fn, fc
+
+
+def render_mesh_images(verts, faces, vert_colors, face_colors, vert_normals, face_normals, H, W, w2c, intrinsic, backend='b200',
+                       single_image_mode=False, device='cuda', sil_mode=False, sil_hard=True, return_buffers=False):
+    """arcnerf/geometry/mesh.py:174-240 render_mesh_images with the same arguments; `backend` is ignored (the one rasteriser of
+    this build, csrc/raster.cu, replaces both open3d and pytorch3d; normals are accepted and unused: the colours are unlit).
+    Returns images (N, H, W, 3) uint8 as numpy (sil_mode: the silhouette, covered pixels white on black like the reference's
+    hard silhouette); return_buffers=True adds the face-id and depth buffers (device tensors)."""
+    dev = torch.device(device if str(device) != 'gpu' else 'cuda')
+    t = lambda a, dt: (a.to(dev, dt) if torch.is_tensor(a) else torch.as_tensor(np.asarray(a), dtype=dt, device=dev)).contiguous()
+    v, f = t(verts, torch.float32), t(faces, torch.int32)
+    cams = t(w2c, torch.float32).reshape(-1, 4, 4).contiguous()
+    n_views = cams.shape[0]
+    vc = t(vert_colors, torch.float32) if (vert_colors is not None and not sil_mode) else None
+    fc = t(face_colors, torch.float32) if (face_colors is not None and vert_colors is None and not sil_mode) else None
+    k = (C.c_float * 9)(*[float(x) for x in np.asarray(intrinsic.cpu() if torch.is_tensor(intrinsic) else intrinsic, np.float64).reshape(-1)])
+    nbytes = C.c_int64()
+    _lib.call('arcb200_raster_scratch_bytes', n_views, int(H), int(W), C.byref(nbytes))
+    scratch = torch.empty(max(1, nbytes.value), dtype=torch.uint8, device=dev)
+    image = torch.empty((n_views, H, W, 3), dtype=torch.uint8, device=dev)
+    fid = torch.empty((n_views, H, W), dtype=torch.int32, device=dev)
+    depth = torch.empty((n_views, H, W), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        _lib.call('arcb200_raster_mesh', v.data_ptr(), f.data_ptr(), _lib.ptr(vc), _lib.ptr(fc), cams.data_ptr(), k, n_views, int(H), int(W),
+                  1e-6, 0.0 if sil_mode else 1.0, scratch.data_ptr(), image.data_ptr(), fid.data_ptr(), depth.data_ptr(), v.shape[0],
+                  f.shape[0], _lib.current_stream())
+    if sil_mode:
+        image = ((fid >= 0).to(torch.uint8) * 255)[..., None].expand(-1, -1, -1, 3).contiguous()
+    out = image.cpu().numpy()
+    return (out, fid, depth) if return_buffers else out

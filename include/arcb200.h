@@ -553,12 +553,24 @@ int arcb200_secant_update(const float *geo_mid, float level, int descent, const 
 int arcb200_secant_select(const uint8_t *mask, const uint8_t *not_occ, const float *z_mid, const float *far, int far_per_ray,
                           float *zvals, int64_t n_rays, void *stream);
 
+/* ---- mesh preview rasteriser (csrc/raster.cu) --------------------------------------------------------------------------------
+ * Replaces the pytorch3d renderer behind render_mesh_images (arcnerf/geometry/mesh.py:174-240, arcnerf/render/
+ * render_pytorch3d.py; blur radius 0, one face per pixel): n_views pinhole views (w2c DEVICE (n_views,4,4); intrinsic HOST 3x3)
+ * of a mesh with vertex colours (V,3), face colours (F,3) or neither (silhouette), image (n_views,H,W,3) uint8 on background
+ * `bkg` (0..1), optional winning face id (n_views,H,W) int32 (-1: none) and depth.  Nearest face per pixel centre through a 64-bit
+ * atomicMin z-buffer (scratch: arcb200_raster_scratch_bytes); faces with a vertex at z <= near are skipped; unlit colours
+ * (pytorch3d's Phong lighting is not reproduced). */
+int arcb200_raster_scratch_bytes(int n_views, int H, int W, int64_t *bytes);
+int arcb200_raster_mesh(const float *verts, const int32_t *faces, const float *vert_colors, const float *face_colors, const float *w2c,
+                        const float *intrinsic, int n_views, int H, int W, float near, float bkg, void *scratch, uint8_t *image,
+                        int32_t *face_id, float *depth, int64_t n_v, int64_t n_f, void *stream);
+
 /* ---- narrow dense layers in fp32 (csrc/small_gemm.cu) -------------------------------------------------------------------
  * The SDF network of the NeuS-NGP configuration (32 -> 64 softplus(100) -> 17, weight-normed, GeoNet of
  * geo_rad_model/linear_network_module.py:17-197 with DenseLayer = nn.Linear + activation, base_modules/linear.py) and the
  * derivative passes autograd builds for forward_with_grad and the eikonal loss (base_network.py:30-44).
  * arcb200_gemm_nt: C (n x N) = A (n x K) . B^T (+ bias), B (N x K), N, K <= 128.   arcb200_gemm_tn: C (N x K) += A^T . B with
- * A (n x N), B (n x K), N * K <= 4096 (caller zeroes C).   arcb200_softplus: order-th derivative (0, 1, 2) of softplus_beta. */
+ * A (n x N), B (n x K), N, K <= 128 (caller zeroes C).   arcb200_softplus: order-th derivative (0, 1, 2) of softplus_beta. */
 int arcb200_gemm_nt(const float *A, int64_t lda, const float *B, int64_t ldb, const float *bias, float *C, int64_t ldc, int64_t n,
                     int N, int K, void *stream);
 int arcb200_gemm_tn(const float *A, int64_t lda, const float *B, int64_t ldb, float *C, int64_t ldc, int64_t n, int N, int K,

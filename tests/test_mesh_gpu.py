@@ -168,3 +168,43 @@ def test_slab_sharded_extraction_tiles_the_whole_mesh():
         if fs_.shape[0]:
             assert int(fs_.max()) < vs_.shape[0]
     assert n_faces == f.shape[0] and f.shape[0] > 0
+
+
+def _look_at(eye, target=(0.0, 0.0, 0.0)):
+    eye, target = np.asarray(eye, np.float64), np.asarray(target, np.float64)
+    fwd = target - eye
+    fwd /= np.linalg.norm(fwd)
+    right = np.cross(fwd, np.array([0.0, 0.0, 1.0]))
+    right /= np.linalg.norm(right)
+    down = np.cross(fwd, right)
+    c2w = np.eye(4)
+    c2w[:3, 0], c2w[:3, 1], c2w[:3, 2], c2w[:3, 3] = right, down, fwd, eye
+    return np.linalg.inv(c2w).astype(np.float32)
+
+
+def test_mesh_rasteriser_equals_restatement():
+    """csrc/raster.cu against oracle/raster.py on an extracted sphere mesh seen from three cameras (one inside the mesh, so that
+    faces behind the near plane are skipped): face-id buffer, depth and colours"""
+    from arcnerf_b200.plugin.mesh import extract_mesh, render_mesh_images
+    from oracle import raster as orr
+    vol, vs, vl = sphere_volume(24, 0.6)
+    v, f, n = extract_mesh(vol, 50.0, vs, vl)
+    vc = (0.5 + 0.5 * n).astype(np.float32)
+    H, W = 48, 64
+    K = np.array([[70.0, 0, W / 2], [0, 70.0, H / 2], [0, 0, 1]], np.float32)
+    w2c = np.stack([_look_at((2.0, 0.3, 0.4)), _look_at((-0.5, 1.8, -0.7)), _look_at((0.1, 0.0, 0.05), (1.0, 0.2, 0.0))])
+    img, fid, depth = render_mesh_images(v, f, vc, None, n, None, H, W, w2c, K, return_buffers=True)
+    r_img, r_fid, r_depth = orr.raster_mesh(v, f, w2c, K, H, W, vert_colors=vc)
+    assert img.shape == (3, H, W, 3) and img.dtype == np.uint8
+    assert np.array_equal(fid.cpu().numpy(), r_fid) and (r_fid[0] >= 0).sum() > 200 and (r_fid[0] < 0).sum() > 200
+    assert np.array_equal(depth.cpu().numpy().view(np.uint32), r_depth.view(np.uint32))
+    assert np.abs(img.astype(np.int32) - r_img.astype(np.int32)).max() <= 1           # fp32 colour blend -> the uint8 rounding edge
+    # face colours and silhouette
+    fc = np.random.RandomState(0).uniform(0, 1, (len(f), 3)).astype(np.float32)
+    img2 = render_mesh_images(v, f, None, fc, None, None, H, W, w2c[:1], K)
+    assert np.array_equal(img2, orr.raster_mesh(v, f, w2c[:1], K, H, W, face_colors=fc)[0])
+    sil = render_mesh_images(v, f, vc, None, None, None, H, W, w2c[:1], K, sil_mode=True)
+    assert np.array_equal(sil[0, :, :, 0] > 0, r_fid[0] >= 0)
+    # empty mesh: background only
+    empty = render_mesh_images(np.zeros((0, 3), np.float32), np.zeros((0, 3), np.int32), None, None, None, None, 8, 8, w2c[:1], K)
+    assert (empty == 255).all()
