@@ -191,9 +191,11 @@ march_warp_kernel(uint32_t n_rays, const float *__restrict__ rays_o, const float
 }
 
 // ------------------------------------------------------------------------------------------------
-// Cascaded (multi-volume) bitfield march with cone stepping: one thread per ray, the reference's control
-// flow (multivol_func_kernel.cu:19-106).  The inner-volume reset makes the step sequence data dependent,
-// so the chain trick above does not apply without re-basing; this sampler is off the NGP headline path.
+// Cascaded (multi-volume) bitfield march with cone stepping (multivol_func_kernel.cu:19-106).  The step depends on the distance
+// (cone stepping) and the inner-volume reset makes the sequence data dependent, so the chain trick above does not apply: the
+// march itself stays one thread per ray.  What the whole warp does together is the dense (n_rays, n_pts) output: a thread
+// stores only the samples it finds; masks and the padded tails of the warp's 32 rows are then written with coalesced stores,
+// and the reference's per-entry clearing loops are gone (every entry they touch is rewritten by the padding).
 __device__ __forceinline__ int mip_level(F3 p, const Box &inner, uint32_t n_cascades) {
     const float cx = (inner.lo.x + inner.hi.x) / 2.0f, cy = (inner.lo.y + inner.hi.y) / 2.0f,
                 cz = (inner.lo.z + inner.hi.z) / 2.0f;
@@ -228,39 +230,58 @@ __global__ void march_multivol_kernel(uint32_t n_rays, const float *__restrict__
                                       float *__restrict__ zvals, uint8_t *__restrict__ mask) {
     arc_pdl_sync();
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_rays) return;
-    const Box inner = load_box(min_aabb), outer = load_box(aabb);
-    Pcg32 rng;
-    rng.state = rng_state;
-    rng.inc = rng_inc;
-    rng.advance((uint64_t)(int64_t)(i * 8u));
-    const F3 o = load3(rays_o + 3 * (size_t)i), d = load3(rays_d + 3 * (size_t)i);
-    float t = fmaxf(near[i], near_distance);
-    const float t_end = far[i];
-    t = t + cone_step(t, cone, smin, smax) * rng.next_f32();
+    const uint32_t lane = threadIdx.x & 31u;
+    const bool live = i < n_rays;
     uint32_t j = 0;
-    float *z = zvals + (size_t)i * n_pts;
-    uint8_t *m = mask + (size_t)i * n_pts;
-    while (t <= t_end && j < n_pts) {
-        const F3 p = ray_at(o, d, t);
-        if (!inside(p, outer)) break;
-        const float dt = cone_step(t, cone, smin, smax);
-        const uint32_t mip = (uint32_t)mip_level(p, inner, n_cascade);
-        if (mip == 0 && !inclusive) {
-            for (uint32_t k = 0; k <= j; ++k) { z[k] = 0.0f; m[k] = 0; }
-            j = 0;
-            const float target = t + next_voxel_distance(p, d, inner, n_grid);
-            do { t = t + dt; } while (t < target);
-        } else if (occupied_cascade(p, bits, mip, inner, n_grid, inclusive != 0)) {
-            z[j] = t; m[j] = 1; ++j;
-            t = t + dt;
-        } else {
-            const float target = t + next_voxel_distance(p, d, inner, n_grid);
-            do { t = t + cone_step(t, cone, smin, smax); } while (t < target);
+    float pad = 0.0f;
+    if (live) {
+        const Box inner = load_box(min_aabb), outer = load_box(aabb);
+        Pcg32 rng;
+        rng.state = rng_state;
+        rng.inc = rng_inc;
+        rng.advance((uint64_t)(int64_t)(i * 8u));
+        const F3 o = load3(rays_o + 3 * (size_t)i), d = load3(rays_d + 3 * (size_t)i);
+        float t = fmaxf(near[i], near_distance);
+        const float t_end = far[i];
+        t = t + cone_step(t, cone, smin, smax) * rng.next_f32();
+        float *z = zvals + (size_t)i * n_pts;
+        while (t <= t_end && j < n_pts) {
+            const F3 p = ray_at(o, d, t);
+            if (!inside(p, outer)) break;
+            const float dt = cone_step(t, cone, smin, smax);
+            const uint32_t mip = (uint32_t)mip_level(p, inner, n_cascade);
+            if (mip == 0 && !inclusive) {
+                // back inside the foreground volume: the samples so far are dropped.  (The reference clears them one by one,
+                // multivol_func_kernel.cu:60-66; every entry from the new count on is rewritten by the padding below.)
+                j = 0;
+                const float target = t + next_voxel_distance(p, d, inner, n_grid);
+                do { t = t + dt; } while (t < target);
+            } else if (occupied_cascade(p, bits, mip, inner, n_grid, inclusive != 0)) {
+                z[j] = t; ++j;
+                pad = t;
+                t = t + dt;
+            } else {
+                const float target = t + next_voxel_distance(p, d, inner, n_grid);
+                do { t = t + cone_step(t, cone, smin, smax); } while (t < target);
+            }
+        }
+        if (j == 0) pad = 0.0f;
+    }
+    // the dense rows are finished by the whole warp, ray by ray: mask = [1] * count + [0] * rest, distances padded with the last
+    // sample - coalesced 128-byte stores instead of up to n_pts scattered ones per thread
+    __syncwarp();
+    const uint32_t ray0 = i - lane;
+    for (uint32_t r = 0; r < 32; ++r) {
+        const uint32_t cnt = __shfl_sync(ARC_FULL_MASK, j, r);
+        const float pv = __shfl_sync(ARC_FULL_MASK, pad, r);
+        if (ray0 + r >= n_rays) break;
+        float *z = zvals + (size_t)(ray0 + r) * n_pts;
+        uint8_t *m = mask + (size_t)(ray0 + r) * n_pts;
+        for (uint32_t k = lane; k < n_pts; k += 32) {
+            if (k >= cnt) z[k] = pv;
+            m[k] = k < cnt ? 1 : 0;
         }
     }
-    const float pad = j > 0 ? z[j - 1] : 0.0f;
-    for (uint32_t k = j; k < n_pts; ++k) { z[k] = pad; m[k] = 0; }
 }
 
 // ------------------------------------------------------------------------------------------------
