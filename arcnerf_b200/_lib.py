@@ -100,6 +100,7 @@ _SIGS = {
     'arcb200_mc_scratch_sizes': [I, I, I, P],
     'arcb200_mc_count': [P, I, I, I, F, I, P, P, P],
     'arcb200_mc_emit': [P, I, I, I, F, I, P, P, P, P, P, P, P, L, P, L, P],
+    'arcb200_check_increasing': [P, L, I, P, P],
     'arcb200_mesh_components': [P, P, L, L, P, P, P, P],
     'arcb200_raster_scratch_bytes': [I, I, I, P],
     'arcb200_raster_mesh': [P, P, P, P, P, P, I, I, I, F, F, P, P, P, P, L, L, P],

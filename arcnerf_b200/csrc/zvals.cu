@@ -127,6 +127,18 @@ __global__ void ray_points_kernel(size_t n_rays, int n_pts, const float *__restr
     pts[3 * i + 2] = rays_o[3 * ray + 2] + rays_d[3 * ray + 2] * z;
 }
 
+// the reference's `assert torch.all(deltas >= 0)` of ray_marching (ray_helper.py:532-534) as a device-side flag: deltas below 1e-5 in
+// magnitude count as zero; a negative (or NaN) interval sets flag[0].  The host reads the flag without stalling the stream.
+__global__ void check_increasing_kernel(size_t n_rays, int p, const float *__restrict__ zvals, int32_t *__restrict__ flag) {
+    arc_pdl_sync();
+    const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < 2 || k >= n_rays * (size_t)(p - 1)) return;
+    const size_t r = k / (p - 1), c = k - r * (p - 1);
+    float d = zvals[r * p + c + 1] - zvals[r * p + c];
+    if (fabsf(d) < 1e-5f) d = 0.0f;
+    if (!(d >= 0.0f)) atomicOr(flag, 1);
+}
+
 // one CTA per row: ascending bitonic sort of `n` floats in shared memory (n_pow2 = next power of two, padded with +inf)
 __global__ void sort_rows_kernel(int n, int n_pow2, const float *in, float *out) {
     arc_pdl_sync();
@@ -203,6 +215,17 @@ int arcb200_ray_points(const float *rays_o, const float *rays_d, const float *zv
     ARC_REQUIRE(rays_o && rays_d && zvals && pts, "ray_points: null pointer");
     arc_launch(ray_points_kernel, arc_blocks(n_rays * n_pts, 256), 256, 0, (cudaStream_t)stream, (size_t)n_rays, n_pts, rays_o,
                rays_d, zvals, pts);
+    ARC_LAUNCH_CHECK();
+    return ARCB200_OK;
+}
+
+// flag[0] |= 1 when some row of zvals (n_rays, p) decreases by 1e-5 or more (or holds a NaN): ray_marching's assertion
+// (ray_helper.py:532-534) evaluated on the device; the caller clears the flag and reads it when convenient.
+int arcb200_check_increasing(const float *zvals, int64_t n_rays, int p, int32_t *flag, void *stream) {
+    ARC_REQUIRE(n_rays >= 0 && p >= 0 && flag, "check_increasing: bad argument");
+    if (n_rays == 0 || p < 2) return ARCB200_OK;
+    ARC_REQUIRE(zvals != nullptr, "check_increasing: null zvals");
+    arc_launch(check_increasing_kernel, arc_blocks(n_rays * (p - 1), 256), 256, 0, (cudaStream_t)stream, (size_t)n_rays, p, zvals, flag);
     ARC_LAUNCH_CHECK();
     return ARCB200_OK;
 }

@@ -2,6 +2,8 @@
 """Drop-in for the integration functions of arcnerf/render/ray_helper.py (ray_marching :476-593, alpha_to_weights
 :596-620, sample_pdf / sample_cdf :410-473) and arcnerf/models/neus_model.py:sdf_to_alpha (:242-265), differentiable,
 on libarcb200's segmented-scan kernels instead of ~15 eager torch ops over padded tensors."""
+import os
+
 import torch
 
 from .. import _lib
@@ -39,6 +41,59 @@ class _CompositeFn(torch.autograd.Function):
         return d_geo, d_rad, None, None, None, None, None, None
 
 
+class _DeferredZvalsAssert:
+    """ray_marching's `assert torch.all(deltas >= 0), 'zvals is not all increase....'` (ray_helper.py:532-534) without the host
+    synchronisation it costs in the reference: the check runs as one small kernel that raises a device flag, the flag travels to
+    pinned host memory behind it, and the AssertionError is raised by the first later call that finds the copy complete (or by
+    check_zvals_assert(), which waits).  ARCB200_STRICT_ASSERTS=1 waits at once, like the reference."""
+
+    def __init__(self):
+        self.state = {}
+
+    def _slot(self, dev):
+        if dev not in self.state:
+            self.state[dev] = dict(flag=torch.zeros(1, dtype=torch.int32, device=dev), host=torch.zeros(1, dtype=torch.int32).pin_memory(),
+                                   event=torch.cuda.Event(), pending=False)
+        return self.state[dev]
+
+    def poll(self, dev, wait=False):
+        st = self.state.get(dev)
+        if st is None or not st['pending']:
+            return
+        if wait:
+            st['event'].synchronize()
+        if st['event'].query():
+            st['pending'] = False
+            if int(st['host'][0]) != 0:
+                st['flag'].zero_()
+                st['host'].zero_()
+                raise AssertionError('zvals is not all increase....')
+
+    def submit(self, zvals):
+        if not zvals.is_cuda or zvals.dim() != 2:
+            return
+        dev = zvals.device
+        self.poll(dev)
+        st = self._slot(dev)
+        z = _f32(zvals.detach())
+        with torch.cuda.device(dev):
+            _lib.call('arcb200_check_increasing', z.data_ptr(), z.shape[0], z.shape[1], st['flag'].data_ptr(), _lib.current_stream())
+            st['host'].copy_(st['flag'], non_blocking=True)
+            st['event'].record()
+        st['pending'] = True
+        if os.environ.get('ARCB200_STRICT_ASSERTS', '0') == '1':
+            self.poll(dev, wait=True)
+
+
+_zvals_assert = _DeferredZvalsAssert()
+
+
+def check_zvals_assert(device=None):
+    """wait for the pending monotonicity checks of ray_marching and raise the reference's AssertionError if one failed"""
+    for dev in ([torch.device(device)] if device is not None else list(_zvals_assert.state)):
+        _zvals_assert.poll(dev, wait=True)
+
+
 def ray_marching(sigma, radiance, zvals, add_inf_z=False, noise_std=0.0, weights_only=False, white_bkg=False, alpha=None,
                  bkg_color=None):
     """Same arguments and output dict as arcnerf.render.ray_helper.ray_marching (:476-593)."""
@@ -47,10 +102,7 @@ def ray_marching(sigma, radiance, zvals, add_inf_z=False, noise_std=0.0, weights
     geo = alpha if is_alpha else sigma
     p = zvals.shape[1]
     m = p if (is_alpha or add_inf_z) else p - 1
-    with torch.no_grad():
-        deltas = zvals[:, 1:] - zvals[:, :-1]
-        deltas = torch.where(deltas.abs() < 1e-5, torch.zeros_like(deltas), deltas)
-        assert torch.all(deltas >= 0), 'zvals is not all increase....'
+    _zvals_assert.submit(zvals)
     noise = None
     if not is_alpha and noise_std > 0.0:
         noise = torch.randn(geo.shape, dtype=torch.float32, device=geo.device) * noise_std

@@ -404,6 +404,9 @@ int arcb200_zvals_fix_step(const float *near, const float *far, float fix_t, int
 /* arcnerf/geometry/ray.py:11-30 get_ray_points_by_zvals. */
 int arcb200_ray_points(const float *rays_o, const float *rays_d, const float *zvals, float *pts, int64_t n_rays, int n_pts,
                        void *stream);
+/* ray_marching's `assert torch.all(deltas >= 0)` (ray_helper.py:532-534) as a device-side flag: flag[0] |= 1 when a row of zvals
+ * (n_rays, p) decreases by 1e-5 or more or holds a NaN.  The caller clears the flag and reads it without stalling the stream. */
+int arcb200_check_increasing(const float *zvals, int64_t n_rays, int p, int32_t *flag, void *stream);
 /* torch.sort(torch.cat([zvals, new_zvals], -1), -1) of NeRF/NeuS upsample_zvals (nerf_model.py:112, neus_model.py:171):
  * ascending sort of every row, n <= 8192, out may alias in. */
 int arcb200_sort_rows(const float *in, float *out, int64_t n_rows, int n, void *stream);

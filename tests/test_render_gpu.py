@@ -207,3 +207,25 @@ def test_fused_composite_huber_train_equals_three_kernels(mode):
     assert torch.equal(dg1, dg2) and torch.equal(dr1, dr2)
     assert abs(float(loss1) - float(loss2)) <= 2e-6 * abs(float(loss1))
     assert float(dg2.abs().max()) > 0 and int(counter) == 42
+
+
+def test_ray_marching_reports_decreasing_zvals_without_stalling():
+    """the reference asserts `zvals is not all increase....` (ray_helper.py:532-534) with a host synchronisation; here the check is a
+    device flag read one call later (or by check_zvals_assert), immediately under ARCB200_STRICT_ASSERTS=1"""
+    from arcnerf_b200.plugin import ray_helper as rh
+    good = torch.linspace(1.0, 2.0, 16, device='cuda')[None].repeat(8, 1).contiguous()
+    bad = good.clone()
+    bad[3, 7] = 0.5
+    sigma, rad = torch.rand((8, 16), device='cuda'), torch.rand((8, 16, 3), device='cuda')
+    rh.check_zvals_assert()
+    rh.ray_marching(sigma, rad, good)
+    rh.check_zvals_assert()                                  # nothing pending fails
+    rh.ray_marching(sigma, rad, bad)                         # queued, not raised yet
+    with pytest.raises(AssertionError, match='zvals is not all increase'):
+        rh.check_zvals_assert()
+    rh.ray_marching(sigma, rad, good)
+    rh.check_zvals_assert()                                  # the flag was cleared by the raise
+    nearly = good.clone()
+    nearly[2, 5] = nearly[2, 4] - 5e-6                       # |delta| < 1e-5 counts as zero (ray_helper.py:533)
+    rh.ray_marching(sigma, rad, nearly)
+    rh.check_zvals_assert()
