@@ -84,7 +84,8 @@ def run(args, rank, world, dev, dist, read_peaks, ClockSampler):
     e1.record()
     barrier()
     ms_total = max_over_ranks(e0.elapsed_time(e1))
-    loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+    from bench_common import LossReader
+    reader = LossReader()
     dbuf = [torch.empty_like(x, device=dev) for x in batches[0]]
     barrier()
     e0.record()
@@ -92,8 +93,8 @@ def run(args, rank, world, dev, dist, read_peaks, ClockSampler):
         for dst, src in zip(dbuf, batches[W + i]):
             dst.copy_(src, non_blocking=True)
         loss = train_step(*dbuf)
-        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        reader.push(loss)
+    reader.finish()
     e1.record()
     barrier()
     ms_e2e = max_over_ranks(e0.elapsed_time(e1))
@@ -112,7 +113,7 @@ def run(args, rank, world, dev, dist, read_peaks, ClockSampler):
                         l2='per-step working set (hash-table gradient + Adam state, 0.2 GB) exceeds the 126 MB L2; every step draws new rays',
                         gradient_exchange='NCCL all-reduce per parameter tensor (48.8 MB hash-table gradient + 5 small tensors)' if world > 1 else 'single GPU'),
             e2e=dict(value=N_RAYS * world * K / (ms_e2e * 1e-3), unit=UNIT, h2d_bytes_per_step=h2d, d2h_bytes_per_step=4, ms_per_step=ms_e2e / K,
-                     path='host pinned buffers -> H2D per step -> Neus.forward + losses + backward (incl. second order) + Adam -> loss D2H + sync'),
+                     path='host pinned buffers -> H2D per step -> Neus.forward + losses + backward (incl. second order) + Adam -> loss D2H every step, read by the host one step behind'),
             gpu_launches=K * 60,
             clocks=clock_info,
             roofline=dict(kernel='adam_kernel on the hash table (dense sweep, the largest fixed cost of the step)', bound='hbm', achieved=None,

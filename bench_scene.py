@@ -125,7 +125,8 @@ def run_ngp_nerfpp(args, rank, world, dev, dist, read_peaks, ClockSampler):
     e1.record()
     barrier()
     ms_total = max_over_ranks(e0.elapsed_time(e1))
-    loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+    from bench_common import LossReader
+    reader = LossReader()
     dbuf = [torch.empty_like(x, device=dev) for x in batches[0]]
     barrier()
     e0.record()
@@ -133,8 +134,8 @@ def run_ngp_nerfpp(args, rank, world, dev, dist, read_peaks, ClockSampler):
         for dst, src in zip(dbuf, batches[W + i]):
             dst.copy_(src, non_blocking=True)
         loss = train_step(*dbuf)
-        loss_host.copy_(loss.detach().reshape(1), non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        reader.push(loss)
+    reader.finish()
     e1.record()
     barrier()
     ms_e2e = max_over_ranks(e0.elapsed_time(e1))
@@ -153,7 +154,7 @@ def run_ngp_nerfpp(args, rank, world, dev, dist, read_peaks, ClockSampler):
                         l2='every step draws new rays; the hash-table gradient + Adam state (0.2 GB) exceed the 126 MB L2'),
             e2e=dict(value=N_RAYS * world * K / (ms_e2e * 1e-3), unit='rays/s', h2d_bytes_per_step=sum(t.numel() * 4 for t in batches[0]),
                      d2h_bytes_per_step=4, ms_per_step=ms_e2e / K,
-                     path='pinned host rays/targets -> H2D -> FullModel.forward (NeRF++ bkg, NGP fg with fused blend) + loss + backward + Adam -> loss D2H'),
+                     path='pinned host rays/targets -> H2D -> FullModel.forward (NeRF++ bkg, NGP fg with fused blend) + loss + backward + Adam -> loss D2H every step, read by the host one step behind'),
             gpu_launches=K * 70, clocks=clock_info,
             roofline=dict(kernel='dense_chain_kernel (8x256 background networks, 524 288 points per step)', bound='tensor', achieved=None,
                           peak=peaks.get('bf16_tflops'), unit='TFLOP/s', frac=None, traffic=None, bkg_chain_flops_per_step=flops,
