@@ -191,11 +191,7 @@ march_warp_kernel(uint32_t n_rays, const float *__restrict__ rays_o, const float
 }
 
 // ------------------------------------------------------------------------------------------------
-// Cascaded (multi-volume) bitfield march with cone stepping (multivol_func_kernel.cu:19-106).  The step depends on the distance
-// (cone stepping) and the inner-volume reset makes the sequence data dependent, so the chain trick above does not apply: the
-// march itself stays one thread per ray.  What the whole warp does together is the dense (n_rays, n_pts) output: a thread
-// stores only the samples it finds; masks and the padded tails of the warp's 32 rows are then written with coalesced stores,
-// and the reference's per-entry clearing loops are gone (every entry they touch is rewritten by the padding).
+// Cascaded (multi-volume) bitfield march with cone stepping (multivol_func_kernel.cu:19-106); the kernel is below the helpers.
 __device__ __forceinline__ int mip_level(F3 p, const Box &inner, uint32_t n_cascades) {
     const float cx = (inner.lo.x + inner.hi.x) / 2.0f, cy = (inner.lo.y + inner.hi.y) / 2.0f,
                 cz = (inner.lo.z + inner.hi.z) / 2.0f;
@@ -221,66 +217,141 @@ __device__ __forceinline__ bool occupied_cascade(F3 p, const uint8_t *__restrict
 }
 __device__ __forceinline__ float cone_step(float t, float cone, float lo, float hi) { return clampf(t * cone, lo, hi); }
 
-__global__ void march_multivol_kernel(uint32_t n_rays, const float *__restrict__ rays_o,
-                                      const float *__restrict__ rays_d, const float *__restrict__ near,
-                                      const float *__restrict__ far, const float *__restrict__ min_aabb,
-                                      const float *__restrict__ aabb, const uint8_t *__restrict__ bits, uint32_t n_grid, uint32_t n_cascade,
-                                      uint32_t n_pts, float cone, float smin, float smax, float near_distance,
-                                      int inclusive, uint64_t rng_state, uint64_t rng_inc,
-                                      float *__restrict__ zvals, uint8_t *__restrict__ mask) {
+// One warp per ray.  Between two visits of the inner volume the reference's loop only ever stands on links of the chain
+// c_0 = t_start, c_{k+1} = fl(c_k + clamp(c_k * cone, smin, smax)): an occupied link steps to the next one, an empty link walks
+// the same chain up to its skip target.  So, as in march_warp_kernel, the 32 lanes evaluate 32 consecutive links at once (32
+// cascade look-ups in flight), ballots and pointer doubling resolve which links the reference would have visited, and occupied
+// visited links are emitted with warp-level compaction.  A visited link inside the inner volume (exclusive mode) leaves the
+// chain - the reference then steps with the FIXED step of that link - so the chunk ends there, the sample count is reset and
+// the chain is re-based on the point that loop reaches.
+__global__ void __launch_bounds__(256)
+march_multivol_kernel(uint32_t n_rays, const float *__restrict__ rays_o, const float *__restrict__ rays_d,
+                      const float *__restrict__ near, const float *__restrict__ far, const float *__restrict__ min_aabb,
+                      const float *__restrict__ aabb, const uint8_t *__restrict__ bits, uint32_t n_grid, uint32_t n_cascade,
+                      uint32_t n_pts, float cone, float smin, float smax, float near_distance, int inclusive,
+                      uint64_t rng_state, uint64_t rng_inc, float *__restrict__ zvals, uint8_t *__restrict__ mask) {
     arc_pdl_sync();
-    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t ray = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const uint32_t lane = threadIdx.x & 31u;
-    const bool live = i < n_rays;
-    uint32_t j = 0;
-    float pad = 0.0f;
-    if (live) {
-        const Box inner = load_box(min_aabb), outer = load_box(aabb);
+    if (ray >= n_rays) return;
+    const Box inner = load_box(min_aabb), outer = load_box(aabb);
+    const F3 o = load3(rays_o + 3 * (size_t)ray), d = load3(rays_d + 3 * (size_t)ray);
+    const float t_end = far[ray];
+    float chain = fmaxf(near[ray], near_distance);
+    {
         Pcg32 rng;
         rng.state = rng_state;
         rng.inc = rng_inc;
-        rng.advance((uint64_t)(int64_t)(i * 8u));
-        const F3 o = load3(rays_o + 3 * (size_t)i), d = load3(rays_d + 3 * (size_t)i);
-        float t = fmaxf(near[i], near_distance);
-        const float t_end = far[i];
-        t = t + cone_step(t, cone, smin, smax) * rng.next_f32();
-        float *z = zvals + (size_t)i * n_pts;
-        while (t <= t_end && j < n_pts) {
-            const F3 p = ray_at(o, d, t);
-            if (!inside(p, outer)) break;
-            const float dt = cone_step(t, cone, smin, smax);
-            const uint32_t mip = (uint32_t)mip_level(p, inner, n_cascade);
-            if (mip == 0 && !inclusive) {
-                // back inside the foreground volume: the samples so far are dropped.  (The reference clears them one by one,
-                // multivol_func_kernel.cu:60-66; every entry from the new count on is rewritten by the padding below.)
-                j = 0;
-                const float target = t + next_voxel_distance(p, d, inner, n_grid);
-                do { t = t + dt; } while (t < target);
-            } else if (occupied_cascade(p, bits, mip, inner, n_grid, inclusive != 0)) {
-                z[j] = t; ++j;
-                pad = t;
-                t = t + dt;
-            } else {
-                const float target = t + next_voxel_distance(p, d, inner, n_grid);
-                do { t = t + cone_step(t, cone, smin, smax); } while (t < target);
+        rng.advance((uint64_t)(int64_t)(ray * 8u));
+        chain = chain + cone_step(chain, cone, smin, smax) * rng.next_f32();
+    }
+    float *z_row = zvals + (size_t)ray * n_pts;
+    uint8_t *m_row = mask + (size_t)ray * n_pts;
+    uint32_t emitted = 0;
+    float reach = -CUDART_INF_F, last_t = 0.0f;
+    bool done = false;
+    const uint32_t lane_lt = (1u << lane) - 1u;
+    uint32_t chunks = 0;
+    while (!done) {
+        if (++chunks > (1u << 17)) break;                 // a step too small to move t never terminates in the reference either
+        // While the next visit is the very link the chain stands on and that link lies in the inner volume (exclusive mode), the
+        // reference resets and re-bases link after link (a camera inside the foreground box crosses about a hundred voxels this
+        // way): pure arithmetic, done by all lanes alike without building a 32-link chunk for each of them.
+        if (!inclusive) {
+            uint32_t guard = 0;
+            while (!(chain < reach) && chain <= t_end && ++guard < (1u << 20)) {
+                const F3 p0 = ray_at(o, d, chain);
+                if (!inside(p0, outer) || mip_level(p0, inner, n_cascade) != 0) break;
+                const float target = chain + next_voxel_distance(p0, d, inner, n_grid);
+                const float dt0 = cone_step(chain, cone, smin, smax);
+                float t = chain;
+                uint32_t g2 = 0;
+                do { t = t + dt0; } while (t < target && ++g2 < (1u << 22));
+                emitted = 0;
+                chain = t;
+                reach = -CUDART_INF_F;
             }
         }
-        if (j == 0) pad = 0.0f;
-    }
-    // the dense rows are finished by the whole warp, ray by ray: mask = [1] * count + [0] * rest, distances padded with the last
-    // sample - coalesced 128-byte stores instead of up to n_pts scattered ones per thread
-    __syncwarp();
-    const uint32_t ray0 = i - lane;
-    for (uint32_t r = 0; r < 32; ++r) {
-        const uint32_t cnt = __shfl_sync(ARC_FULL_MASK, j, r);
-        const float pv = __shfl_sync(ARC_FULL_MASK, pad, r);
-        if (ray0 + r >= n_rays) break;
-        float *z = zvals + (size_t)(ray0 + r) * n_pts;
-        uint8_t *m = mask + (size_t)(ray0 + r) * n_pts;
-        for (uint32_t k = lane; k < n_pts; k += 32) {
-            if (k >= cnt) z[k] = pv;
-            m[k] = k < cnt ? 1 : 0;
+        float mine = chain;
+        #pragma unroll
+        for (uint32_t s = 0; s < 32; ++s) {
+            if (s == lane) mine = chain;
+            chain = chain + cone_step(chain, cone, smin, smax);
         }
+        const F3 p = ray_at(o, d, mine);
+        const bool live = (mine <= t_end) && inside(p, outer);
+        bool occ = false, reset = false;
+        if (live) {
+            const uint32_t mip = (uint32_t)mip_level(p, inner, n_cascade);
+            if (mip == 0 && !inclusive) reset = true;
+            else occ = occupied_cascade(p, bits, mip, inner, n_grid, inclusive != 0);
+        }
+        const float skip_to = mine + next_voxel_distance(p, d, inner, n_grid);
+        const uint32_t live_mask = __ballot_sync(ARC_FULL_MASK, live);
+        const uint32_t occ_mask = __ballot_sync(ARC_FULL_MASK, occ);
+        const uint32_t reset_mask = __ballot_sync(ARC_FULL_MASK, reset);
+        const uint32_t cand = __ballot_sync(ARC_FULL_MASK, !(mine < reach));
+        if (cand == 0) continue;                          // the next visit lies in a later chunk
+        const uint32_t entry = __ffs(cand) - 1;
+        uint32_t hop;
+        {
+            uint32_t lo = 0;
+            #pragma unroll
+            for (uint32_t step = 16; step >= 1; step >>= 1) {
+                const float probe = __shfl_sync(ARC_FULL_MASK, mine, lo + step - 1);
+                if (probe < skip_to) lo += step;
+            }
+            const float c31 = __shfl_sync(ARC_FULL_MASK, mine, 31);
+            if (lo == 31 && c31 < skip_to) lo = 32;
+            hop = occ ? lane + 1 : max(lane + 1, lo);
+            if (reset || !live) hop = 32;                 // the walk ends on such a link
+        }
+        uint32_t visited = 1u << entry;
+        #pragma unroll
+        for (int r = 0; r < 5; ++r) {
+            const uint32_t add = (((visited >> lane) & 1u) && hop < 32) ? (1u << hop) : 0u;
+            visited |= __reduce_or_sync(ARC_FULL_MASK, add);
+            const uint32_t hop2 = __shfl_sync(ARC_FULL_MASK, hop, hop & 31u);
+            hop = hop < 32 ? hop2 : 32u;
+        }
+        // the walk inside this chunk ends at the first visited link that is dead (past `far` / outside) or inside the inner volume
+        const uint32_t stop = visited & (~live_mask | reset_mask);
+        uint32_t valid = visited;
+        int stop_lane = -1;
+        if (stop) { stop_lane = __ffs(stop) - 1; valid &= (1u << stop_lane) - 1u; }
+        const uint32_t emit = valid & occ_mask;
+        const uint32_t room = n_pts - emitted;
+        const uint32_t rank = __popc(emit & lane_lt);
+        const bool write = ((emit >> lane) & 1u) && rank < room;
+        if (write) z_row[emitted + rank] = mine;
+        const uint32_t wrote = __ballot_sync(ARC_FULL_MASK, write);
+        if (wrote) {
+            last_t = __shfl_sync(ARC_FULL_MASK, mine, 31 - __clz(wrote));
+            emitted += __popc(wrote);
+        }
+        if (emitted >= n_pts) { done = true; continue; }  // the reference's `j < n_pts` ends the loop before the next link is looked at
+        if (stop_lane >= 0) {
+            if (!((live_mask >> stop_lane) & 1u)) { done = true; continue; }
+            // inner volume: samples so far are dropped, then fixed steps of this link's size up to its skip target
+            const float ti = __shfl_sync(ARC_FULL_MASK, mine, stop_lane);
+            const float target = __shfl_sync(ARC_FULL_MASK, skip_to, stop_lane);
+            const float dti = cone_step(ti, cone, smin, smax);
+            float t = ti;
+            uint32_t guard = 0;
+            do { t = t + dti; } while (t < target && ++guard < (1u << 22));
+            emitted = 0;
+            chain = t;
+            reach = -CUDART_INF_F;
+            continue;
+        }
+        const uint32_t last = 31 - __clz(valid);
+        const float carry = __shfl_sync(ARC_FULL_MASK, skip_to, last);
+        reach = ((occ_mask >> last) & 1u) ? -CUDART_INF_F : carry;
+    }
+    const float pad = emitted > 0 ? last_t : 0.0f;
+    for (uint32_t k = lane; k < n_pts; k += 32) {
+        if (k >= emitted) z_row[k] = pad;
+        m_row[k] = k < emitted ? 1 : 0;
     }
 }
 
@@ -483,7 +554,7 @@ int arcb200_sparse_sampling_in_multivol_bitfield(const float *rays_o, const floa
     ARC_REQUIRE(rays_o && rays_d && near && far && min_aabb && aabb && bitfield && zvals && mask,
                 "multivol sampling: null pointer");
     ARC_REQUIRE(n_pts > 0 && n_grid > 0 && n_cascade > 0 && min_step > 0.0f, "multivol sampling: invalid sizes/steps");
-    arc_launch(march_multivol_kernel, arc_blocks(n_rays, 128), 128, 0, (cudaStream_t)stream, 
+    arc_launch(march_multivol_kernel, arc_blocks(n_rays * 32, 256), 256, 0, (cudaStream_t)stream, 
         (uint32_t)n_rays, rays_o, rays_d, near, far, min_aabb, aabb, bitfield,
         (uint32_t)n_grid, (uint32_t)n_cascade, (uint32_t)n_pts, cone_angle, min_step, max_step, near_distance,
         inclusive, rng_state, rng_inc, zvals, mask);
