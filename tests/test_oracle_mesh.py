@@ -74,3 +74,28 @@ def test_vertices_lie_on_the_level_set_of_the_trilinear_edges():
     t = idx[np.arange(len(v)), ax] - lo[np.arange(len(v)), ax]
     val = vol[lo[:, 0], lo[:, 1], lo[:, 2]] * (1 - t) + vol[hi[:, 0], hi[:, 1], hi[:, 2]] * t
     assert np.abs(val - level).max() < 2e-2 * np.abs(vol).max()
+
+
+def test_raster_restatement_covers_the_projected_sphere():
+    """oracle/raster.py on an extracted sphere: the covered pixels form the projected disc, depth runs from the near pole to the
+    silhouette, colours are the interpolated vertex colours, a camera inside the mesh skips the faces behind its near plane"""
+    from oracle import raster as orr
+    n, r = 24, 0.6
+    vol, vs, vl = sphere_volume(n, r)
+    v, f, nr = M.extract_mesh(vol, 50.0, vs, vl)
+    H, W, foc, dist = 48, 64, 70.0, 2.0
+    K = np.array([[foc, 0, W / 2], [0, foc, H / 2], [0, 0, 1]], np.float32)
+    w2c = np.eye(4, dtype=np.float32)
+    w2c[2, 3] = dist                                          # camera on the -z axis looking along +z
+    img, fid, depth = orr.raster_mesh(v, f, w2c[None], K, H, W, vert_colors=(0.5 + 0.5 * nr).astype(np.float32))
+    cov = fid[0] >= 0
+    # silhouette radius of a sphere seen from distance d: f r / sqrt(d^2 - r^2)
+    rad = foc * r / np.sqrt(dist * dist - r * r)
+    assert abs(cov.sum() / (np.pi * rad * rad) - 1) < 0.05
+    assert abs(depth[0][cov].min() - (dist - r)) < 0.02 and depth[0][cov].max() < dist
+    assert (img[0][~cov] == 255).all()
+    centre = img[0, H // 2, W // 2].astype(np.float32) / 255.0      # normal at the near pole is -z: colour (0.5, 0.5, 0)
+    assert np.abs(centre - np.array([0.5, 0.5, 0.0])).max() < 0.08
+    inside_cam = np.eye(4, dtype=np.float32)
+    _, fid2, depth2 = orr.raster_mesh(v, f, inside_cam[None], K, H, W)
+    assert (fid2[0] >= 0).all() and abs(depth2[0, H // 2, W // 2] - r) < 0.02      # only the far half is in front of the camera
