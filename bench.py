@@ -51,12 +51,15 @@ def read_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region.  index None: no sampling (ranks other
+    than 0 - eight nvidia-smi pollers beside eight host-bound training loops cost more than they tell)."""
 
     def __init__(self, index):
         self.index, self.proc, self.lines = index, None, []
 
     def start(self):
+        if self.index is None:
+            return
         q = ('clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,'
              'clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap')
         try:
@@ -278,7 +281,7 @@ def main():
         pipe.train_step(o, d, t, b)
     barrier()
 
-    clocks = ClockSampler(dev.index)
+    clocks = ClockSampler(dev.index if rank == 0 else None)
     clocks.start()
     # ---- timed: resident inputs
     occ_every = args.occ_every

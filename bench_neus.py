@@ -74,7 +74,7 @@ def run(args, rank, world, dev, dist, read_peaks, ClockSampler):
     for i in range(W):
         train_step(*resident[i])
     barrier()
-    clocks = ClockSampler(dev.index)
+    clocks = ClockSampler(dev.index if rank == 0 else None)
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()

@@ -115,7 +115,7 @@ def run_ngp_nerfpp(args, rank, world, dev, dist, read_peaks, ClockSampler):
     for i in range(W):
         train_step(*resident[i])
     barrier()
-    clocks = ClockSampler(dev.index)
+    clocks = ClockSampler(dev.index if rank == 0 else None)
     clocks.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -233,7 +233,7 @@ def run_mesh(args, rank, world, dev, dist, read_peaks, ClockSampler):
         frame()
         mesh()
     barrier()
-    clocks = ClockSampler(dev.index)
+    clocks = ClockSampler(dev.index if rank == 0 else None)
     clocks.start()
     e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
     t_frame, t_mesh = [], []
